@@ -1,0 +1,266 @@
+// C-ABI entry points of the SpMM path: plan (long-row split table), forward, backward-x,
+// and the slice fix-up kernel.  See include/dgl_b200.h for the contracts and
+// spmm_kernel.cuh for the kernel design.
+#include <string>
+
+#include "scan.cuh"
+#include "spmm_kernel.cuh"
+
+namespace dglb200 {
+
+// ---- long-row plan ---------------------------------------------------------------------------
+
+__global__ void plan_flag_rows(const int64_t* indptr, int64_t n_rows, int chunk, int32_t* is_long,
+                               int64_t* n_slices) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n_rows) return;
+  const int64_t d = indptr[r + 1] - indptr[r];
+  const bool lg = d > chunk;
+  is_long[r] = lg ? 1 : 0;
+  n_slices[r] = lg ? (d + chunk - 1) / chunk : 0;
+}
+
+__global__ void plan_emit(const int32_t* is_long, const int32_t* long_pos, const int64_t* slice_pos,
+                          int64_t n_rows, int64_t capacity, int32_t* long_rows, int64_t* chunk_ptr) {
+  int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r > n_rows) return;
+  if (r == n_rows) {  // terminator
+    const int32_t nl = long_pos[n_rows];
+    if (nl <= capacity) chunk_ptr[nl] = slice_pos[n_rows];
+    return;
+  }
+  if (is_long[r]) {
+    const int32_t k = long_pos[r];
+    if (k < capacity) {
+      long_rows[k] = (int32_t)r;
+      chunk_ptr[k] = slice_pos[r];
+    }
+  }
+}
+
+// y[row, f] = ordered reduce of the row's slices.  One thread per (long row, feature).
+template <typename T, int RED>
+__global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, int n_long,
+                           const float* partial, const int32_t* partial_arg, int64_t feat, T* y,
+                           int32_t* arg) {
+  const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int lr = blockIdx.y;
+  if (f >= feat || lr >= n_long) return;
+  const int64_t c0 = chunk_ptr[lr], c1 = chunk_ptr[lr + 1];
+  float acc = (RED == DGLB200_RED_MAX) ? -INFINITY : 0.f;
+  int32_t best = -1;
+  for (int64_t c = c0; c < c1; ++c) {
+    const float v = partial[c * feat + f];
+    if (RED == DGLB200_RED_SUM) {
+      acc += v;
+    } else if (c == c0 || v > acc) {
+      acc = v;
+      if (partial_arg) best = partial_arg[c * feat + f];
+    }
+  }
+  const int64_t row = long_rows[lr];
+  if (RED == DGLB200_RED_MAX && arg) arg[row * feat + f] = best;
+  if (sizeof(T) == 4) reinterpret_cast<float*>(y)[row * feat + f] = acc;
+  else reinterpret_cast<__nv_bfloat16*>(y)[row * feat + f] = __float2bfloat16_rn(acc);
+}
+
+SpmmTuning& spmm_tuning() {
+  static SpmmTuning t;
+  return t;
+}
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_plan_t* plan,
+                    cudaStream_t stream) {
+  a.chunk = 1 << 30;
+  a.n_long_rows = 0;
+  a.n_chunks = 0;
+  a.long_rows = nullptr;
+  a.chunk_ptr = nullptr;
+  a.partial = nullptr;
+  a.partial_arg = nullptr;
+  if (plan != nullptr && plan->n_long_rows > 0) {
+    DGLB200_REQUIRE(plan->chunk >= 32 && plan->chunk % 32 == 0, "spmm: plan chunk %d invalid",
+                    plan->chunk);
+    DGLB200_REQUIRE(plan->long_rows && plan->chunk_ptr && plan->partial,
+                    "spmm: plan with long rows needs long_rows, chunk_ptr and partial");
+    const size_t need = (size_t)plan->n_chunks * (size_t)a.feat * sizeof(float);
+    DGLB200_REQUIRE(plan->partial_bytes >= need, "spmm: plan partial buffer %zu < %zu bytes",
+                    plan->partial_bytes, need);
+    a.chunk = plan->chunk;
+    a.n_long_rows = plan->n_long_rows;
+    a.n_chunks = plan->n_chunks;
+    a.long_rows = plan->long_rows;
+    a.chunk_ptr = plan->chunk_ptr;
+    a.partial = static_cast<float*>(plan->partial);
+    a.partial_arg = (red == DGLB200_RED_MAX) ? plan->partial_arg : nullptr;
+    DGLB200_REQUIRE(!(red == DGLB200_RED_MAX && a.arg != nullptr && a.partial_arg == nullptr),
+                    "spmm: MAX with arg over a plan needs plan->partial_arg");
+  }
+  const int full_vec = dtype == DGLB200_F32 ? 4 : 8;
+  bool vec = a.feat % full_vec == 0 && aligned16(a.x) && aligned16(a.y);
+  if (a.w != nullptr && (a.w_mode == kWFull || msg == DGLB200_MSG_COPY_EDGE)) vec = vec && aligned16(a.w);
+  int rc = dtype == DGLB200_F32 ? launch_spmm_f32(a, msg, red, vec, stream)
+                                : launch_spmm_bf16(a, msg, red, vec, stream);
+  if (rc != 0) return rc;
+  if (a.n_long_rows > 0) {
+    dim3 grid((unsigned)ceil_div(a.feat, 128), (unsigned)a.n_long_rows);
+    DGLB200_REQUIRE(a.n_long_rows < 65536 * 1024, "spmm: too many long rows");
+    // grid.y is limited to 65535: fold the overflow into several launches
+    for (int base = 0; base < a.n_long_rows; base += 65535) {
+      const int n = min(65535, a.n_long_rows - base);
+      grid.y = (unsigned)n;
+#define FIX(T, R)                                                                          \
+  spmm_fixup<T, R><<<grid, 128, 0, stream>>>(a.long_rows + base, a.chunk_ptr + base, n,    \
+                                             a.partial, a.partial_arg, a.feat,             \
+                                             static_cast<T*>(a.y), a.arg)
+      if (dtype == DGLB200_F32) {
+        if (red == DGLB200_RED_SUM) FIX(float, DGLB200_RED_SUM); else FIX(float, DGLB200_RED_MAX);
+      } else {
+        if (red == DGLB200_RED_SUM) FIX(__nv_bfloat16, DGLB200_RED_SUM);
+        else FIX(__nv_bfloat16, DGLB200_RED_MAX);
+      }
+#undef FIX
+      DGLB200_POST_LAUNCH("spmm_fixup");
+    }
+  }
+  return 0;
+}
+
+}  // namespace dglb200
+
+using namespace dglb200;
+
+extern "C" {
+
+int dglb200_set_tuning(const char* key, int64_t value) {
+  clear_error();
+  DGLB200_REQUIRE(key != nullptr, "set_tuning: key is NULL");
+  SpmmTuning& t = spmm_tuning();
+  const std::string k(key);
+  if (k == "spmm_ucap") t.ucap = (int)value;
+  else if (k == "spmm_slab_chunks") t.slab_chunks = (int)value;
+  else if (k == "spmm_threads") t.threads = (int)value;
+  else {
+    set_error("set_tuning: unknown key '%s'", key);
+    return -1;
+  }
+  return 0;
+}
+
+int dglb200_spmm_plan_workspace_bytes(int64_t n_rows, size_t* bytes_host) {
+  DGLB200_REQUIRE(bytes_host != nullptr && n_rows >= 0, "spmm_plan_workspace_bytes: bad args");
+  size_t b = 0;
+  b += align_up((size_t)(n_rows + 1) * sizeof(int32_t)) * 2;  // is_long, long_pos
+  b += align_up((size_t)(n_rows + 1) * sizeof(int64_t)) * 2;  // n_slices, slice_pos
+  b += scan_workspace_bytes(n_rows + 1, sizeof(int64_t)) * 2;
+  *bytes_host = b + 1024;
+  return 0;
+}
+
+int dglb200_spmm_plan(int64_t n_rows, const int64_t* indptr, int32_t chunk, int64_t capacity,
+                      int32_t* long_rows, int64_t* chunk_ptr, int64_t* counts_host,
+                      void* workspace, size_t workspace_bytes, void* stream_) {
+  clear_error();
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  DGLB200_REQUIRE(n_rows >= 0 && n_rows < (1ll << 31), "spmm_plan: n_rows %lld out of range",
+                  (long long)n_rows);
+  DGLB200_REQUIRE(chunk >= 32 && chunk % 32 == 0, "spmm_plan: chunk must be a multiple of 32");
+  DGLB200_REQUIRE(counts_host != nullptr, "spmm_plan: counts_host is NULL");
+  counts_host[0] = counts_host[1] = 0;
+  if (n_rows == 0) return 0;
+  Workspace ws(workspace, workspace_bytes);
+  int32_t* is_long = ws.take<int32_t>(n_rows + 1);
+  int32_t* long_pos = ws.take<int32_t>(n_rows + 1);
+  int64_t* n_slices = ws.take<int64_t>(n_rows + 1);
+  int64_t* slice_pos = ws.take<int64_t>(n_rows + 1);
+  DGLB200_REQUIRE(is_long && long_pos && n_slices && slice_pos, "spmm_plan: workspace too small");
+  const unsigned blocks = (unsigned)ceil_div(n_rows + 1, 256);
+  plan_flag_rows<<<blocks, 256, 0, stream>>>(indptr, n_rows, chunk, is_long, n_slices);
+  DGLB200_POST_LAUNCH("plan_flag_rows");
+  if (exclusive_scan<int32_t, int32_t>(is_long, long_pos, n_rows, 1, ws, stream) != 0) return -1;
+  if (exclusive_scan<int64_t, int64_t>(n_slices, slice_pos, n_rows, 1, ws, stream) != 0) return -1;
+  int32_t n_long = 0;
+  int64_t n_sl = 0;
+  DGLB200_CUDA(cudaMemcpyAsync(&n_long, long_pos + n_rows, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+  DGLB200_CUDA(cudaMemcpyAsync(&n_sl, slice_pos + n_rows, sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
+  DGLB200_CUDA(cudaStreamSynchronize(stream));
+  counts_host[0] = n_long;
+  counts_host[1] = n_sl;
+  if (n_long == 0) return 0;
+  DGLB200_REQUIRE(long_rows != nullptr && chunk_ptr != nullptr && capacity >= n_long,
+                  "spmm_plan: capacity %lld < %d long rows", (long long)capacity, n_long);
+  plan_emit<<<blocks, 256, 0, stream>>>(is_long, long_pos, slice_pos, n_rows, capacity, long_rows,
+                                        chunk_ptr);
+  DGLB200_POST_LAUNCH("plan_emit");
+  return 0;
+}
+
+int dglb200_spmm_csr(int64_t n_rows, int64_t x_rows, int64_t nnz, const int64_t* indptr,
+                     const int32_t* indices, const int32_t* eids, int msg_op, int reduce_op,
+                     int dtype, const void* x, int64_t feat, const void* w, int64_t w_width,
+                     void* y, int32_t* arg, const dglb200_spmm_plan_t* plan, void* stream) {
+  clear_error();
+  DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && feat >= 1, "spmm_csr: bad sizes n_rows=%lld nnz=%lld feat=%lld",
+                  (long long)n_rows, (long long)nnz, (long long)feat);
+  DGLB200_REQUIRE(n_rows < (1ll << 31) && nnz < (1ll << 31) && x_rows < (1ll << 31),
+                  "spmm_csr: sizes must be < 2^31");
+  DGLB200_REQUIRE(dtype == DGLB200_F32 || dtype == DGLB200_BF16, "spmm_csr: unknown dtype %d", dtype);
+  DGLB200_REQUIRE(msg_op >= DGLB200_MSG_COPY_SRC && msg_op <= DGLB200_MSG_COPY_EDGE,
+                  "spmm_csr: unknown msg_op %d", msg_op);
+  DGLB200_REQUIRE(reduce_op == DGLB200_RED_SUM || reduce_op == DGLB200_RED_MAX,
+                  "spmm_csr: unknown reduce_op %d", reduce_op);
+  if (n_rows == 0) return 0;
+  DGLB200_REQUIRE(indptr != nullptr && y != nullptr, "spmm_csr: indptr / y is NULL");
+  DGLB200_REQUIRE(nnz == 0 || msg_op == DGLB200_MSG_COPY_EDGE || (indices != nullptr && x != nullptr),
+                  "spmm_csr: indices / x is NULL");
+  SpmmArgs a{};
+  a.n_rows = n_rows; a.indptr = indptr; a.indices = indices; a.eids = eids;
+  a.x = x; a.w = w; a.y = y; a.arg = arg; a.feat = feat;
+  a.w_width = 1; a.w_group = feat; a.w_mode = kWScalar;
+  if (msg_op != DGLB200_MSG_COPY_SRC) {
+    DGLB200_REQUIRE(nnz == 0 || w != nullptr, "spmm_csr: edge data w is NULL");
+    if (msg_op == DGLB200_MSG_COPY_EDGE) {
+      DGLB200_REQUIRE(w_width == feat, "spmm_csr: copy_edge needs w_width == feat (%lld != %lld)",
+                      (long long)w_width, (long long)feat);
+    } else {
+      DGLB200_REQUIRE(w_width >= 1 && feat % w_width == 0,
+                      "spmm_csr: w_width %lld must divide feat %lld", (long long)w_width, (long long)feat);
+    }
+    a.w_width = w_width;
+    a.w_group = feat / w_width;
+    a.w_mode = w_width == 1 ? kWScalar : (w_width == feat ? kWFull : kWGrouped);
+  } else {
+    a.w = nullptr;
+  }
+  if (reduce_op != DGLB200_RED_MAX) a.arg = nullptr;
+  return run_spmm(a, msg_op, reduce_op, dtype, plan, static_cast<cudaStream_t>(stream));
+}
+
+int dglb200_spmm_csr_backward_x(int64_t n_rows, int64_t nnz, const int64_t* indptr,
+                                const int32_t* indices, const int32_t* eids, int dtype,
+                                const void* dy, int64_t feat, const void* w, int64_t w_width,
+                                const int32_t* arg, void* dx, const dglb200_spmm_plan_t* plan,
+                                void* stream) {
+  clear_error();
+  DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && feat >= 1, "spmm_csr_backward_x: bad sizes");
+  DGLB200_REQUIRE(n_rows < (1ll << 31) && nnz < (1ll << 31), "spmm_csr_backward_x: sizes must be < 2^31");
+  DGLB200_REQUIRE(dtype == DGLB200_F32 || dtype == DGLB200_BF16, "spmm_csr_backward_x: unknown dtype");
+  if (n_rows == 0) return 0;
+  DGLB200_REQUIRE(indptr && dx && (nnz == 0 || (indices && dy)), "spmm_csr_backward_x: NULL pointer");
+  SpmmArgs a{};
+  a.n_rows = n_rows; a.indptr = indptr; a.indices = indices; a.eids = eids;
+  a.x = dy; a.w = w; a.y = dx; a.arg = const_cast<int32_t*>(arg); a.feat = feat;
+  a.w_width = 1; a.w_group = feat; a.w_mode = kWScalar;
+  if (w != nullptr) {
+    DGLB200_REQUIRE(w_width >= 1 && feat % w_width == 0, "spmm_csr_backward_x: w_width must divide feat");
+    a.w_width = w_width;
+    a.w_group = feat / w_width;
+    a.w_mode = w_width == 1 ? kWScalar : (w_width == feat ? kWFull : kWGrouped);
+  }
+  int msg = (arg != nullptr) ? (int)kMsgMasked : (w != nullptr ? (int)DGLB200_MSG_SRC_MUL_EDGE : (int)DGLB200_MSG_COPY_SRC);
+  return run_spmm(a, msg, DGLB200_RED_SUM, dtype, plan, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

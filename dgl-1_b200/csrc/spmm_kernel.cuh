@@ -1,0 +1,379 @@
+// Kernels (1) and (2): generalised message -> reduce SpMM over a CSR, sm_100a.
+//
+// Replaces SPMVExecutor.run / SPMVWithDataExecutor.run -> th.sparse.mm
+// (python/dgl/runtime/ir/executor.py:452-473,535-566; python/dgl/backend/pytorch/tensor.py:143-146)
+// and the builtin fallbacks of python/dgl/runtime/scheduler.py:540-570.
+//
+// Shape of the kernel (HBM/L2-bound gather-reduce; no tensor cores on purpose):
+//  * a WORK ITEM is one destination row, or one `chunk`-edge slice of a long row (plan).
+//    A group of G lanes owns an item; 32/G items per warp.  G*TILES*VEC features are covered
+//    per pass, wider rows are split into feature slabs along blockIdx.y (slab-major dispatch
+//    keeps one slab of x resident in the 126 MB L2 while every row is visited).
+//  * lanes read 16 B of the source row each (4 fp32 / 8 bf16): one 128-bit LDG, fully coalesced
+//    per edge.  Column ids (and edge ids / scalar weights) are read 'G at a time' by the group,
+//    coalesced, L1-bypassing, and broadcast with warp shuffles.
+//  * the edge loop is a two-stage software pipeline: the U x TILES 128-bit loads of step q+1 are
+//    issued before step q is accumulated, so no load waits behind a dependent FADD.
+//  * accumulation is fp32, sequential in slot order: for rows that fit one item this is the
+//    exact sequence of adds th.sparse.mm performs on the reference's COO (edge-id order).
+//  * long-row slices write fp32 partials; a fix-up kernel combines them in slice order
+//    (deterministic; no float atomics).
+#pragma once
+#include <type_traits>
+
+#include "common.cuh"
+
+namespace dglb200 {
+
+enum { kMsgMasked = 3 };  // internal: backward of MAX (gather form)
+enum { kWScalar = 0, kWFull = 1, kWGrouped = 2 };
+
+struct SpmmArgs {
+  int64_t n_rows;
+  const int64_t* indptr;
+  const int32_t* indices;
+  const int32_t* eids;
+  const void* x;
+  const void* w;
+  void* y;
+  int32_t* arg;            // MAX: output; MASKED: input mask [x_rows, feat]
+  int64_t feat;
+  int64_t w_width;
+  int64_t w_group;         // feat / w_width
+  int w_mode;
+  // long-row plan
+  int chunk;
+  int n_long_rows;
+  int64_t n_chunks;
+  const int32_t* long_rows;
+  const int64_t* chunk_ptr;
+  float* partial;
+  int32_t* partial_arg;
+  int64_t n_chunk_warps;   // leading warps of the grid that process slices
+};
+
+constexpr int kSpmmThreads = 256;
+constexpr int kSpmmWarps = kSpmmThreads / 32;
+// One pipeline stage: the U edges of a step, their loaded rows and per-edge scalars.
+template <int U, int TILES, int VEC, bool MUL, bool MASKED>
+struct SpmmStage {
+  float xv[U][TILES][VEC];
+  float wv[MUL ? U : 1][MUL ? TILES : 1][MUL ? VEC : 1];     // non-scalar edge weights
+  int32_t am[MASKED ? U : 1][MASKED ? TILES : 1][MASKED ? VEC : 1];  // argmax mask (backward of max)
+  int32_t s[U];   // source row (or -1: no edge)
+  int32_t e[U];   // edge id
+  float ws[U];    // scalar edge weight
+};
+
+template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads>
+__global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
+  constexpr int RPW = 32 / G;  // items per warp
+  constexpr bool kMul = (MSG == DGLB200_MSG_SRC_MUL_EDGE || MSG == kMsgMasked);
+  constexpr bool kMasked = (MSG == kMsgMasked);
+  constexpr bool kMax = (RED == DGLB200_RED_MAX);
+  constexpr bool kNeedE = (MSG != DGLB200_MSG_COPY_SRC) || kMax;
+  constexpr bool kNeedX = (MSG != DGLB200_MSG_COPY_EDGE);
+  // register budget per stage: 32 loaded floats for plain gathers, 16 when weights/masks ride along
+  constexpr int kBudget = kMul ? 16 : 32;
+  constexpr int U0 = kBudget / (TILES * VEC);
+  constexpr int UA = U0 >= 4 ? 4 : (U0 >= 2 ? 2 : 1);
+  constexpr int U = UCAP > 0 ? (UCAP < G ? UCAP : G) : UA;  // UCAP > 0: tuning override
+  constexpr int SPI = G / U;  // steps served by one coalesced index load
+  using Stage = SpmmStage<U, TILES, VEC, kMul, kMasked>;
+
+  const int lane = threadIdx.x & 31;
+  const int gl = lane % G;     // lane inside the group
+  const int grp = lane / G;
+  const int64_t gw = (int64_t)blockIdx.x * (NT / 32) + (threadIdx.x >> 5);
+  const int64_t fbase = (int64_t)blockIdx.y * (G * TILES * VEC);
+
+  // ---- which item does this group own? ------------------------------------------------
+  int64_t start = 0, end = 0, out_row = -1;
+  bool to_partial = false;
+  if (gw < a.n_chunk_warps) {
+    const int64_t item = gw * RPW + grp;
+    if (item < a.n_chunks) {
+      int lo = 0, hi = a.n_long_rows;  // last lr with chunk_ptr[lr] <= item
+      while (hi - lo > 1) {
+        int mid = (lo + hi) >> 1;
+        if (a.chunk_ptr[mid] <= item) lo = mid; else hi = mid;
+      }
+      const int64_t row = a.long_rows[lo];
+      const int64_t ci = item - a.chunk_ptr[lo];
+      start = a.indptr[row] + ci * a.chunk;
+      end = min(start + (int64_t)a.chunk, a.indptr[row + 1]);
+      out_row = item;
+      to_partial = true;
+    }
+  } else {
+    const int64_t row = (gw - a.n_chunk_warps) * RPW + grp;
+    if (row < a.n_rows) {
+      start = a.indptr[row];
+      end = a.indptr[row + 1];
+      out_row = row;
+      if (a.n_long_rows > 0 && end - start > a.chunk) {  // handled by slices + fix-up
+        end = start;
+        out_row = -1;
+      }
+    }
+  }
+
+  // ---- per-lane feature ownership --------------------------------------------------------
+  const T* __restrict__ x = static_cast<const T*>(a.x);
+  const T* __restrict__ w = static_cast<const T*>(a.w);
+  int64_t foff[TILES];
+  bool fvalid[TILES];
+#pragma unroll
+  for (int t = 0; t < TILES; ++t) {
+    foff[t] = fbase + (int64_t)(t * G + gl) * VEC;
+    fvalid[t] = foff[t] < a.feat;
+  }
+  const bool w_scalar = kMul && a.w != nullptr && a.w_mode == kWScalar;
+  const bool w_full = kMul && a.w != nullptr && a.w_mode == kWFull;
+  const bool w_grouped = kMul && a.w != nullptr && a.w_mode == kWGrouped;
+
+  float acc[TILES][VEC];
+  int32_t best[kMax ? TILES : 1][kMax ? VEC : 1];
+#pragma unroll
+  for (int t = 0; t < TILES; ++t)
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) {
+      acc[t][v] = kMax ? -INFINITY : 0.f;
+      if constexpr (kMax) best[t][v] = -1;
+    }
+
+  const int len = (int)(end - start);
+  int steps = (len + U - 1) / U;
+  if (G < 32) steps = __reduce_max_sync(0xffffffffu, steps);
+
+  // coalesced read of G column ids (+ edge ids, scalar weights) of index block `it`
+  auto load_idx = [&](int it, int32_t& s, int32_t& e, float& wsc) {
+    const int64_t p = start + (int64_t)it * G + gl;
+    s = -1; e = 0; wsc = 0.f;
+    if (p < end) {
+      s = kNeedX ? ld_stream_i32(a.indices + p) : 0;
+      if (kNeedE) e = a.eids ? ld_stream_i32(a.eids + p) : (int32_t)p;
+      if (w_scalar) wsc = to_float(w[e]);
+    }
+  };
+  // issue every global load of one step; nothing here depends on another in-flight load
+  auto load_stage = [&](Stage& st, int32_t s, int32_t e, float wsc, int jj) {
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      st.s[k] = __shfl_sync(0xffffffffu, s, jj + k, G);
+      if (kNeedE) st.e[k] = __shfl_sync(0xffffffffu, e, jj + k, G);
+      if (kMul) st.ws[k] = __shfl_sync(0xffffffffu, wsc, jj + k, G);
+    }
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+#pragma unroll
+      for (int t = 0; t < TILES; ++t) {
+        const bool ok = st.s[k] >= 0 && fvalid[t];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) st.xv[k][t][v] = kMax ? -INFINITY : 0.f;
+        if (ok) {
+          if (MSG == DGLB200_MSG_COPY_EDGE)
+            Chunk<T, VEC>::load(w + (int64_t)st.e[k] * a.feat + foff[t], st.xv[k][t]);
+          else
+            Chunk<T, VEC>::load(x + (int64_t)st.s[k] * a.feat + foff[t], st.xv[k][t]);
+          if constexpr (kMul) {
+            if (w_full) {
+              Chunk<T, VEC>::load(w + (int64_t)st.e[k] * a.feat + foff[t], st.wv[k][t]);
+            } else if (w_grouped) {
+#pragma unroll
+              for (int v = 0; v < VEC; ++v)
+                st.wv[k][t][v] =
+                    to_float(w[(int64_t)st.e[k] * a.w_width + (foff[t] + v) / a.w_group]);
+            }
+          }
+          if constexpr (kMasked) {
+#pragma unroll
+            for (int v = 0; v < VEC; ++v)
+              st.am[k][t][v] = a.arg ? a.arg[(int64_t)st.s[k] * a.feat + foff[t] + v] : st.e[k];
+          }
+        }
+      }
+    }
+  };
+  // fold one step into the accumulators, strictly in slot order
+  auto consume = [&](const Stage& st) {
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+#pragma unroll
+      for (int t = 0; t < TILES; ++t) {
+        const bool ok = st.s[k] >= 0 && fvalid[t];
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+          float m = st.xv[k][t][v];
+          if constexpr (kMul) {
+            if (w_scalar) m *= st.ws[k];
+            else if (w_full || w_grouped) m *= (ok ? st.wv[k][t][v] : 0.f);
+            if (kMasked && ok && st.am[k][t][v] != st.e[k]) m = 0.f;
+          }
+          if (!kMax) {
+            acc[t][v] += m;
+          } else if (ok && (best[t][v] < 0 || m > acc[t][v])) {  // strict '>': earliest slot wins ties
+            acc[t][v] = m;
+            best[t][v] = st.e[k];
+          }
+        }
+      }
+    }
+  };
+
+  if (steps > 0) {
+    int32_t sA, eA, sB, eB;
+    float wA, wB;
+    load_idx(0, sA, eA, wA);
+    load_idx(1, sB, eB, wB);
+    Stage st0, st1;
+    load_stage(st0, sA, eA, wA, 0);
+    // two-stage software pipeline, unrolled by two so the stages are fixed registers
+    for (int q = 0; q < steps; q += 2) {
+      int qn = q + 1;
+      if (qn % SPI == 0) { sA = sB; eA = eB; wA = wB; load_idx(qn / SPI + 1, sB, eB, wB); }
+      if (qn < steps) load_stage(st1, sA, eA, wA, (qn % SPI) * U);
+      consume(st0);
+      if (qn < steps) {
+        qn = q + 2;
+        if (qn % SPI == 0) { sA = sB; eA = eB; wA = wB; load_idx(qn / SPI + 1, sB, eB, wB); }
+        if (qn < steps) load_stage(st0, sA, eA, wA, (qn % SPI) * U);
+        consume(st1);
+      }
+    }
+  }
+
+  // ---- epilogue ---------------------------------------------------------------------------
+  if (out_row < 0) return;
+  if (to_partial) {
+#pragma unroll
+    for (int t = 0; t < TILES; ++t) {
+      if (!fvalid[t]) continue;
+      float* dst = a.partial + out_row * a.feat + foff[t];
+#pragma unroll
+      for (int v = 0; v < VEC; ++v) dst[v] = acc[t][v];
+      if constexpr (kMax) {
+        if (a.partial_arg != nullptr) {
+          int32_t* da = a.partial_arg + out_row * a.feat + foff[t];
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) da[v] = best[t][v];
+        }
+      }
+    }
+  } else {
+    T* __restrict__ y = static_cast<T*>(a.y);
+#pragma unroll
+    for (int t = 0; t < TILES; ++t) {
+      if (!fvalid[t]) continue;
+      if constexpr (kMax) {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v)
+          if (best[t][v] < 0) acc[t][v] = 0.f;
+        if (a.arg != nullptr) {
+          int32_t* da = a.arg + out_row * a.feat + foff[t];
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) da[v] = best[t][v];
+        }
+      }
+      Chunk<T, VEC>::store(y + out_row * a.feat + foff[t], acc[t]);
+    }
+  }
+}
+
+// ---- dispatch over (G, TILES, MSG, RED) for one storage type -----------------------------------
+
+template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads>
+int launch_one(const SpmmArgs& a, cudaStream_t stream) {
+  constexpr int RPW = 32 / G;
+  SpmmArgs args = a;
+  args.n_chunk_warps = ceil_div(a.n_chunks, RPW);
+  const int64_t warps = args.n_chunk_warps + ceil_div(a.n_rows, RPW);
+  const int64_t blocks = ceil_div(warps, NT / 32);
+  const int64_t slabs = ceil_div(ceil_div(a.feat, VEC), (int64_t)G * TILES);
+  DGLB200_REQUIRE(blocks < (1ll << 31) && slabs < 65536, "spmm: grid too large (%lld x %lld)",
+                  (long long)blocks, (long long)slabs);
+  if (blocks == 0) return 0;
+  dim3 grid((unsigned)blocks, (unsigned)slabs);
+  spmm_kernel<T, VEC, G, TILES, MSG, RED, UCAP, NT><<<grid, NT, 0, stream>>>(args);
+  DGLB200_POST_LAUNCH("spmm_kernel");
+  return 0;
+}
+
+// Tuning knobs (dglb200_set_tuning): only the fp32 vector copy_src->sum kernel, the one the
+// headline benchmark times, is instantiated in several shapes.
+struct SpmmTuning {
+  int ucap = 0;         // edges per pipeline stage (0 = auto)
+  int slab_chunks = 0;  // 16-byte chunks of a row per pass: 16, 32 or 64 (0 = auto)
+  int threads = 0;      // CTA size: 128, 256 or 512 (0 = auto)
+};
+SpmmTuning& spmm_tuning();
+
+template <typename T, int VEC, int MSG, int RED>
+int launch_tuned(const SpmmArgs& a, cudaStream_t stream, bool* handled) {
+  *handled = false;
+  if constexpr (std::is_same<T, float>::value && VEC == 4 && MSG == DGLB200_MSG_COPY_SRC &&
+                RED == DGLB200_RED_SUM) {
+    const SpmmTuning& t = spmm_tuning();
+    if (t.ucap == 0 && t.slab_chunks == 0 && t.threads == 0) return 0;
+    const int u = t.ucap ? t.ucap : 4, sc = t.slab_chunks ? t.slab_chunks : 64,
+              nt = t.threads ? t.threads : 256;
+    *handled = true;
+#define DGLB200_TUNED(UC, G_, TL, NT_) \
+  if (u == UC && sc == G_ * TL && nt == NT_) \
+    return launch_one<T, VEC, G_, TL, MSG, RED, UC, NT_>(a, stream);
+#define DGLB200_TUNED_U(G_, TL, NT_) \
+  DGLB200_TUNED(1, G_, TL, NT_) DGLB200_TUNED(2, G_, TL, NT_) DGLB200_TUNED(4, G_, TL, NT_) \
+  DGLB200_TUNED(8, G_, TL, NT_)
+#define DGLB200_TUNED_NT(G_, TL) \
+  DGLB200_TUNED_U(G_, TL, 128) DGLB200_TUNED_U(G_, TL, 256) DGLB200_TUNED_U(G_, TL, 512)
+    DGLB200_TUNED_NT(16, 1) DGLB200_TUNED_NT(32, 1) DGLB200_TUNED_NT(32, 2)
+#undef DGLB200_TUNED_NT
+#undef DGLB200_TUNED_U
+#undef DGLB200_TUNED
+    set_error("spmm tuning: unsupported combination ucap=%d slab_chunks=%d threads=%d", u, sc, nt);
+    return -1;
+  }
+  return 0;
+}
+
+template <typename T, int VEC, int MSG, int RED>
+int launch_shape(const SpmmArgs& a, cudaStream_t stream) {
+  bool handled = false;
+  const int rc = launch_tuned<T, VEC, MSG, RED>(a, stream, &handled);
+  if (handled || rc != 0) return rc;
+  const int64_t chunks = ceil_div(a.feat, VEC);
+  if (chunks <= 4) return launch_one<T, VEC, 4, 1, MSG, RED>(a, stream);
+  if (chunks <= 8) return launch_one<T, VEC, 8, 1, MSG, RED>(a, stream);
+  if (chunks <= 16) return launch_one<T, VEC, 16, 1, MSG, RED>(a, stream);
+  if (chunks <= 32) return launch_one<T, VEC, 32, 1, MSG, RED>(a, stream);
+  if (VEC * sizeof(T) == 16 && sizeof(T) == 2)  // bf16 vector path: 8 accumulators per tile
+    return launch_one<T, VEC, 32, (VEC == 1 ? 4 : 2), MSG, RED>(a, stream);
+  if (chunks <= 64 || VEC != 1) return launch_one<T, VEC, 32, 2, MSG, RED>(a, stream);
+  return launch_one<T, VEC, 32, 4, MSG, RED>(a, stream);
+}
+
+template <typename T, int VEC>
+int launch_ops(const SpmmArgs& a, int msg, int red, cudaStream_t stream) {
+  if (red == DGLB200_RED_SUM) {
+    switch (msg) {
+      case DGLB200_MSG_COPY_SRC: return launch_shape<T, VEC, DGLB200_MSG_COPY_SRC, DGLB200_RED_SUM>(a, stream);
+      case DGLB200_MSG_SRC_MUL_EDGE: return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_SUM>(a, stream);
+      case DGLB200_MSG_COPY_EDGE: return launch_shape<T, VEC, DGLB200_MSG_COPY_EDGE, DGLB200_RED_SUM>(a, stream);
+      case kMsgMasked: return launch_shape<T, VEC, kMsgMasked, DGLB200_RED_SUM>(a, stream);
+    }
+  } else if (red == DGLB200_RED_MAX) {
+    switch (msg) {
+      case DGLB200_MSG_COPY_SRC: return launch_shape<T, VEC, DGLB200_MSG_COPY_SRC, DGLB200_RED_MAX>(a, stream);
+      case DGLB200_MSG_SRC_MUL_EDGE: return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_MAX>(a, stream);
+      case DGLB200_MSG_COPY_EDGE: return launch_shape<T, VEC, DGLB200_MSG_COPY_EDGE, DGLB200_RED_MAX>(a, stream);
+    }
+  }
+  set_error("spmm: unsupported (msg_op=%d, reduce_op=%d)", msg, red);
+  return -1;
+}
+
+// one translation unit per storage type keeps nvcc parallel
+int launch_spmm_f32(const SpmmArgs& a, int msg, int red, bool vec, cudaStream_t stream);
+int launch_spmm_bf16(const SpmmArgs& a, int msg, int red, bool vec, cudaStream_t stream);
+
+}  // namespace dglb200

@@ -1,0 +1,11 @@
+"""dgl_b200: B200-native engine for DGL 0.1.x's builtin message-passing path.
+
+Host side mirrors the reference's interface for that path (python/dgl/graph.py update_all /
+send_and_recv / pull, python/dgl/function); all computation is in libdgl_b200.so
+(include/dgl_b200.h).  Importing this package does not need a GPU; calling an op does.
+"""
+from .base import ALL, DGLError
+from . import function
+from . import ops
+
+__version__ = "0.1.0"

@@ -1,0 +1,229 @@
+"""Thin tensor-level wrappers over the C ABI (include/dgl_b200.h).
+
+This is the layer that plays `F.spmm` / `F.sparse_matrix` of the reference's backend shim
+(python/dgl/backend/pytorch/tensor.py:34-54,138-146): torch supplies device memory and the
+current CUDA stream, every computation is a libdgl_b200.so kernel.  No function here has a
+CPU or eager-PyTorch fallback; a non-CUDA tensor raises DGLError.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from .base import DGLError
+
+MSG_COPY_SRC, MSG_SRC_MUL_EDGE, MSG_COPY_EDGE = 0, 1, 2
+RED_SUM, RED_MAX = 0, 1
+F32, BF16 = 0, 1
+SDDMM_DOT, SDDMM_ADD, SDDMM_MUL = 0, 1, 2
+SOFTMAX_STABLE, SOFTMAX_GAT_EXAMPLE = 0, 1
+
+DEFAULT_CHUNK = 512
+
+
+def _stream():
+    return ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _ptr(t):
+    if t is None:
+        return ctypes.c_void_p(0)
+    return ctypes.c_void_p(t.data_ptr())
+
+
+def _need_cuda(*tensors):
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise DGLError("dgl_b200 ops need CUDA tensors (got %s); there is no CPU path" % t.device)
+
+
+def _dtype_code(t):
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise DGLError("unsupported feature dtype %s (float32 / bfloat16 only)" % t.dtype)
+
+
+def _workspace(nbytes, device):
+    return torch.empty(max(int(nbytes), 1), dtype=torch.uint8, device=device)
+
+
+class CSR(object):
+    """Engine-side CSR: int64 indptr[n_rows+1], int32 indices[nnz], int32 eids[nnz]."""
+
+    def __init__(self, n_rows, n_cols, indptr, indices, eids):
+        self.n_rows = int(n_rows)
+        self.n_cols = int(n_cols)
+        self.indptr = indptr
+        self.indices = indices
+        self.eids = eids
+        self.nnz = int(indices.shape[0])
+        self._plans = {}
+
+    @property
+    def device(self):
+        return self.indptr.device
+
+    def plan(self, chunk=DEFAULT_CHUNK):
+        """Long-row split table for this CSR (cached per chunk)."""
+        if chunk not in self._plans:
+            self._plans[chunk] = SpmmPlan(self, chunk)
+        return self._plans[chunk]
+
+
+def csr_build(row, col, n_rows, n_cols, eid=None, order=0):
+    """dglb200_csr_build: CSR keyed by `row` of the COO (row, col[, eid]) (int64, CUDA)."""
+    _need_cuda(row, col, eid)
+    lib = _lib.get_lib()
+    nnz = int(row.shape[0])
+    if row.dtype != torch.int64 or col.dtype != torch.int64 or (eid is not None and eid.dtype != torch.int64):
+        raise DGLError("csr_build: ids must be int64 (c_api_common.h:35-38 IsValidIdArray)")
+    row = row.contiguous()
+    col = col.contiguous()
+    eid = eid.contiguous() if eid is not None else None
+    dev = row.device
+    indptr = torch.empty(n_rows + 1, dtype=torch.int64, device=dev)
+    indices = torch.empty(nnz, dtype=torch.int32, device=dev)
+    eids = torch.empty(nnz, dtype=torch.int32, device=dev)
+    nbytes = ctypes.c_size_t(0)
+    _lib.check_call(lib.dglb200_csr_build_workspace_bytes(n_rows, nnz, ctypes.byref(nbytes)))
+    ws = _workspace(nbytes.value, dev)
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_csr_build(n_rows, n_cols, nnz, _ptr(row), _ptr(col), _ptr(eid),
+                                              order, _ptr(indptr), _ptr(indices), _ptr(eids),
+                                              _ptr(ws), nbytes.value, _stream()))
+    return CSR(n_rows, n_cols, indptr, indices, eids)
+
+
+def widen(t):
+    """int32 engine array -> int64 (the reference's id dtype)."""
+    _need_cuda(t)
+    out = torch.empty(t.shape, dtype=torch.int64, device=t.device)
+    with torch.cuda.device(t.device):
+        _lib.check_call(_lib.get_lib().dglb200_widen_i32_to_i64(t.numel(), _ptr(t), _ptr(out), _stream()))
+    return out
+
+
+def degrees(csr):
+    out = torch.empty(csr.n_rows, dtype=torch.int64, device=csr.device)
+    with torch.cuda.device(csr.device):
+        _lib.check_call(_lib.get_lib().dglb200_degrees_from_indptr(csr.n_rows, _ptr(csr.indptr), _ptr(out), _stream()))
+    return out
+
+
+def csr_row_ids(csr):
+    out = torch.empty(csr.nnz, dtype=torch.int64, device=csr.device)
+    with torch.cuda.device(csr.device):
+        _lib.check_call(_lib.get_lib().dglb200_csr_row_ids(csr.n_rows, csr.nnz, _ptr(csr.indptr), _ptr(out), _stream()))
+    return out
+
+
+class SpmmPlan(object):
+    """Host handle of dglb200_spmm_plan_t; owns the device tables and the partial buffers."""
+
+    def __init__(self, csr, chunk):
+        lib = _lib.get_lib()
+        self.chunk = int(chunk)
+        self.csr = csr
+        dev = csr.device
+        nbytes = ctypes.c_size_t(0)
+        _lib.check_call(lib.dglb200_spmm_plan_workspace_bytes(csr.n_rows, ctypes.byref(nbytes)))
+        ws = _workspace(nbytes.value, dev)
+        # upper bound on long rows: every long row has > chunk edges
+        cap = csr.nnz // self.chunk + 1
+        self.long_rows = torch.empty(cap, dtype=torch.int32, device=dev)
+        self.chunk_ptr = torch.empty(cap + 1, dtype=torch.int64, device=dev)
+        counts = (ctypes.c_int64 * 2)()
+        with torch.cuda.device(dev):
+            _lib.check_call(lib.dglb200_spmm_plan(csr.n_rows, _ptr(csr.indptr), self.chunk, cap,
+                                                  _ptr(self.long_rows), _ptr(self.chunk_ptr), counts,
+                                                  _ptr(ws), nbytes.value, _stream()))
+        self.n_long_rows = int(counts[0])
+        self.n_chunks = int(counts[1])
+        self._partial = None
+        self._partial_arg = None
+
+    def struct(self, feat, want_arg):
+        """Fill a dglb200_spmm_plan_t for a call with `feat` features (None if no long rows)."""
+        if self.n_long_rows == 0:
+            return None
+        need = self.n_chunks * feat
+        dev = self.csr.device
+        if self._partial is None or self._partial.numel() < need:
+            self._partial = torch.empty(need, dtype=torch.float32, device=dev)
+        if want_arg and (self._partial_arg is None or self._partial_arg.numel() < need):
+            self._partial_arg = torch.empty(need, dtype=torch.int32, device=dev)
+        st = _lib.SpmmPlanStruct()
+        st.chunk = self.chunk
+        st.n_long_rows = self.n_long_rows
+        st.n_chunks = self.n_chunks
+        st.long_rows = self.long_rows.data_ptr()
+        st.chunk_ptr = self.chunk_ptr.data_ptr()
+        st.partial = self._partial.data_ptr()
+        st.partial_arg = self._partial_arg.data_ptr() if want_arg else None
+        st.partial_bytes = self._partial.numel() * 4
+        return st
+
+
+def _flatten(t, n):
+    """(n, d1, d2, ...) -> (n, prod d) as SPMVExecutor.run does (ir/executor.py:457-472)."""
+    if t.dim() == 1:
+        return t.reshape(n, 1)
+    return t.reshape(n, -1)
+
+
+def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chunk=DEFAULT_CHUNK,
+         out=None):
+    """y[r] = reduce over row r of msg(x[indices], w[eids]); 2-D (rows, feat) tensors.
+
+    Returns (y, arg) where arg is int32 (rows, feat) for RED_MAX with want_arg, else None.
+    """
+    lib = _lib.get_lib()
+    ref = x if x is not None else w
+    _need_cuda(ref, x, w, csr.indptr)
+    if msg_op == MSG_COPY_EDGE:
+        feat = int(w.shape[1])
+        w_width = feat
+    else:
+        feat = int(x.shape[1])
+    dt = _dtype_code(ref)
+    if x is not None:
+        x = x.contiguous()
+        if x.shape[0] != csr.n_cols:
+            raise DGLError("spmm: x has %d rows, CSR has %d columns" % (x.shape[0], csr.n_cols))
+    if w is not None:
+        w = w.contiguous()
+        if w.dtype != ref.dtype:
+            raise DGLError("spmm: edge data dtype %s != feature dtype %s" % (w.dtype, ref.dtype))
+    y = out if out is not None else torch.empty((csr.n_rows, feat), dtype=ref.dtype, device=ref.device)
+    arg = None
+    if reduce_op == RED_MAX and want_arg:
+        arg = torch.empty((csr.n_rows, feat), dtype=torch.int32, device=ref.device)
+    plan = csr.plan(chunk).struct(feat, arg is not None) if chunk else None
+    plan_ref = ctypes.byref(plan) if plan is not None else None
+    with torch.cuda.device(ref.device):
+        _lib.check_call(lib.dglb200_spmm_csr(
+            csr.n_rows, csr.n_cols, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids),
+            msg_op, reduce_op, dt, _ptr(x), feat, _ptr(w), w_width, _ptr(y), _ptr(arg),
+            plan_ref, _stream()))
+    return y, arg
+
+
+def spmm_backward_x(csr_t, dy, w=None, w_width=1, arg=None, chunk=DEFAULT_CHUNK):
+    """dx over the CSR keyed by source (see dglb200_spmm_csr_backward_x)."""
+    lib = _lib.get_lib()
+    _need_cuda(dy, w, arg)
+    dy = dy.contiguous()
+    feat = int(dy.shape[1])
+    dx = torch.empty((csr_t.n_rows, feat), dtype=dy.dtype, device=dy.device)
+    plan = csr_t.plan(chunk).struct(feat, False) if chunk else None
+    plan_ref = ctypes.byref(plan) if plan is not None else None
+    if w is not None:
+        w = w.contiguous()
+    with torch.cuda.device(dy.device):
+        _lib.check_call(lib.dglb200_spmm_csr_backward_x(
+            csr_t.n_rows, csr_t.nnz, _ptr(csr_t.indptr), _ptr(csr_t.indices), _ptr(csr_t.eids),
+            _dtype_code(dy), _ptr(dy), feat, _ptr(w), w_width, _ptr(arg), _ptr(dx), plan_ref,
+            _stream()))
+    return dx

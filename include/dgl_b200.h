@@ -1,0 +1,272 @@
+/*
+ * dgl_b200.h - C ABI of libdgl_b200.so, the B200 (sm_100a) message-passing engine that
+ * sits behind DGL 0.1.x's builtin-function path (update_all / send_and_recv / pull with
+ * dgl.function.{copy_src, src_mul_edge, copy_edge} -> {sum, max}).
+ *
+ * Conventions (they follow the reference's C API conventions, src/c_api_common.h:18-53 and
+ * include/dgl/runtime/c_runtime_api.h:157-515 of GaiYu0/dgl-1):
+ *   - every entry point returns 0 on success and -1 on failure; the message is then
+ *     available from dglb200_last_error() (thread-local, like DGLGetLastError,
+ *     src/runtime/c_runtime_api.cc:130-148).  Nothing aborts, nothing throws across the ABI.
+ *   - plain pointers and sizes only.  All data pointers are DEVICE pointers on the current
+ *     CUDA device unless the parameter name ends in _host.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).  Kernels are
+ *     launched on it and nothing synchronises unless documented ("syncs").
+ *   - node / edge ids that cross the reference's surface are int64 (c_api_common.h:35-38,
+ *     IsValidIdArray).  Engine-internal structure arrays use int32 column / edge ids
+ *     (all configs have N, E < 2^31) and int64 row pointers.
+ *   - outputs are caller-allocated (the Python host hands in torch tensors so torch's caching
+ *     allocator and stream semantics apply); the library only uses caller-provided workspace
+ *     whose size comes from the matching *_workspace_bytes query.
+ *
+ * Feature layout: node features x are row-major [n, feat] with the trailing dims flattened
+ * exactly like SPMVExecutor.run does (python/dgl/runtime/ir/executor.py:452-473).
+ */
+#ifndef DGL_B200_H_
+#define DGL_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DGLB200_ABI_VERSION 1
+
+/* message builtins: python/dgl/function/message.py:47 (src_mul_edge), :102 (copy_src), :145 (copy_edge) */
+enum { DGLB200_MSG_COPY_SRC = 0, DGLB200_MSG_SRC_MUL_EDGE = 1, DGLB200_MSG_COPY_EDGE = 2 };
+/* reduce builtins: python/dgl/function/reducer.py:52 (sum), :75 (max) */
+enum { DGLB200_RED_SUM = 0, DGLB200_RED_MAX = 1 };
+/* storage type of features / edge data; accumulation is always fp32 */
+enum { DGLB200_F32 = 0, DGLB200_BF16 = 1 };
+/* u-op-v edge ops of the SDDMM */
+enum { DGLB200_SDDMM_DOT = 0, DGLB200_SDDMM_ADD = 1, DGLB200_SDDMM_MUL = 2 };
+/* edge-softmax flavours of the fused GAT kernel */
+enum {
+  DGLB200_SOFTMAX_STABLE = 0,  /* exp(s - rowmax) / sum */
+  DGLB200_SOFTMAX_GAT_EXAMPLE = 1 /* clamp(exp(s), -10, 10) / sum, as examples/pytorch/gat/train.py:74-97 */
+};
+
+/* ---- library ------------------------------------------------------------------------- */
+
+/* ABI version of the loaded library (== DGLB200_ABI_VERSION). */
+int dglb200_abi_version(void);
+/* Last error message of the calling thread ("" if none).  Mirrors DGLGetLastError. */
+const char* dglb200_last_error(void);
+/* Number of kernels this library has launched since load (all threads).  bench.py reports it. */
+int64_t dglb200_launch_count(void);
+/* Compute capability of the current device as major*10+minor; -1 + error if no CUDA device. */
+int dglb200_device_cc(void);
+
+/*
+ * Kernel-selection override for benchmarking sweeps (cf. the env-var style knobs of the reference,
+ * docs/source/env_var.rst).  Keys: "spmm_ucap" (edges per pipeline stage: 1,2,4,8),
+ * "spmm_slab_chunks" (16-byte chunks of a feature row per pass: 16,32,64), "spmm_threads"
+ * (CTA size: 128,256,512); value 0 restores the automatic choice.  Only the fp32 vectorised
+ * copy_src->sum kernel honours them.  Results never depend on the knobs.
+ */
+int dglb200_set_tuning(const char* key, int64_t value);
+
+/* ---- (4) graph structure: in-edge CSR / out-edge CSR build --------------------------- */
+
+/*
+ * Replaces Graph::GetAdj(transpose, "csr") (src/graph/graph.cc:525-549) and
+ * ImmutableGraph::CSR::FromEdges (src/graph/immutable_graph.cc:206-237).
+ *
+ * Builds the CSR of a COO edge list keyed by `row` (pass dst for the in-edge CSR that
+ * aggregation uses, src for the out-edge CSR that its gradient uses).
+ *   order == 0: within a row, edges keep ascending position in the input (== ascending edge id
+ *               when eid == NULL): the mutable Graph's adjacency-list order (graph.cc:540-547).
+ *   order == 1: within a row, sorted by `col`, ties by input position: the immutable graph's
+ *               layout (immutable_graph.cc:211-217; std::sort leaves ties unspecified).
+ * row/col/eid are int64 device arrays of length nnz (eid may be NULL = identity).
+ * Outputs: indptr int64[n_rows+1], indices int32[nnz] (= col), eids int32[nnz].
+ * Errors if any id is out of range or n_rows/n_cols/nnz >= 2^31.  Syncs the stream once
+ * (range check).
+ */
+int dglb200_csr_build_workspace_bytes(int64_t n_rows, int64_t nnz, size_t* bytes_host);
+int dglb200_csr_build(int64_t n_rows, int64_t n_cols, int64_t nnz,
+                      const int64_t* row, const int64_t* col, const int64_t* eid, int order,
+                      int64_t* indptr, int32_t* indices, int32_t* eids,
+                      void* workspace, size_t workspace_bytes, void* stream);
+
+/* Widen an int32 engine array to the reference's int64 surface (GetAdj returns int64). */
+int dglb200_widen_i32_to_i64(int64_t n, const int32_t* in, int64_t* out, void* stream);
+/* In-degrees from a row pointer: deg[i] = indptr[i+1]-indptr[i] (Graph::InDegrees, graph.cc:412-424). */
+int dglb200_degrees_from_indptr(int64_t n_rows, const int64_t* indptr, int64_t* deg, void* stream);
+/* COO of a CSR: row id of every slot (ImmutableGraph::GetAdj "coo", immutable_graph.cc:559-573). */
+int dglb200_csr_row_ids(int64_t n_rows, int64_t nnz, const int64_t* indptr, int64_t* row_of_slot,
+                        void* stream);
+
+/* ---- (1)(2) SpMM: generalised message -> reduce over a CSR -------------------------- */
+
+/*
+ * Replaces SPMVExecutor.run / SPMVWithDataExecutor.run (python/dgl/runtime/ir/executor.py:
+ * 452-473, 535-566) -> F.spmm -> th.sparse.mm (python/dgl/backend/pytorch/tensor.py:143-146)
+ * and, for max / copy_edge / non-scalar weights, the degree-bucketing and e2v fallbacks
+ * (python/dgl/runtime/scheduler.py:540-570) with the semantics of the builtins' __call__
+ * (function/message.py:75-91,128-135,173-180; function/reducer.py:45-46).
+ *
+ *   y[r, f] = reduce_{p in [indptr[r], indptr[r+1])} msg(p, f)
+ *     COPY_SRC      msg = x[indices[p], f]
+ *     SRC_MUL_EDGE  msg = x[indices[p], f] * w[e(p), f / (feat / w_width)]   (w_width | feat)
+ *     COPY_EDGE     msg = w[e(p), f]                                          (w_width == feat)
+ *   e(p) = eids[p], or p itself when eids == NULL.
+ *   SUM: rows are accumulated in fp32 in slot order (ascending edge id on an order-0 CSR);
+ *        rows longer than the plan's chunk are summed chunk by chunk in a fixed order, so
+ *        results are run-to-run deterministic.  Empty rows give 0.
+ *   MAX: y = max over the row; empty rows give 0 and arg = -1 (the bucketing path fills
+ *        zero-degree nodes from the zero initializer, runtime/degree_bucketing.py:72-78).
+ *        If arg != NULL, arg[r, f] = e(p) of the winning slot, ties to the smallest slot.
+ * The transpose product for the gradient (kernel 2) is this same call on the CSR keyed by src.
+ *
+ * `plan` (nullable) is the long-row split table made by dglb200_spmm_plan for this indptr;
+ * without it every row is reduced by a single warp group (correct, slower on hub rows).
+ * x_rows bounds-checks nothing at run time; it is recorded for error messages only.
+ */
+typedef struct dglb200_spmm_plan_t {
+  int32_t chunk;              /* edges per work item for long rows (multiple of 32) */
+  int32_t n_long_rows;        /* rows with degree > chunk */
+  int64_t n_chunks;           /* total work items over long rows */
+  const int32_t* long_rows;   /* [n_long_rows] row ids (device) */
+  const int64_t* chunk_ptr;   /* [n_long_rows+1] first work item of each long row (device) */
+  void* partial;              /* [n_chunks, feat] fp32 scratch (device), >= partial_bytes */
+  int32_t* partial_arg;       /* [n_chunks, feat] int32 scratch for MAX with arg (nullable) */
+  size_t partial_bytes;
+} dglb200_spmm_plan_t;
+
+/*
+ * Scan indptr for rows longer than `chunk` and emit the split table.  long_rows/chunk_ptr must
+ * hold `capacity` (+1) entries; counts_host[0] = n_long_rows, counts_host[1] = n_chunks.
+ * Rows are listed in ascending id.  Syncs the stream (returns counts to the host).
+ */
+int dglb200_spmm_plan(int64_t n_rows, const int64_t* indptr, int32_t chunk, int64_t capacity,
+                      int32_t* long_rows, int64_t* chunk_ptr, int64_t* counts_host,
+                      void* workspace, size_t workspace_bytes, void* stream);
+int dglb200_spmm_plan_workspace_bytes(int64_t n_rows, size_t* bytes_host);
+
+int dglb200_spmm_csr(int64_t n_rows, int64_t x_rows, int64_t nnz,
+                     const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                     int msg_op, int reduce_op, int dtype,
+                     const void* x, int64_t feat,
+                     const void* w, int64_t w_width,
+                     void* y, int32_t* arg,
+                     const dglb200_spmm_plan_t* plan, void* stream);
+
+/*
+ * Gradient of MAX wrt x (and of SUM, with arg == NULL) in gather form over the CSR keyed by
+ * src (rows = source nodes, indices = dst, eids = edge id):
+ *   dx[u, f] = sum_{p in row u} [arg == NULL or arg[indices[p], f] == e(p)] * wgt * dy[indices[p], f]
+ *   wgt = 1, or w[e(p), f / (feat / w_width)] when w != NULL (src_mul_edge).
+ * Deterministic (no atomics).  This is what torch's sparse.mm backward provides in the
+ * reference (call site backend/pytorch/tensor.py:146).
+ */
+int dglb200_spmm_csr_backward_x(int64_t n_rows, int64_t nnz,
+                                const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                                int dtype, const void* dy, int64_t feat,
+                                const void* w, int64_t w_width, const int32_t* arg,
+                                void* dx, const dglb200_spmm_plan_t* plan, void* stream);
+
+/* ---- (3) SDDMM, per-destination edge softmax, fused GAT aggregation ------------------ */
+
+/*
+ * Per-edge u-op-v over the in-edge CSR (rows = dst):  for slot p of row r, s = indices[p]:
+ *   DOT: out[e(p), h]      = sum_d u[s, h, d] * v[r, h, d]          out is [nnz, heads]
+ *   ADD: out[e(p), h, d]   = u[s, h, d] + v[r, h, d]                out is [nnz, heads*dim]
+ *   MUL: out[e(p), h, d]   = u[s, h, d] * v[r, h, d]
+ * DOT is d(loss)/d(w) of SRC_MUL_EDGE (u = x, v = dy) and the u.v attention score
+ * the north-star names; ADD is the reference GAT example's a1[src] + a2[dst]
+ * (examples/pytorch/gat/train.py:90-92; replaces READ_ROW x2 + EDGE_UDF of
+ * runtime/scheduler.py:234-277,572-583).
+ */
+int dglb200_sddmm_csr(int64_t n_rows, int64_t nnz,
+                      const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                      int op, int dtype, const void* u, const void* v,
+                      int64_t heads, int64_t dim, void* out, void* stream);
+
+/*
+ * Edge softmax over the in-edges of every destination, per head:
+ *   alpha[e, h] = exp(score[e, h] - max_row) / sum_row(...)          (stable flavour)
+ * score/alpha are [nnz, heads] indexed by edge id e(p).  fp32 only.
+ * Backward: dscore[e,h] = alpha[e,h] * (dalpha[e,h] - sum_{row} alpha*dalpha).
+ */
+int dglb200_edge_softmax_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr,
+                             const int32_t* eids, int64_t heads,
+                             const float* score, float* alpha, void* stream);
+int dglb200_edge_softmax_backward_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr,
+                                      const int32_t* eids, int64_t heads,
+                                      const float* alpha, const float* dalpha, float* dscore,
+                                      void* stream);
+
+/*
+ * One launch for the reference GAT layer's edge path
+ * (examples/pytorch/gat/train.py:61-97: apply_edges(edge_attention) ->
+ *  update_all([src_mul_edge('ft','a_drop','ft'), copy_edge('a','a')], [sum, sum]) -> ft / z):
+ *   s[p,h]   = leaky_relu(a_src[indices[p], h] + a_dst[r, h], negative_slope)
+ *   a[p,h]   = GAT_EXAMPLE: min(max(exp(s), -10), 10)      STABLE: exp(s - max_row s)
+ *   out[r,h,:] = sum_p a[p,h] * ft[indices[p], h, :] / sum_p a[p,h]
+ * Optional outputs (nullable): a_out[nnz, heads] unnormalised a by edge id, z_out[n_rows, heads]
+ * the normaliser (what the example keeps in edata['a'] / ndata['z']).  Empty rows: out = 0/0 in
+ * the reference (NaN); here out = 0 and z = 0 is documented in DESIGN.md.  fp32 only.
+ */
+int dglb200_gat_aggregate_csr(int64_t n_rows, int64_t nnz,
+                              const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                              const float* a_src, const float* a_dst, const float* ft,
+                              int64_t heads, int64_t dim, float negative_slope, int flavour,
+                              float* out, float* a_out, float* z_out, void* stream);
+
+/* ---- (4b) degree bucketing ----------------------------------------------------------- */
+
+/*
+ * Replaces sched::DegreeBucketing (src/scheduler/scheduler.cc:13-93; PackedFunc
+ * "runtime.degree_bucketing._CAPI_DGLDegreeBucketing", src/scheduler/scheduler_apis.cc:16-23).
+ * In:  msg_ids[M], vids[M] (destination of every message), recv_ids[R]; ids in [0, id_bound).
+ * Out (int64, device), in CANONICAL order - the reference's order is std::unordered_map
+ * iteration order, i.e. unspecified:
+ *   degs[B]         distinct non-zero in-degrees, ascending; then 0 if any recv id got no message
+ *   nids[K]         nodes grouped by bucket, ascending id inside a bucket
+ *   nid_section[B]  nodes per bucket
+ *   mids[M]         message ids grouped by bucket then node; per node in INPUT order
+ *   mid_section[B'] deg * bucket size for the non-zero buckets (B' = B or B-1)
+ * Capacities the caller must provide: degs/nid_section/mid_section >= dglb200_bucket_capacity(M)
+ * entries, nids >= M + R, mids >= M.  counts_host[0..2] = B, K, B'.  Syncs the stream.
+ */
+int64_t dglb200_bucket_capacity(int64_t n_msgs);
+int dglb200_degree_bucketing_workspace_bytes(int64_t n_msgs, int64_t n_recv, size_t* bytes_host);
+int dglb200_degree_bucketing(int64_t n_msgs, int64_t n_recv, int64_t id_bound,
+                             const int64_t* msg_ids, const int64_t* vids, const int64_t* recv_ids,
+                             int64_t* degs, int64_t* nids, int64_t* nid_section,
+                             int64_t* mids, int64_t* mid_section, int64_t* counts_host,
+                             void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- subset message passing (send_and_recv / pull): unique-ascending relabel --------- */
+
+/*
+ * Replaces F.unique + F.sort_1d + utils.build_relabel_map + the COO build of
+ * build_adj_matrix_uv (python/dgl/runtime/scheduler.py:136,341; python/dgl/utils.py:321-361;
+ * python/dgl/runtime/spmv.py:154-227).  Sorted unique values of ids[n] (< id_bound):
+ * uniq[counts_host[0]] ascending; inverse[i] = position of ids[i] in uniq (nullable).  Syncs.
+ */
+int dglb200_unique_workspace_bytes(int64_t n, size_t* bytes_host);
+int dglb200_unique_sorted(int64_t n, int64_t id_bound, const int64_t* ids,
+                          int64_t* uniq, int64_t* inverse, int64_t* counts_host,
+                          void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- hook into the reference's PackedFunc registry ----------------------------------- */
+
+/*
+ * Registers the entry points above as PackedFunc globals of an already-loaded libdgl.so
+ * (names "b200._CAPI_*", plus an override of
+ * "runtime.degree_bucketing._CAPI_DGLDegreeBucketing" when override_reference != 0) using only
+ * libdgl's C ABI: DGLFuncCreateFromCFunc / DGLFuncRegisterGlobal / DGLCFuncSetReturn /
+ * DGLAPISetLastError (include/dgl/runtime/c_runtime_api.h:255-350).  `libdgl_handle` is the
+ * dlopen handle of libdgl.so (ctypes: CDLL._handle).  Returns the number of globals registered
+ * or -1.
+ */
+int dglb200_register_packed_funcs(void* libdgl_handle, int override_reference);
+
+#ifdef __cplusplus
+}
+#endif
+#endif  /* DGL_B200_H_ */

@@ -1,0 +1,205 @@
+"""-m gpu: kernels (1)/(2) SpMM vs the oracle through the C ABI.
+
+Mirrors the reference's tests/compute/test_specialization.py (v2v / e2v / fallback
+equivalence, 1-D / 2-D / 3-D features, scalar and (E,1) weights, zero-in-degree nodes,
+fn.max) and tests/compute/test_function.py:24-49 (literal known answers).
+Tolerance: fp32 rtol 1e-5 (north-star), bf16 rtol 1e-2; argmax ids bit-exact.
+"""
+import numpy as np
+import pytest
+import torch
+
+from oracle import oracle
+from tests.util import random_graph, hub_graph, HUB_EDGE_H
+
+pytestmark = pytest.mark.gpu
+
+RTOL_F32 = 1e-5
+RTOL_BF16 = 1e-2
+
+
+def _csr(src, dst, n, transpose=False):
+    from dgl_b200 import ops
+    s = torch.from_numpy(src).cuda()
+    d = torch.from_numpy(dst).cuda()
+    row, col = (s, d) if transpose else (d, s)
+    return ops.csr_build(row, col, n, n, order=0)
+
+
+def _close(got, want, rtol, scale=None):
+    got = got.float().cpu().numpy()
+    scale = np.abs(want).max() + 1e-30 if scale is None else scale
+    np.testing.assert_allclose(got, want, rtol=rtol, atol=rtol * scale)
+
+
+def test_known_answers_hub_graph():
+    """tests/compute/test_function.py:24-49 of the reference."""
+    from dgl_b200 import ops
+    src, dst = hub_graph()
+    csr = _csr(src, dst, 10)
+    h = torch.arange(1, 11, dtype=torch.float32).cuda().reshape(10, 1)
+    e = torch.tensor(HUB_EDGE_H, dtype=torch.float32).cuda().reshape(17, 1)
+    y, _ = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=h)
+    assert y.flatten().tolist() == [10., 1., 1., 1., 1., 1., 1., 1., 1., 44.]
+    y, _ = ops.spmm(csr, ops.MSG_COPY_EDGE, ops.RED_SUM, w=e)
+    assert y.flatten().tolist() == [10., 1., 1., 1., 1., 1., 1., 1., 1., 44.]
+    y, _ = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=h, w=e, w_width=1)
+    assert y.flatten().tolist() == [100., 1., 1., 1., 1., 1., 1., 1., 1., 284.]
+
+
+FEATS = [1, 3, 4, 5, 16, 41, 64, 128, 256, 260, 602]
+
+
+@pytest.mark.parametrize("feat", FEATS)
+@pytest.mark.parametrize("chunk", [0, 32, 512])
+def test_copy_src_sum(feat, chunk):
+    from dgl_b200 import ops
+    n = 400
+    src, dst = random_graph(n, 6000, feat, hubs=3, hub_deg=700, zero_deg_frac=0.2)
+    csr = _csr(src, dst, n)
+    x = np.random.RandomState(feat).randn(n, feat).astype(np.float32)
+    want = oracle.update_all(src, dst, n, "copy_src", "sum", x=x)
+    y, _ = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=torch.from_numpy(x).cuda(), chunk=chunk)
+    _close(y, want, RTOL_F32)
+    if chunk == 0:
+        # single-item rows add in edge-id order, the reference's COO order: bit-exact
+        assert np.array_equal(y.cpu().numpy(), want)
+
+
+@pytest.mark.parametrize("feat,wshape", [(1, ()), (8, ()), (8, (1,)), (64, ()), (64, (64,)),
+                                         (64, (8,)), (60, (5,)), (7, (7,)), (256, ())])
+@pytest.mark.parametrize("chunk", [32, 512])
+def test_src_mul_edge_sum(feat, wshape, chunk):
+    from dgl_b200 import ops
+    n = 300
+    src, dst = random_graph(n, 5000, 7 + feat, hubs=2, hub_deg=400)
+    E = len(src)
+    rng = np.random.RandomState(feat)
+    x = rng.randn(n, feat).astype(np.float32)
+    w = rng.rand(*((E,) + wshape)).astype(np.float32)
+    csr = _csr(src, dst, n)
+    w_width = int(np.prod(wshape)) if wshape else 1
+    if w_width not in (1, feat):  # per-head layout (N,H,D) * (E,H,1)
+        xs = x.reshape(n, w_width, feat // w_width)
+        ws = w.reshape(E, w_width, 1)
+    else:
+        xs, ws = x, w
+    want = oracle.update_all(src, dst, n, "src_mul_edge", "sum", x=xs, w=ws).reshape(n, feat)
+    y, _ = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=torch.from_numpy(x).cuda(),
+                    w=torch.from_numpy(w.reshape(E, -1)).cuda(), w_width=w_width, chunk=chunk)
+    _close(y, want, RTOL_F32)
+
+
+@pytest.mark.parametrize("feat", [1, 5, 8, 64, 200])
+@pytest.mark.parametrize("reduce_op", ["sum", "max"])
+def test_copy_edge(feat, reduce_op):
+    from dgl_b200 import ops
+    n = 200
+    src, dst = random_graph(n, 3000, 11 + feat, hubs=2, hub_deg=300, zero_deg_frac=0.25)
+    E = len(src)
+    w = np.random.RandomState(feat).randn(E, feat).astype(np.float32)
+    csr = _csr(src, dst, n)
+    red = ops.RED_SUM if reduce_op == "sum" else ops.RED_MAX
+    for chunk in (0, 64):
+        y, arg = ops.spmm(csr, ops.MSG_COPY_EDGE, red, w=torch.from_numpy(w).cuda(),
+                          want_arg=True, chunk=chunk)
+        if reduce_op == "sum":
+            _close(y, oracle.update_all(src, dst, n, "copy_edge", "sum", w=w), RTOL_F32)
+        else:
+            want, warg = oracle.reduce_max(dst, w, n)
+            assert np.array_equal(y.cpu().numpy(), want)          # max is exact
+            assert np.array_equal(arg.cpu().numpy().astype(np.int64), warg)
+
+
+@pytest.mark.parametrize("feat", [1, 4, 6, 64, 256])
+@pytest.mark.parametrize("msg", ["copy_src", "src_mul_edge"])
+def test_max_with_argmax(feat, msg):
+    from dgl_b200 import ops
+    n = 150
+    src, dst = random_graph(n, 2500, 3 + feat, hubs=2, hub_deg=500, zero_deg_frac=0.3)
+    E = len(src)
+    rng = np.random.RandomState(feat)
+    # few distinct values => many ties: exercises the smallest-slot tie rule
+    x = rng.randint(-3, 4, size=(n, feat)).astype(np.float32)
+    w = rng.randint(1, 3, size=(E,)).astype(np.float32)
+    csr = _csr(src, dst, n)
+    m = oracle.message(msg, src, x, w if msg == "src_mul_edge" else None)
+    want, warg = oracle.reduce_max(dst, m, n)
+    for chunk in (0, 32, 512):
+        y, arg = ops.spmm(csr, ops.MSG_COPY_SRC if msg == "copy_src" else ops.MSG_SRC_MUL_EDGE,
+                          ops.RED_MAX, x=torch.from_numpy(x).cuda(),
+                          w=torch.from_numpy(w).cuda() if msg == "src_mul_edge" else None,
+                          w_width=1, want_arg=True, chunk=chunk)
+        assert np.array_equal(y.cpu().numpy(), want)
+        assert np.array_equal(arg.cpu().numpy().astype(np.int64), warg)
+
+
+@pytest.mark.parametrize("feat", [8, 64, 256, 264])
+def test_bf16(feat):
+    from dgl_b200 import ops
+    n = 300
+    src, dst = random_graph(n, 4000, feat, hubs=2, hub_deg=600)
+    x = torch.from_numpy(np.random.RandomState(1).randn(n, feat).astype(np.float32)).cuda().bfloat16()
+    csr = _csr(src, dst, n)
+    want = oracle.update_all(src, dst, n, "copy_src", "sum", x=x.float().cpu().numpy())
+    y, _ = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=x)
+    assert y.dtype == torch.bfloat16
+    _close(y, want, RTOL_BF16)
+
+
+@pytest.mark.parametrize("feat,w_width", [(16, 0), (16, 1), (64, 8), (5, 5), (256, 0)])
+def test_backward_x_sum(feat, w_width):
+    """dx = A^T dy (torch's sparse.mm backward in the reference)."""
+    from dgl_b200 import ops
+    n = 250
+    src, dst = random_graph(n, 4000, 5 + feat, hubs=2, hub_deg=400)
+    E = len(src)
+    rng = np.random.RandomState(feat)
+    dy = rng.randn(n, feat).astype(np.float32)
+    w = rng.rand(E, w_width).astype(np.float32) if w_width else None
+    csr_t = _csr(src, dst, n, transpose=True)
+    if w is not None and w_width not in (1, feat):
+        want = oracle.spmm_grad(src, dst, n, dy.reshape(n, w_width, -1), w.reshape(E, w_width, 1)).reshape(n, feat)
+    else:
+        want = oracle.spmm_grad(src, dst, n, dy, w)
+    dx = ops.spmm_backward_x(csr_t, torch.from_numpy(dy).cuda(),
+                             w=torch.from_numpy(w).cuda() if w is not None else None,
+                             w_width=max(w_width, 1), chunk=64)
+    _close(dx, want, RTOL_F32)
+
+
+def test_backward_x_max():
+    from dgl_b200 import ops
+    n, feat = 120, 12
+    src, dst = random_graph(n, 1500, 42, hubs=1, hub_deg=300, zero_deg_frac=0.2)
+    rng = np.random.RandomState(0)
+    x = rng.randn(n, feat).astype(np.float32)
+    dy = rng.randn(n, feat).astype(np.float32)
+    csr = _csr(src, dst, n)
+    csr_t = _csr(src, dst, n, transpose=True)
+    _, arg = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_MAX, x=torch.from_numpy(x).cuda(), want_arg=True)
+    dx = ops.spmm_backward_x(csr_t, torch.from_numpy(dy).cuda(), arg=arg, chunk=32)
+    warg = oracle.reduce_max(dst, x[src], n)[1]
+    want = np.zeros((n, feat), dtype=np.float32)
+    for v in range(n):
+        for f in range(feat):
+            if warg[v, f] >= 0:
+                want[src[warg[v, f]], f] += dy[v, f]
+    _close(dx, want, RTOL_F32)
+
+
+def test_determinism_and_large():
+    """Reddit-like degree skew at a size the oracle still handles; run-to-run bit-stable."""
+    from dgl_b200 import ops
+    n, feat = 20000, 128
+    src, dst = random_graph(n, 300000, 9, hubs=8, hub_deg=5000)
+    x = np.random.RandomState(3).randn(n, feat).astype(np.float32)
+    csr = _csr(src, dst, n)
+    xt = torch.from_numpy(x).cuda()
+    y1, _ = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=xt)
+    y2, _ = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=xt)
+    assert torch.equal(y1, y2)
+    import scipy.sparse as sp
+    A = sp.csr_matrix((np.ones(len(src), np.float32), (dst, src)), shape=(n, n))
+    want = (A.astype(np.float64) @ x.astype(np.float64)).astype(np.float32)
+    _close(y1, want, RTOL_F32)
