@@ -22,7 +22,7 @@ constexpr int kSortRounds = 16;                          // items per thread
 constexpr int kSortTile = kSortThreads * kSortRounds;    // 4096 elements per CTA
 constexpr int kSortWarpSpan = 32 * kSortRounds;          // 512 contiguous elements per warp
 
-__global__ void __launch_bounds__(kSortThreads)
+static __global__ void __launch_bounds__(kSortThreads)
 radix_hist(const uint32_t* __restrict__ keys, int64_t n, int shift, int32_t* __restrict__ ghist,
            int64_t tiles) {
   __shared__ int32_t hist[kRadix];
@@ -39,7 +39,7 @@ radix_hist(const uint32_t* __restrict__ keys, int64_t n, int shift, int32_t* __r
   ghist[(int64_t)threadIdx.x * tiles + blockIdx.x] = hist[threadIdx.x];
 }
 
-__global__ void __launch_bounds__(kSortThreads)
+static __global__ void __launch_bounds__(kSortThreads)
 radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
               uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n,
               int shift, const int32_t* __restrict__ goff, int64_t tiles) {

@@ -1,0 +1,383 @@
+// Kernel family (3): per-edge u-op-v (SDDMM), per-destination edge softmax (+ backward) and the
+// fused GAT aggregation.  See include/dgl_b200.h for the contracts.
+//
+// SDDMM is slot-parallel over the in-edge CSR (perfectly balanced whatever the degree skew):
+// a group of LPE lanes owns a run of consecutive slots; it finds the row of its first slot by
+// one binary search in indptr and then walks rows forward.  For a slot it reads the D-wide
+// head segments of u[src] and v[dst] with 128-bit loads and (DOT) reduces with shuffles.
+#include "common.cuh"
+
+namespace dglb200 {
+
+constexpr int kSddmmThreads = 256;
+constexpr int kSlotsPerGroup = 8;
+
+template <typename T>
+__device__ __forceinline__ void store_one(T* p, float v);
+template <>
+__device__ __forceinline__ void store_one<float>(float* p, float v) { *p = v; }
+template <>
+__device__ __forceinline__ void store_one<__nv_bfloat16>(__nv_bfloat16* p, float v) {
+  *p = __float2bfloat16_rn(v);
+}
+
+template <typename T, int VEC, int LPE, int OP>
+__global__ void __launch_bounds__(kSddmmThreads)
+sddmm_kernel(int64_t n_rows, int64_t nnz, const int64_t* __restrict__ indptr,
+             const int32_t* __restrict__ indices, const int32_t* __restrict__ eids,
+             const T* __restrict__ u, const T* __restrict__ v, int64_t heads, int64_t dim,
+             T* __restrict__ out) {
+  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t group = tid / LPE;
+  const int gl = (int)(tid % LPE);
+  const unsigned lane = threadIdx.x & 31;
+  // mask of the lanes of this group inside the warp (groups never straddle warps: LPE | 32)
+  const unsigned gmask = (LPE == 32) ? 0xffffffffu : (((1u << LPE) - 1u) << (lane / LPE * LPE));
+  int64_t p = group * kSlotsPerGroup;
+  const int64_t p_end = min(p + (int64_t)kSlotsPerGroup, nnz);
+  if (p >= nnz) return;
+  // row of the first slot: last r with indptr[r] <= p
+  int64_t lo = 0, hi = n_rows;
+  while (hi - lo > 1) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (indptr[mid] <= p) lo = mid; else hi = mid;
+  }
+  int64_t r = lo;
+  int64_t r_end = indptr[r + 1];
+  const int64_t feat = heads * dim;
+  for (; p < p_end; ++p) {
+    while (p >= r_end) { ++r; r_end = indptr[r + 1]; }
+    const int64_t s = indices[p];
+    const int64_t e = eids ? (int64_t)eids[p] : p;
+    const T* up = u + s * feat;
+    const T* vp = v + r * feat;
+    for (int64_t h = 0; h < heads; ++h) {
+      float acc = 0.f;
+      for (int64_t d = (int64_t)gl * VEC; d < dim; d += (int64_t)LPE * VEC) {
+        float a[VEC], b[VEC];
+        Chunk<T, VEC>::load(up + h * dim + d, a);
+        Chunk<T, VEC>::load(vp + h * dim + d, b);
+        if (OP == DGLB200_SDDMM_DOT) {
+#pragma unroll
+          for (int k = 0; k < VEC; ++k) acc = fmaf(a[k], b[k], acc);
+        } else {
+          float o[VEC];
+#pragma unroll
+          for (int k = 0; k < VEC; ++k) o[k] = (OP == DGLB200_SDDMM_ADD) ? a[k] + b[k] : a[k] * b[k];
+          Chunk<T, VEC>::store(out + e * feat + h * dim + d, o);
+        }
+      }
+      if (OP == DGLB200_SDDMM_DOT) {
+#pragma unroll
+        for (int o = LPE / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(gmask, acc, o);
+        if (gl == 0) store_one<T>(out + e * heads + h, acc);
+      }
+    }
+  }
+}
+
+template <typename T, int VEC, int OP>
+int launch_sddmm_lpe(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32_t* indices,
+                     const int32_t* eids, const T* u, const T* v, int64_t heads, int64_t dim,
+                     T* out, cudaStream_t stream) {
+  const int64_t per = ceil_div(dim, VEC);
+  int lpe = 1;
+  while (lpe < 32 && lpe < per) lpe <<= 1;
+  const int64_t groups = ceil_div(nnz, kSlotsPerGroup);
+  const int64_t blocks = ceil_div(groups * lpe, kSddmmThreads);
+  DGLB200_REQUIRE(blocks < (1ll << 31), "sddmm: grid too large");
+#define DGLB200_SDDMM_CASE(L)                                                                   \
+  case L:                                                                                       \
+    sddmm_kernel<T, VEC, L, OP><<<(unsigned)blocks, kSddmmThreads, 0, stream>>>(                 \
+        n_rows, nnz, indptr, indices, eids, u, v, heads, dim, out);                              \
+    break;
+  switch (lpe) {
+    DGLB200_SDDMM_CASE(1) DGLB200_SDDMM_CASE(2) DGLB200_SDDMM_CASE(4) DGLB200_SDDMM_CASE(8)
+    DGLB200_SDDMM_CASE(16) DGLB200_SDDMM_CASE(32)
+  }
+#undef DGLB200_SDDMM_CASE
+  DGLB200_POST_LAUNCH("sddmm_kernel");
+  return 0;
+}
+
+template <typename T, int VECFULL>
+int launch_sddmm(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32_t* indices,
+                 const int32_t* eids, int op, const void* u_, const void* v_, int64_t heads,
+                 int64_t dim, void* out_, cudaStream_t stream) {
+  const T* u = static_cast<const T*>(u_);
+  const T* v = static_cast<const T*>(v_);
+  T* out = static_cast<T*>(out_);
+  auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  const bool vec = dim % VECFULL == 0 && al(u) && al(v) && (op == DGLB200_SDDMM_DOT || al(out));
+#define DGLB200_SDDMM_OP(OPC)                                                                    \
+  return vec ? launch_sddmm_lpe<T, VECFULL, OPC>(n_rows, nnz, indptr, indices, eids, u, v, heads, \
+                                                 dim, out, stream)                               \
+             : launch_sddmm_lpe<T, 1, OPC>(n_rows, nnz, indptr, indices, eids, u, v, heads, dim,  \
+                                           out, stream)
+  switch (op) {
+    case DGLB200_SDDMM_DOT: DGLB200_SDDMM_OP(DGLB200_SDDMM_DOT);
+    case DGLB200_SDDMM_ADD: DGLB200_SDDMM_OP(DGLB200_SDDMM_ADD);
+    case DGLB200_SDDMM_MUL: DGLB200_SDDMM_OP(DGLB200_SDDMM_MUL);
+  }
+#undef DGLB200_SDDMM_OP
+  set_error("sddmm: unknown op %d", op);
+  return -1;
+}
+
+// ---- edge softmax ----------------------------------------------------------------------------
+// One warp per destination row; heads are looped, lanes stride over the row's slots.
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__global__ void __launch_bounds__(256)
+edge_softmax_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
+                    const int32_t* __restrict__ eids, int64_t heads,
+                    const float* __restrict__ score, float* __restrict__ alpha) {
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= n_rows) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t s = indptr[r], e = indptr[r + 1];
+  if (s == e) return;
+  for (int64_t h = 0; h < heads; ++h) {
+    float mx = -INFINITY;
+    for (int64_t p = s + lane; p < e; p += 32) {
+      const int64_t ed = eids ? (int64_t)eids[p] : p;
+      mx = fmaxf(mx, score[ed * heads + h]);
+    }
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int64_t p = s + lane; p < e; p += 32) {
+      const int64_t ed = eids ? (int64_t)eids[p] : p;
+      sum += expf(score[ed * heads + h] - mx);
+    }
+    sum = warp_sum(sum);
+    for (int64_t p = s + lane; p < e; p += 32) {
+      const int64_t ed = eids ? (int64_t)eids[p] : p;
+      alpha[ed * heads + h] = expf(score[ed * heads + h] - mx) / sum;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+edge_softmax_backward_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
+                             const int32_t* __restrict__ eids, int64_t heads,
+                             const float* __restrict__ alpha, const float* __restrict__ dalpha,
+                             float* __restrict__ dscore) {
+  const int64_t r = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (r >= n_rows) return;
+  const int lane = threadIdx.x & 31;
+  const int64_t s = indptr[r], e = indptr[r + 1];
+  if (s == e) return;
+  for (int64_t h = 0; h < heads; ++h) {
+    float dot = 0.f;
+    for (int64_t p = s + lane; p < e; p += 32) {
+      const int64_t ed = eids ? (int64_t)eids[p] : p;
+      dot += alpha[ed * heads + h] * dalpha[ed * heads + h];
+    }
+    dot = warp_sum(dot);
+    for (int64_t p = s + lane; p < e; p += 32) {
+      const int64_t ed = eids ? (int64_t)eids[p] : p;
+      dscore[ed * heads + h] = alpha[ed * heads + h] * (dalpha[ed * heads + h] - dot);
+    }
+  }
+}
+
+// ---- fused GAT aggregation -------------------------------------------------------------------
+// One launch for apply_edges(edge_attention) + update_all([src_mul_edge, copy_edge],[sum,sum]) +
+// ft / z of examples/pytorch/gat/train.py:61-97.  A group of G lanes owns a destination row;
+// lane chunk = VEC features of one head.  Pass 1 (STABLE only) finds the per-head row maximum of
+// the scores, pass 2 accumulates a * ft[src] and z = sum a in slot order, pass 3 (optional)
+// writes the per-edge attention by edge id.
+
+__device__ __forceinline__ float gat_score(float as, float ad, float slope) {
+  const float s = as + ad;
+  return s >= 0.f ? s : s * slope;
+}
+
+template <int VEC, int G, int TILES>
+__global__ void __launch_bounds__(128)
+gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
+                     const int32_t* __restrict__ indices, const int32_t* __restrict__ eids,
+                     const float* __restrict__ a_src, const float* __restrict__ a_dst,
+                     const float* __restrict__ ft, int64_t heads, int64_t dim, float slope,
+                     int flavour, float* __restrict__ out, float* __restrict__ a_out,
+                     float* __restrict__ z_out) {
+  constexpr int RPW = 32 / G;
+  const int lane = threadIdx.x & 31;
+  const int gl = lane % G, grp = lane / G;
+  const int64_t row = ((int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * RPW + grp;
+  const int64_t feat = heads * dim;
+  const bool rvalid = row < n_rows;
+  const int64_t start = rvalid ? indptr[row] : 0;
+  const int64_t end = rvalid ? indptr[row + 1] : 0;
+  int64_t foff[TILES];
+  int64_t head[TILES];
+  bool fvalid[TILES];
+  float adst[TILES], mx[TILES], z[TILES];
+  float acc[TILES][VEC];
+#pragma unroll
+  for (int t = 0; t < TILES; ++t) {
+    foff[t] = (int64_t)(t * G + gl) * VEC;
+    fvalid[t] = rvalid && foff[t] < feat;
+    head[t] = fvalid[t] ? foff[t] / dim : 0;
+    adst[t] = fvalid[t] ? a_dst[row * heads + head[t]] : 0.f;
+    mx[t] = 0.f;
+    z[t] = 0.f;
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) acc[t][v] = 0.f;
+  }
+  if (flavour == DGLB200_SOFTMAX_STABLE) {
+#pragma unroll
+    for (int t = 0; t < TILES; ++t) mx[t] = -INFINITY;
+    for (int64_t p = start; p < end; ++p) {
+      const int64_t s = indices[p];
+#pragma unroll
+      for (int t = 0; t < TILES; ++t)
+        if (fvalid[t]) mx[t] = fmaxf(mx[t], gat_score(a_src[s * heads + head[t]], adst[t], slope));
+    }
+  }
+  for (int64_t p = start; p < end; ++p) {
+    const int64_t s = indices[p];
+#pragma unroll
+    for (int t = 0; t < TILES; ++t) {
+      if (!fvalid[t]) continue;
+      const float sc = gat_score(a_src[s * heads + head[t]], adst[t], slope);
+      float a;
+      if (flavour == DGLB200_SOFTMAX_STABLE) a = expf(sc - mx[t]);
+      else a = fminf(fmaxf(expf(sc), -10.f), 10.f);
+      float x[VEC];
+      Chunk<float, VEC>::load(ft + s * feat + foff[t], x);
+      z[t] += a;
+#pragma unroll
+      for (int v = 0; v < VEC; ++v) acc[t][v] = fmaf(a, x[v], acc[t][v]);
+    }
+  }
+#pragma unroll
+  for (int t = 0; t < TILES; ++t) {
+    if (!fvalid[t]) continue;
+    float o[VEC];
+#pragma unroll
+    for (int v = 0; v < VEC; ++v) o[v] = (end > start) ? acc[t][v] / z[t] : 0.f;
+    Chunk<float, VEC>::store(out + row * feat + foff[t], o);
+    if (z_out != nullptr && foff[t] % dim == 0) z_out[row * heads + head[t]] = z[t];
+  }
+  if (a_out != nullptr) {
+    for (int64_t p = start; p < end; ++p) {
+      const int64_t s = indices[p];
+      const int64_t e = eids ? (int64_t)eids[p] : p;
+#pragma unroll
+      for (int t = 0; t < TILES; ++t) {
+        if (!fvalid[t] || foff[t] % dim != 0) continue;  // one writer per head
+        const float sc = gat_score(a_src[s * heads + head[t]], adst[t], slope);
+        a_out[e * heads + head[t]] = (flavour == DGLB200_SOFTMAX_STABLE)
+                                         ? expf(sc - mx[t]) / z[t]
+                                         : fminf(fmaxf(expf(sc), -10.f), 10.f);
+      }
+    }
+  }
+}
+
+template <int VEC>
+int launch_gat(int64_t n_rows, const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+               const float* a_src, const float* a_dst, const float* ft, int64_t heads, int64_t dim,
+               float slope, int flavour, float* out, float* a_out, float* z_out,
+               cudaStream_t stream) {
+  const int64_t chunks = ceil_div(heads * dim, VEC);
+  DGLB200_REQUIRE(chunks <= 128, "gat_aggregate: heads*dim = %lld too wide for the fused kernel "
+                  "(max %d); use sddmm + edge_softmax + spmm", (long long)(heads * dim), 128 * VEC);
+#define DGLB200_GAT(G_, TL)                                                                      \
+  {                                                                                              \
+    const int64_t rows_per_block = 4 * (32 / G_);                                                \
+    gat_aggregate_kernel<VEC, G_, TL><<<(unsigned)ceil_div(n_rows, rows_per_block), 128, 0,      \
+                                        stream>>>(n_rows, indptr, indices, eids, a_src, a_dst,   \
+                                                  ft, heads, dim, slope, flavour, out, a_out,    \
+                                                  z_out);                                        \
+  }
+  if (chunks <= 4) DGLB200_GAT(4, 1)
+  else if (chunks <= 8) DGLB200_GAT(8, 1)
+  else if (chunks <= 16) DGLB200_GAT(16, 1)
+  else if (chunks <= 32) DGLB200_GAT(32, 1)
+  else if (chunks <= 64) DGLB200_GAT(32, 2)
+  else DGLB200_GAT(32, 4)
+#undef DGLB200_GAT
+  DGLB200_POST_LAUNCH("gat_aggregate_kernel");
+  return 0;
+}
+
+}  // namespace dglb200
+
+using namespace dglb200;
+
+extern "C" {
+
+int dglb200_sddmm_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32_t* indices,
+                      const int32_t* eids, int op, int dtype, const void* u, const void* v,
+                      int64_t heads, int64_t dim, void* out, void* stream) {
+  clear_error();
+  DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && heads >= 1 && dim >= 1, "sddmm_csr: bad sizes");
+  DGLB200_REQUIRE(n_rows < (1ll << 31) && nnz < (1ll << 31), "sddmm_csr: sizes must be < 2^31");
+  DGLB200_REQUIRE(dtype == DGLB200_F32 || dtype == DGLB200_BF16, "sddmm_csr: unknown dtype %d", dtype);
+  if (nnz == 0) return 0;
+  DGLB200_REQUIRE(indptr && indices && u && v && out, "sddmm_csr: NULL pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return dtype == DGLB200_F32
+             ? launch_sddmm<float, 4>(n_rows, nnz, indptr, indices, eids, op, u, v, heads, dim, out, st)
+             : launch_sddmm<__nv_bfloat16, 8>(n_rows, nnz, indptr, indices, eids, op, u, v, heads, dim, out, st);
+}
+
+int dglb200_edge_softmax_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr,
+                             const int32_t* eids, int64_t heads, const float* score, float* alpha,
+                             void* stream) {
+  clear_error();
+  DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && heads >= 1, "edge_softmax_csr: bad sizes");
+  if (nnz == 0 || n_rows == 0) return 0;
+  DGLB200_REQUIRE(indptr && score && alpha, "edge_softmax_csr: NULL pointer");
+  edge_softmax_kernel<<<(unsigned)ceil_div(n_rows * 32, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      n_rows, indptr, eids, heads, score, alpha);
+  DGLB200_POST_LAUNCH("edge_softmax_kernel");
+  return 0;
+}
+
+int dglb200_edge_softmax_backward_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr,
+                                      const int32_t* eids, int64_t heads, const float* alpha,
+                                      const float* dalpha, float* dscore, void* stream) {
+  clear_error();
+  DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && heads >= 1, "edge_softmax_backward_csr: bad sizes");
+  if (nnz == 0 || n_rows == 0) return 0;
+  DGLB200_REQUIRE(indptr && alpha && dalpha && dscore, "edge_softmax_backward_csr: NULL pointer");
+  edge_softmax_backward_kernel<<<(unsigned)ceil_div(n_rows * 32, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      n_rows, indptr, eids, heads, alpha, dalpha, dscore);
+  DGLB200_POST_LAUNCH("edge_softmax_backward_kernel");
+  return 0;
+}
+
+int dglb200_gat_aggregate_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr,
+                              const int32_t* indices, const int32_t* eids, const float* a_src,
+                              const float* a_dst, const float* ft, int64_t heads, int64_t dim,
+                              float negative_slope, int flavour, float* out, float* a_out,
+                              float* z_out, void* stream) {
+  clear_error();
+  DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && heads >= 1 && dim >= 1, "gat_aggregate_csr: bad sizes");
+  DGLB200_REQUIRE(flavour == DGLB200_SOFTMAX_STABLE || flavour == DGLB200_SOFTMAX_GAT_EXAMPLE,
+                  "gat_aggregate_csr: unknown flavour %d", flavour);
+  if (n_rows == 0) return 0;
+  DGLB200_REQUIRE(indptr && out && a_dst && (nnz == 0 || (indices && a_src && ft)),
+                  "gat_aggregate_csr: NULL pointer");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool vec = dim % 4 == 0 && ((reinterpret_cast<uintptr_t>(ft) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+  return vec ? launch_gat<4>(n_rows, indptr, indices, eids, a_src, a_dst, ft, heads, dim,
+                             negative_slope, flavour, out, a_out, z_out, st)
+             : launch_gat<1>(n_rows, indptr, indices, eids, a_src, a_dst, ft, heads, dim,
+                             negative_slope, flavour, out, a_out, z_out, st);
+}
+
+}  // extern "C"

@@ -227,3 +227,115 @@ def spmm_backward_x(csr_t, dy, w=None, w_width=1, arg=None, chunk=DEFAULT_CHUNK)
             _dtype_code(dy), _ptr(dy), feat, _ptr(w), w_width, _ptr(arg), _ptr(dx), plan_ref,
             _stream()))
     return dx
+
+
+def sddmm(csr, op, u, v, heads, dim):
+    """Per-edge u-op-v over the in-edge CSR (dglb200_sddmm_csr).  u: (n_cols, heads*dim),
+    v: (n_rows, heads*dim).  DOT -> (nnz, heads); ADD / MUL -> (nnz, heads*dim); by edge id."""
+    lib = _lib.get_lib()
+    _need_cuda(u, v)
+    u = u.contiguous()
+    v = v.contiguous()
+    if u.dtype != v.dtype:
+        raise DGLError("sddmm: dtype mismatch %s vs %s" % (u.dtype, v.dtype))
+    width = heads if op == SDDMM_DOT else heads * dim
+    out = torch.empty((csr.nnz, width), dtype=u.dtype, device=u.device)
+    with torch.cuda.device(u.device):
+        _lib.check_call(lib.dglb200_sddmm_csr(csr.n_rows, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices),
+                                              _ptr(csr.eids), op, _dtype_code(u), _ptr(u), _ptr(v),
+                                              heads, dim, _ptr(out), _stream()))
+    return out
+
+
+def edge_softmax(csr, score):
+    """Stable per-destination softmax of (nnz, heads) fp32 scores indexed by edge id."""
+    lib = _lib.get_lib()
+    _need_cuda(score)
+    score = score.contiguous().float()
+    heads = int(score.shape[1])
+    alpha = torch.zeros_like(score)
+    with torch.cuda.device(score.device):
+        _lib.check_call(lib.dglb200_edge_softmax_csr(csr.n_rows, csr.nnz, _ptr(csr.indptr), _ptr(csr.eids),
+                                                     heads, _ptr(score), _ptr(alpha), _stream()))
+    return alpha
+
+
+def edge_softmax_backward(csr, alpha, dalpha):
+    lib = _lib.get_lib()
+    _need_cuda(alpha, dalpha)
+    alpha = alpha.contiguous()
+    dalpha = dalpha.contiguous()
+    heads = int(alpha.shape[1])
+    dscore = torch.zeros_like(alpha)
+    with torch.cuda.device(alpha.device):
+        _lib.check_call(lib.dglb200_edge_softmax_backward_csr(csr.n_rows, csr.nnz, _ptr(csr.indptr),
+                                                              _ptr(csr.eids), heads, _ptr(alpha),
+                                                              _ptr(dalpha), _ptr(dscore), _stream()))
+    return dscore
+
+
+def gat_aggregate(csr, a_src, a_dst, ft, negative_slope, flavour=SOFTMAX_GAT_EXAMPLE, want_edge=True):
+    """Fused GAT edge path (dglb200_gat_aggregate_csr).  a_src: (n_cols, H), a_dst: (n_rows, H),
+    ft: (n_cols, H, D) fp32.  Returns (out (n_rows, H, D), a (nnz, H) or None, z (n_rows, H))."""
+    lib = _lib.get_lib()
+    _need_cuda(a_src, a_dst, ft)
+    heads, dim = int(ft.shape[1]), int(ft.shape[2])
+    a_src = a_src.reshape(-1, heads).contiguous().float()
+    a_dst = a_dst.reshape(-1, heads).contiguous().float()
+    ft = ft.contiguous().float()
+    out = torch.empty((csr.n_rows, heads, dim), dtype=torch.float32, device=ft.device)
+    a = torch.zeros((csr.nnz, heads), dtype=torch.float32, device=ft.device) if want_edge else None
+    z = torch.empty((csr.n_rows, heads), dtype=torch.float32, device=ft.device)
+    with torch.cuda.device(ft.device):
+        _lib.check_call(lib.dglb200_gat_aggregate_csr(
+            csr.n_rows, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids), _ptr(a_src),
+            _ptr(a_dst), _ptr(ft), heads, dim, float(negative_slope), flavour, _ptr(out), _ptr(a),
+            _ptr(z), _stream()))
+    return out, a, z
+
+
+def degree_bucketing(msg_ids, vids, recv_ids, id_bound):
+    """dglb200_degree_bucketing: canonical (degs, nids, nid_section, mids, mid_section), int64 CUDA."""
+    lib = _lib.get_lib()
+    _need_cuda(msg_ids, vids, recv_ids)
+    dev = vids.device
+    m, r = int(vids.shape[0]), int(recv_ids.shape[0])
+    msg_ids = msg_ids.contiguous()
+    vids = vids.contiguous()
+    recv_ids = recv_ids.contiguous()
+    cap = int(lib.dglb200_bucket_capacity(m))
+    i64 = dict(dtype=torch.int64, device=dev)
+    degs = torch.empty(cap, **i64)
+    nsec = torch.empty(cap, **i64)
+    msec = torch.empty(cap, **i64)
+    nids = torch.empty(m + r, **i64)
+    mids = torch.empty(m, **i64)
+    nbytes = ctypes.c_size_t(0)
+    _lib.check_call(lib.dglb200_degree_bucketing_workspace_bytes(m, r, ctypes.byref(nbytes)))
+    ws = _workspace(nbytes.value, dev)
+    counts = (ctypes.c_int64 * 3)()
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_degree_bucketing(
+            m, r, int(id_bound), _ptr(msg_ids), _ptr(vids), _ptr(recv_ids), _ptr(degs), _ptr(nids),
+            _ptr(nsec), _ptr(mids), _ptr(msec), counts, _ptr(ws), nbytes.value, _stream()))
+    b, k, bnz = int(counts[0]), int(counts[1]), int(counts[2])
+    return degs[:b], nids[:k], nsec[:b], mids, msec[:bnz]
+
+
+def unique_sorted(ids, id_bound, want_inverse=True):
+    """dglb200_unique_sorted: (sorted unique ids, inverse positions)."""
+    lib = _lib.get_lib()
+    _need_cuda(ids)
+    ids = ids.contiguous()
+    n = int(ids.shape[0])
+    dev = ids.device
+    uniq = torch.empty(n, dtype=torch.int64, device=dev)
+    inv = torch.empty(n, dtype=torch.int64, device=dev) if want_inverse else None
+    nbytes = ctypes.c_size_t(0)
+    _lib.check_call(lib.dglb200_unique_workspace_bytes(n, ctypes.byref(nbytes)))
+    ws = _workspace(nbytes.value, dev)
+    counts = (ctypes.c_int64 * 1)()
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_unique_sorted(n, int(id_bound), _ptr(ids), _ptr(uniq), _ptr(inv),
+                                                  counts, _ptr(ws), nbytes.value, _stream()))
+    return uniq[:int(counts[0])], inv
