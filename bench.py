@@ -1,0 +1,413 @@
+"""bench.py - the number of record for the hot path.
+
+One "step" = one pass of the hot path over one batch of synthetic input: the GCN aggregation
+`update_all(copy_src, sum)` forward (in-edge CSR SpMM) + its gradient (the transposed SpMM
+over the out-edge CSR), fp32, on the workload BASELINE.json's metric is quoted on:
+
+  C2  Reddit-shaped graph, N=232,965, E=114,615,892, aggregated width F=256  (default, all N)
+  C5  RMAT graph, N=50M, E=150M, F=128 (`--workload c5`; the multi-GPU config of BASELINE.json)
+
+N GPUs (`--gpus N`, launched by torchrun, one rank per GPU): destination rows are 1-D
+partitioned into N contiguous edge-balanced blocks; each rank owns the rows of X, Y, dY, dX of
+its block; the halo exchange is an NCCL all-gather of the feature blocks, then the local SpMM
+runs over the rank's row block.  Strong scaling: the graph is fixed as N grows.
+
+Prints ONE JSON line (rank 0).  `value` is whole-job ALGORITHMIC GB/s of the SpMM aggregation
+(gather model of SURVEY.md 8d: E*(F*4+4) + N*F*4 + (N+1)*8 bytes per SpMM, two SpMMs per step)
+with inputs resident in HBM; `e2e` is the same metric through the host API (DGLGraph.update_all
++ backward) with HOST (pinned) feature buffers, H2D / D2H copies inside the timed region.
+
+`--impl reference` times the reference's own CPU implementation of the path - the call
+`th.sparse.mm(uncoalesced COO adjacency, X)` + its autograd backward, exactly what
+SPMVExecutor.run -> F.spmm does (python/dgl/runtime/ir/executor.py:452-473;
+python/dgl/backend/pytorch/tensor.py:45-51,143-146) - on the box's host cores, on a bounded
+sample of the same workload.  torch is the third-party dependency that holds the arithmetic in
+the reference; oracle/ provides the adjacency restatement (Graph::GetAdj "coo").
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "dgl-1_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+from benchmarks import graphs  # noqa: E402
+
+METRIC = "spmm_aggregation_alg_GBps"
+UNIT = "GB/s"
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:  # noqa: BLE001
+        return 6650.0, "fallback"
+
+
+def workload_cfg(name):
+    if name == "c2":
+        c = graphs.C2_REDDIT
+        return dict(name="C2 reddit-shaped GCN aggregation copy_src->sum fwd+bwd",
+                    n=c["n"], e=c["e"], feat=c["hidden"], seed=c["seed"], kind="powerlaw")
+    if name == "c5":
+        c = graphs.C5_RMAT
+        return dict(name="C5 RMAT SSE/GCN aggregation copy_src->sum fwd+bwd",
+                    n=c["n"], e=c["e"], feat=c["feat"], seed=c["seed"], kind="rmat")
+    if name == "tiny":  # CI / debugging only
+        return dict(name="tiny powerlaw", n=20000, e=2000000, feat=256, seed=1, kind="powerlaw")
+    raise SystemExit("unknown workload %s" % name)
+
+
+def make_edges(cfg, device, e=None, scale_deg=1.0):
+    e = cfg["e"] if e is None else e
+    if cfg["kind"] == "powerlaw":
+        return graphs.powerlaw_symmetric(cfg["n"], e, cfg["seed"], device,
+                                         max_deg=max(64, int(22000 * scale_deg)))
+    return graphs.rmat(26, e, cfg["seed"], device, n=cfg["n"])
+
+
+# ---------------------------------------------------------------------------------------------
+# reference arm / cpu_baseline: torch.sparse.mm on the uncoalesced COO, CPU
+# ---------------------------------------------------------------------------------------------
+
+def cpu_reference(cfg, steps, warmup, budget_s=25.0):
+    """Times fwd+bwd of th.sparse.mm on a bounded sample (same N and F, E/k edges of the same
+    generator) sized so that steps+warmup passes take about `budget_s` seconds."""
+    from oracle import oracle
+    n, feat = cfg["n"], cfg["feat"]
+    cores = torch.get_num_threads()
+    # probe the machine with a small slice to size the sample
+    probe_e = min(cfg["e"], 2_000_000)
+    src, dst = make_edges(cfg, "cpu", probe_e, probe_e / cfg["e"])
+
+    def one_pass(src, dst, reps):
+        idx, _ = oracle.get_adj_coo(src.numpy(), dst.numpy())          # Graph::GetAdj "coo"
+        e = src.shape[0]
+        adj = torch.sparse_coo_tensor(torch.from_numpy(idx).view(2, e), torch.ones(e), (n, n))
+        x = torch.randn(n, feat, requires_grad=True)
+        dy = torch.randn(n, feat)
+        ts = []
+        for _ in range(reps):
+            t0 = time.perf_counter()
+            y = torch.sparse.mm(adj, x)
+            y.backward(dy)
+            ts.append(time.perf_counter() - t0)
+            x.grad = None
+        return ts
+
+    t_probe = min(one_pass(src, dst, 2))
+    per_edge = t_probe / probe_e
+    total = max(1, steps + warmup)
+    e_s = int(min(cfg["e"], max(probe_e, budget_s / total / per_edge)))
+    e_s -= e_s % 2
+    src, dst = make_edges(cfg, "cpu", e_s, e_s / cfg["e"])
+    ts = one_pass(src, dst, total)[warmup:] or [t_probe]
+    t = sum(ts) / len(ts)
+    alg = 2 * graphs.spmm_alg_bytes(e_s, n, feat)
+    return dict(value=alg / t / 1e9, unit=UNIT, cores=cores, kind="port",
+                sample="th.sparse.mm(COO)+autograd bwd, fp32, N=%d F=%d, E=%d of %d edges (1/%.1f), "
+                       "%d timed passes, %.3f s/pass" % (n, feat, e_s, cfg["e"], cfg["e"] / e_s,
+                                                         len(ts), t),
+                edge_feat_per_s=2 * e_s * feat / t, ms_per_step=t * 1e3, sample_edges=e_s)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg = workload_cfg(args.workload)
+    r = cpu_reference(cfg, args.steps, args.warmup, budget_s=60.0)
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": cfg["name"], "n": cfg["n"], "e": cfg["e"], "feat": cfg["feat"],
+                   "sample_edges": r["sample_edges"]},
+        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "edge_feat_per_s": r["edge_feat_per_s"], "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------------
+
+class ClockSampler(object):
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+    NAMES = ("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap")
+
+    def __init__(self, index):
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        self.p = None
+        try:
+            self.p = subprocess.Popen(
+                ["nvidia-smi", "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
+                 "-lms", "100", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
+        if self.p is None:
+            return out
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        sm, mx, reasons, power = [], [], set(), []
+        for ln in self.f.read().splitlines():
+            parts = [s.strip() for s in ln.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+                power.append(float(parts[2]))
+            except ValueError:
+                continue
+            for name, val in zip(self.NAMES, parts[3:7]):
+                if val == "Active":
+                    reasons.add(name)
+        self.f.close()
+        os.unlink(self.f.name)
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons),
+                       samples=len(sm), power_w_max=max(power))
+        return out
+
+
+# ---------------------------------------------------------------------------------------------
+# B200 arm
+# ---------------------------------------------------------------------------------------------
+
+def edge_balanced_bounds(indptr_in, indptr_out, parts):
+    """Row-block boundaries with (in + out) edges balanced across `parts` ranks."""
+    load = (indptr_in + indptr_out).to(torch.float64)
+    total = float(load[-1])
+    targets = torch.arange(1, parts, dtype=torch.float64, device=load.device) * (total / parts)
+    cuts = torch.searchsorted(load, targets).tolist()
+    return [0] + [int(c) for c in cuts] + [int(indptr_in.shape[0] - 1)]
+
+
+def run_b200(args):
+    import torch.distributed as dist
+    from dgl_b200 import ops, _lib
+    import dgl_b200
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1:
+        torch.cuda.set_device(local)
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    cfg = workload_cfg(args.workload)
+    n, e, feat = cfg["n"], cfg["e"], cfg["feat"]
+    lib = _lib.get_lib()
+
+    # ---- graph + structure (one-off, cached per graph like GraphIndex.adjacency_matrix) ------
+    t0 = time.time()
+    g = dgl_b200.DGLGraph()
+    g.add_nodes(n)
+    src, dst = make_edges(cfg, dev)
+    g.add_edges(src, dst)
+    del src, dst
+    csr_in = g.in_csr()        # rows = dst (forward)
+    csr_out = g.out_csr()      # rows = src (gradient)
+    g.drop_coo()
+    torch.cuda.synchronize()
+    t_build = time.time() - t0
+
+    if world > 1:
+        bounds = edge_balanced_bounds(csr_in.indptr, csr_out.indptr, world)
+        r0, r1 = bounds[rank], bounds[rank + 1]
+        loc_in = ops.csr_row_block(csr_in, r0, r1)
+        loc_out = ops.csr_row_block(csr_out, r0, r1)
+        del csr_in, csr_out
+        g.clear_cache()
+        torch.cuda.empty_cache()
+    else:
+        bounds = [0, n]
+        r0, r1 = 0, n
+        loc_in, loc_out = csr_in, csr_out
+    rows = r1 - r0
+    loc_in.plan()
+    loc_out.plan()
+
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(1234 + rank)
+    x_full = torch.empty(n, feat, device=dev)
+    dy_full = torch.empty(n, feat, device=dev)
+    x_full[r0:r1] = torch.randn(rows, feat, device=dev, generator=gen)
+    dy_full[r0:r1] = torch.randn(rows, feat, device=dev, generator=gen)
+    y_loc = torch.empty(rows, feat, device=dev)
+    dx_loc = torch.empty(rows, feat, device=dev)
+    x_views = [x_full[bounds[p]:bounds[p + 1]] for p in range(world)]
+    dy_views = [dy_full[bounds[p]:bounds[p + 1]] for p in range(world)]
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
+    kern_events = []
+
+    def step(record):
+        if world > 1:
+            dist.all_gather(x_views, x_views[rank])
+        if record:
+            a, b = ev(), ev()
+            a.record()
+        ops.spmm(loc_in, ops.MSG_COPY_SRC, ops.RED_SUM, x=x_full, out=y_loc)
+        if record:
+            b.record()
+            kern_events.append((a, b))
+        if world > 1:
+            dist.all_gather(dy_views, dy_views[rank])
+        if record:
+            a, b = ev(), ev()
+            a.record()
+        ops.spmm(loc_out, ops.MSG_COPY_SRC, ops.RED_SUM, x=dy_full, out=dx_loc)
+        if record:
+            b.record()
+            kern_events.append((a, b))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step(False)
+    barrier()
+    sampler = ClockSampler(local) if rank == 0 else None
+    l0 = _lib.launch_count()
+    s_ev, e_ev = ev(), ev()
+    s_ev.record()
+    for _ in range(args.steps):
+        step(True)
+    e_ev.record()
+    barrier()
+    launches = _lib.launch_count() - l0
+    clocks = sampler.stop() if sampler else None
+    ms_total = s_ev.elapsed_time(e_ev)
+    if world > 1:
+        t = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total = float(t.item())
+    ms_step = ms_total / args.steps
+    alg_step = 2 * graphs.spmm_alg_bytes(e, n, feat)          # whole job, all ranks
+    value = alg_step / (ms_step * 1e-3) / 1e9
+
+    # dominant kernel: the SpMM launches of this rank (forward and gradient are the same kernel)
+    kms = [a.elapsed_time(b) for a, b in kern_events]
+    k_avg_ms = sum(kms) / len(kms)
+    loc_e = (loc_in.nnz + loc_out.nnz) / 2.0
+    alg_launch = graphs.spmm_alg_bytes(loc_e, rows, feat)
+    peak, peak_kind = measured_peak()
+    achieved = alg_launch / (k_avg_ms * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic_%s.json" % args.workload)
+    if world == 1 and os.path.exists(tpath):
+        with open(tpath) as f:
+            traffic = json.load(f).get("dram_bytes_per_launch")
+    roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
+                "kernel": "spmm_kernel<float,4,...,copy_src,sum>", "kernel_ms": k_avg_ms,
+                "alg_bytes_per_launch": alg_launch,
+                "min_bytes_per_launch": graphs.spmm_min_bytes(loc_e, n, rows, feat)}
+
+    # ---- e2e: host API with HOST feature buffers ---------------------------------------------
+    e2e = None
+    if world == 1 and not args.no_e2e:
+        from dgl_b200 import function as fn
+        xh = torch.randn(n, feat).pin_memory()
+        dyh = torch.randn(n, feat).pin_memory()
+        yh = torch.empty(n, feat).pin_memory()
+        dxh = torch.empty(n, feat).pin_memory()
+        g.set_csr(loc_in, loc_out)
+
+        def e2e_step():
+            xd = xh.to(dev, non_blocking=True).requires_grad_(True)
+            g.ndata["h"] = xd
+            g.update_all(fn.copy_src("h", "m"), fn.sum("m", "y"))
+            y = g.ndata["y"]
+            yh.copy_(y.detach(), non_blocking=True)
+            y.backward(dyh.to(dev, non_blocking=True))
+            dxh.copy_(xd.grad, non_blocking=True)
+            torch.cuda.synchronize()
+
+        for _ in range(2):
+            e2e_step()
+        k = max(3, min(args.steps, 10))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(k):
+            e2e_step()
+        torch.cuda.synchronize()
+        t_e2e = (time.perf_counter() - t0) / k
+        e2e = {"value": alg_step / t_e2e / 1e9, "unit": UNIT,
+               "h2d_bytes_per_step": 2 * n * feat * 4, "d2h_bytes_per_step": 2 * n * feat * 4,
+               "ms_per_step": t_e2e * 1e3, "steps": k}
+        del xh, dyh, yh, dxh
+    elif world > 1:
+        e2e = None
+
+    cpu = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        cpu = cpu_reference(cfg, 2, 1, budget_s=20.0)
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": cfg["name"], "n": n, "e": e, "feat": feat,
+                       "l2": "inputs_exceed_l2 (X %.0f MB + structure %.0f MB per SpMM; no flush)"
+                             % (n * feat * 4 / 1e6, e * 4 / 1e6),
+                       "parallelism": "row-partition x%d + NCCL all-gather halo" % world,
+                       "graph_build_s": round(t_build, 2)},
+            "edge_feat_per_s": 2 * e * feat / (ms_step * 1e-3),
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": int(launches), "clocks": clocks,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c2", "c5", "tiny"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -55,15 +55,19 @@ sddmm_kernel(int64_t n_rows, int64_t nnz, const int64_t* __restrict__ indptr,
       float acc = 0.f;
       for (int64_t d = (int64_t)gl * VEC; d < dim; d += (int64_t)LPE * VEC) {
         float a[VEC], b[VEC];
-        Chunk<T, VEC>::load(up + h * dim + d, a);
-        Chunk<T, VEC>::load(vp + h * dim + d, b);
+        if (OP != DGLB200_SDDMM_COPY_V) Chunk<T, VEC>::load(up + h * dim + d, a);
+        if (OP != DGLB200_SDDMM_COPY_U) Chunk<T, VEC>::load(vp + h * dim + d, b);
         if (OP == DGLB200_SDDMM_DOT) {
 #pragma unroll
           for (int k = 0; k < VEC; ++k) acc = fmaf(a[k], b[k], acc);
         } else {
           float o[VEC];
 #pragma unroll
-          for (int k = 0; k < VEC; ++k) o[k] = (OP == DGLB200_SDDMM_ADD) ? a[k] + b[k] : a[k] * b[k];
+          for (int k = 0; k < VEC; ++k)
+            o[k] = (OP == DGLB200_SDDMM_ADD)      ? a[k] + b[k]
+                   : (OP == DGLB200_SDDMM_MUL)    ? a[k] * b[k]
+                   : (OP == DGLB200_SDDMM_COPY_U) ? a[k]
+                                                  : b[k];
           Chunk<T, VEC>::store(out + e * feat + h * dim + d, o);
         }
       }
@@ -108,7 +112,8 @@ int launch_sddmm(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32
   const T* v = static_cast<const T*>(v_);
   T* out = static_cast<T*>(out_);
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
-  const bool vec = dim % VECFULL == 0 && al(u) && al(v) && (op == DGLB200_SDDMM_DOT || al(out));
+  const bool vec = dim % VECFULL == 0 && (u == nullptr || al(u)) && (v == nullptr || al(v)) &&
+                   (op == DGLB200_SDDMM_DOT || al(out));
 #define DGLB200_SDDMM_OP(OPC)                                                                    \
   return vec ? launch_sddmm_lpe<T, VECFULL, OPC>(n_rows, nnz, indptr, indices, eids, u, v, heads, \
                                                  dim, out, stream)                               \
@@ -118,6 +123,8 @@ int launch_sddmm(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32
     case DGLB200_SDDMM_DOT: DGLB200_SDDMM_OP(DGLB200_SDDMM_DOT);
     case DGLB200_SDDMM_ADD: DGLB200_SDDMM_OP(DGLB200_SDDMM_ADD);
     case DGLB200_SDDMM_MUL: DGLB200_SDDMM_OP(DGLB200_SDDMM_MUL);
+    case DGLB200_SDDMM_COPY_U: DGLB200_SDDMM_OP(DGLB200_SDDMM_COPY_U);
+    case DGLB200_SDDMM_COPY_V: DGLB200_SDDMM_OP(DGLB200_SDDMM_COPY_V);
   }
 #undef DGLB200_SDDMM_OP
   set_error("sddmm: unknown op %d", op);
@@ -327,7 +334,9 @@ int dglb200_sddmm_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr, const 
   DGLB200_REQUIRE(n_rows < (1ll << 31) && nnz < (1ll << 31), "sddmm_csr: sizes must be < 2^31");
   DGLB200_REQUIRE(dtype == DGLB200_F32 || dtype == DGLB200_BF16, "sddmm_csr: unknown dtype %d", dtype);
   if (nnz == 0) return 0;
-  DGLB200_REQUIRE(indptr && indices && u && v && out, "sddmm_csr: NULL pointer");
+  DGLB200_REQUIRE(indptr && indices && out, "sddmm_csr: NULL pointer");
+  DGLB200_REQUIRE(u != nullptr || op == DGLB200_SDDMM_COPY_V, "sddmm_csr: u is NULL");
+  DGLB200_REQUIRE(v != nullptr || op == DGLB200_SDDMM_COPY_U, "sddmm_csr: v is NULL");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return dtype == DGLB200_F32
              ? launch_sddmm<float, 4>(n_rows, nnz, indptr, indices, eids, op, u, v, heads, dim, out, st)

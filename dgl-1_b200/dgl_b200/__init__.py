@@ -7,5 +7,7 @@ send_and_recv / pull, python/dgl/function); all computation is in libdgl_b200.so
 from .base import ALL, DGLError
 from . import function
 from . import ops
+from .graph import DGLGraph
+from .udf import EdgeBatch, NodeBatch
 
 __version__ = "0.1.0"

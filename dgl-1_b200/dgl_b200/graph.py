@@ -1,0 +1,324 @@
+"""DGLGraph: host-side mirror of the reference's message-passing entry points.
+
+Same method names, argument meaning and ordering guarantees as python/dgl/graph.py
+(update_all :2398, send_and_recv :2089, pull :2198, push :2301, apply_nodes :1800,
+apply_edges :1854) for the builtin-function path; graph mutation / queries beyond what that path
+needs are out of scope.  Structure lives on the device as an edge list in edge-id
+order plus cached in-/out-edge CSRs (built by kernel 4); features are torch tensors.
+
+Scheduling follows python/dgl/runtime/scheduler.py (see scheduler.py in this package); every
+call records its executor plan in `last_prog` (plan.Prog) before running it.
+"""
+import torch
+
+from . import ops
+from .autograd import Adjacency
+from .base import ALL, DGLError, is_all
+
+
+class FeatureDict(dict):
+    """ndata / edata: field -> tensor with a fixed number of rows (cf. Frame, frame.py:179)."""
+
+    def __init__(self, num_rows_fn, kind):
+        super(FeatureDict, self).__init__()
+        self._num_rows_fn = num_rows_fn
+        self._kind = kind
+
+    def __setitem__(self, key, val):
+        if not torch.is_tensor(val):
+            raise DGLError("%s feature '%s' must be a tensor" % (self._kind, key))
+        if val.shape[0] != self._num_rows_fn():
+            raise DGLError("Expect number of features to match number of %ss. Got %d and %d instead."
+                           % (self._kind, val.shape[0], self._num_rows_fn()))
+        super(FeatureDict, self).__setitem__(key, val)
+
+
+def _as_ids(v, device=None):
+    """Normalise an id container to an int64 tensor (utils.Index, python/dgl/utils.py:12-219)."""
+    if torch.is_tensor(v):
+        t = v.to(torch.int64)
+    elif isinstance(v, int):
+        t = torch.tensor([v], dtype=torch.int64)
+    else:
+        t = torch.as_tensor(list(v), dtype=torch.int64)
+    if device is not None and t.device != device:
+        t = t.to(device)
+    return t.reshape(-1)
+
+
+class DGLGraph(object):
+    def __init__(self, multigraph=True, readonly=False):
+        self._n = 0
+        self._src = torch.empty(0, dtype=torch.int64)
+        self._dst = torch.empty(0, dtype=torch.int64)
+        self._e = 0
+        self._device = None
+        self._adj = None            # Adjacency of the whole graph (cache)
+        self._readonly = readonly
+        self.ndata = FeatureDict(self.number_of_nodes, "node")
+        self.edata = FeatureDict(self.number_of_edges, "edge")
+        self._message_func = None
+        self._reduce_func = None
+        self._apply_node_func = None
+        self._apply_edge_func = None
+        self.last_prog = None
+        self.execute = True         # False: only record the plan in last_prog (tests diff it)
+
+    # ---- structure -----------------------------------------------------------------------
+    def add_nodes(self, num):
+        self._n += int(num)
+        self.clear_cache()
+
+    def add_edge(self, u, v):
+        self.add_edges([u], [v])
+
+    def add_edges(self, u, v):
+        """Append edges; edge ids are assigned in insertion order (Graph::AddEdges, graph.cc:66-97)."""
+        dev = self._device if self._device is not None else (u.device if torch.is_tensor(u) else None)
+        u = _as_ids(u, dev)
+        v = _as_ids(v, u.device)
+        if u.numel() == 1 and v.numel() > 1:
+            u = u.expand(v.numel())
+        if v.numel() == 1 and u.numel() > 1:
+            v = v.expand(u.numel())
+        if u.numel() != v.numel():
+            raise DGLError("add_edges: u and v have different lengths")
+        if self._e == 0:
+            self._src, self._dst = u.contiguous(), v.contiguous()
+        else:
+            self._src = torch.cat([self._src.to(u.device), u])
+            self._dst = torch.cat([self._dst.to(u.device), v])
+        self._e = int(self._src.shape[0])
+        if u.is_cuda:
+            self._device = u.device
+        self.clear_cache()
+
+    def to(self, device):
+        """Move the structure to `device` (features are moved by the user, as in the reference)."""
+        device = torch.device(device)
+        self._device = device
+        if self._src is not None:
+            self._src = self._src.to(device)
+            self._dst = self._dst.to(device)
+        self.clear_cache()
+        return self
+
+    def number_of_nodes(self):
+        return self._n
+
+    def number_of_edges(self):
+        return self._e
+
+    def __len__(self):
+        return self._n
+
+    def clear_cache(self):
+        """Drop the cached device CSRs (GraphIndex.clear_cache, graph_index.py:113-115)."""
+        self._adj = None
+
+    def _need_device(self):
+        if self._device is None or self._device.type != "cuda":
+            raise DGLError("the graph structure is not on a CUDA device: call g.to('cuda') first "
+                           "(dgl_b200 has no CPU path)")
+        return self._device
+
+    def adjacency(self):
+        """Whole-graph Adjacency (cached): rows = dst, cols = src, edge-id order inside a row, i.e.
+        Graph::GetAdj(false, "csr") (src/graph/graph.cc:525-549)."""
+        if self._adj is None:
+            self._need_device()
+            if self._src is None:
+                raise DGLError("edge list was dropped and the CSR cache was cleared")
+            self._adj = Adjacency(self._n, self._n, coo=(self._dst, self._src, None))
+        return self._adj
+
+    def in_csr(self):
+        return self.adjacency().csr_in
+
+    def out_csr(self):
+        return self.adjacency().csr_out
+
+    def set_csr(self, csr_in, csr_out):
+        """Install prebuilt CSRs (benchmarks that build / slice the structure themselves)."""
+        self._adj = Adjacency(csr_in.n_rows, csr_in.n_cols, csr_in=csr_in, csr_out=csr_out)
+
+    def drop_coo(self):
+        """Free the int64 edge list once both CSRs exist (16 B/edge); subset ops that need
+        (u, v) pairs recover them from the CSRs."""
+        self.adjacency().drop_coo()
+        self._src = self._dst = None
+
+    def adjacency_csr(self, transpose=False):
+        """(indptr, indices, eid) int64, as _CAPI_DGLGraphGetAdj(handle, transpose, "csr") returns
+        (src/graph/graph_apis.cc:474-482)."""
+        csr = self.out_csr() if transpose else self.in_csr()
+        return csr.indptr, ops.widen(csr.indices), ops.widen(csr.eids)
+
+    def edges(self):
+        """(src, dst) in edge-id order (Graph::Edges, graph.cc:368-409, sorted=False)."""
+        if self._src is None:
+            csr = self.in_csr()
+            src = torch.empty(self._e, dtype=torch.int64, device=self._device)
+            dst = torch.empty(self._e, dtype=torch.int64, device=self._device)
+            e = csr.eids.long()
+            src[e] = csr.indices.long()
+            dst[e] = ops.csr_row_ids(csr)
+            return src, dst
+        return self._src, self._dst
+
+    def in_degrees(self, v=ALL):
+        """Graph::InDegrees (graph.cc:412-424)."""
+        deg = ops.degrees(self.in_csr())
+        return deg if is_all(v) else deg[_as_ids(v, self._device)]
+
+    def out_degrees(self, v=ALL):
+        deg = ops.degrees(self.out_csr())
+        return deg if is_all(v) else deg[_as_ids(v, self._device)]
+
+    # ---- edge queries used by the subset entry points ---------------------------------------
+    @staticmethod
+    def _rows_of(csr, nodes):
+        """Slots of the CSR rows `nodes` (in the order given): (row position, slot) int64."""
+        lo = csr.indptr[nodes]
+        cnt = csr.indptr[nodes + 1] - lo
+        total = int(cnt.sum())
+        which = torch.repeat_interleave(torch.arange(nodes.numel(), device=nodes.device), cnt,
+                                        output_size=total)
+        start = torch.cumsum(cnt, 0) - cnt
+        slot = lo[which] + (torch.arange(total, device=nodes.device) - start[which])
+        return which, slot
+
+    def in_edges(self, v):
+        """(u, v, eid) of the in-edges of nodes v, per node in edge-id order
+        (Graph::InEdges(IdArray), graph.cc:294-319)."""
+        v = _as_ids(v, self._need_device())
+        csr = self.in_csr()
+        which, slot = self._rows_of(csr, v)
+        return csr.indices[slot].long(), v[which], csr.eids[slot].long()
+
+    def out_edges(self, u):
+        """(u, v, eid) of the out-edges of nodes u (Graph::OutEdges(IdArray), graph.cc:340-365)."""
+        u = _as_ids(u, self._need_device())
+        csr = self.out_csr()
+        which, slot = self._rows_of(csr, u)
+        return u[which], csr.indices[slot].long(), csr.eids[slot].long()
+
+    def find_edges(self, eid):
+        """(u, v, eid) of the given edge ids (Graph::FindEdges, graph.cc:252-269)."""
+        eid = _as_ids(eid, self._need_device())
+        src, dst = self.edges()
+        return src[eid], dst[eid], eid
+
+    def edge_ids(self, u, v):
+        """All edges between the pairs (u[i], v[i]) - (src, dst, eid), grouped by pair, ascending
+        edge id inside a pair (Graph::EdgeIds, graph.cc:205-249)."""
+        dev = self._need_device()
+        u = _as_ids(u, dev)
+        v = _as_ids(v, dev)
+        if u.numel() == 1 and v.numel() > 1:
+            u = u.expand(v.numel())
+        if v.numel() == 1 and u.numel() > 1:
+            v = v.expand(u.numel())
+        csr = self.out_csr()                       # row u: (dst, eid) in ascending edge id
+        which, slot = self._rows_of(csr, u)
+        hit = csr.indices[slot].long() == v[which]
+        which, slot = which[hit], slot[hit]
+        return u[which], v[which], csr.eids[slot].long()
+
+    # ---- default functions (graph.py:1700-1798 register_*_func) ------------------------------
+    def register_message_func(self, func):
+        self._message_func = func
+
+    def register_reduce_func(self, func):
+        self._reduce_func = func
+
+    def register_apply_node_func(self, func):
+        self._apply_node_func = func
+
+    def register_apply_edge_func(self, func):
+        self._apply_edge_func = func
+
+    def _defaults(self, message_func, reduce_func, apply_node_func):
+        if message_func == "default":
+            message_func = self._message_func
+        if reduce_func == "default":
+            reduce_func = self._reduce_func
+        if apply_node_func == "default":
+            apply_node_func = self._apply_node_func
+        assert message_func is not None
+        assert reduce_func is not None
+        return message_func, reduce_func, apply_node_func
+
+    # ---- message passing entry points --------------------------------------------------------
+    def _run(self, build):
+        from .plan import Prog
+        prog = Prog()
+        build(prog)
+        self.last_prog = prog
+        if self.execute:
+            prog.run()
+
+    def update_all(self, message_func="default", reduce_func="default", apply_node_func="default"):
+        """python/dgl/graph.py:2398-2441."""
+        from . import scheduler
+        m, r, a = self._defaults(message_func, reduce_func, apply_node_func)
+        self._run(lambda prog: scheduler.schedule_update_all(prog, self, m, r, a))
+
+    def send_and_recv(self, edges, message_func="default", reduce_func="default",
+                      apply_node_func="default", inplace=False):
+        """python/dgl/graph.py:2089-2196.  `edges` is an edge-id container or a (u, v) pair."""
+        from . import scheduler
+        m, r, a = self._defaults(message_func, reduce_func, apply_node_func)
+        if isinstance(edges, tuple):
+            u, v, eid = self.edge_ids(edges[0], edges[1])
+        else:
+            u, v, eid = self.find_edges(edges)
+        if eid.numel() == 0:
+            return   # no edge to be triggered (graph.py:2179-2181)
+        self._run(lambda prog: scheduler.schedule_snr(prog, self, (u, v, eid), m, r, a, inplace))
+
+    def pull(self, v, message_func="default", reduce_func="default", apply_node_func="default",
+             inplace=False):
+        """python/dgl/graph.py:2198-2299."""
+        from . import scheduler
+        m, r, a = self._defaults(message_func, reduce_func, apply_node_func)
+        v = _as_ids(v, self._need_device())
+        if v.numel() == 0:
+            return
+        self._run(lambda prog: scheduler.schedule_pull(prog, self, v, m, r, a, inplace))
+
+    def push(self, u, message_func="default", reduce_func="default", apply_node_func="default",
+             inplace=False):
+        """python/dgl/graph.py:2301-2396: send along the out-edges of u, then receive."""
+        from . import scheduler
+        m, r, a = self._defaults(message_func, reduce_func, apply_node_func)
+        u = _as_ids(u, self._need_device())
+        if u.numel() == 0:
+            return
+        uu, vv, eid = self.out_edges(u)
+        if eid.numel() == 0:
+            return   # scheduler.py:302-305
+        self._run(lambda prog: scheduler.schedule_snr(prog, self, (uu, vv, eid), m, r, a, inplace))
+
+    def apply_nodes(self, func="default", v=ALL, inplace=False):
+        """python/dgl/graph.py:1800-1852."""
+        from . import scheduler
+        if func == "default":
+            func = self._apply_node_func
+        v = None if is_all(v) else _as_ids(v, self._device)
+        self._run(lambda prog: scheduler.schedule_apply_nodes(prog, self, v, func, inplace))
+
+    def apply_edges(self, func="default", edges=ALL, inplace=False):
+        """python/dgl/graph.py:1854-1924."""
+        from . import scheduler
+        if func == "default":
+            func = self._apply_edge_func
+        assert func is not None
+        if is_all(edges):
+            u, v = self.edges()
+            eid = None
+        elif isinstance(edges, tuple):
+            u, v, eid = self.edge_ids(edges[0], edges[1])
+        else:
+            u, v, eid = self.find_edges(edges)
+        self._run(lambda prog: scheduler.schedule_apply_edges(prog, self, u, v, eid, func, inplace))

@@ -15,7 +15,7 @@ from .base import DGLError
 MSG_COPY_SRC, MSG_SRC_MUL_EDGE, MSG_COPY_EDGE = 0, 1, 2
 RED_SUM, RED_MAX = 0, 1
 F32, BF16 = 0, 1
-SDDMM_DOT, SDDMM_ADD, SDDMM_MUL = 0, 1, 2
+SDDMM_DOT, SDDMM_ADD, SDDMM_MUL, SDDMM_COPY_U, SDDMM_COPY_V = 0, 1, 2, 3, 4
 SOFTMAX_STABLE, SOFTMAX_GAT_EXAMPLE = 0, 1
 
 DEFAULT_CHUNK = 512
@@ -94,6 +94,15 @@ def csr_build(row, col, n_rows, n_cols, eid=None, order=0):
                                               order, _ptr(indptr), _ptr(indices), _ptr(eids),
                                               _ptr(ws), nbytes.value, _stream()))
     return CSR(n_rows, n_cols, indptr, indices, eids)
+
+
+def csr_row_block(csr, r0, r1):
+    """Rows [r0, r1) of a CSR as a CSR over the same columns (views of indices / eids; the row
+    pointer is rebased).  This is the 1-D destination-row partition of SURVEY.md 8e."""
+    lo = int(csr.indptr[r0])
+    hi = int(csr.indptr[r1])
+    indptr = (csr.indptr[r0:r1 + 1] - lo).contiguous()
+    return CSR(r1 - r0, csr.n_cols, indptr, csr.indices[lo:hi], csr.eids[lo:hi])
 
 
 def widen(t):
@@ -234,15 +243,16 @@ def sddmm(csr, op, u, v, heads, dim):
     v: (n_rows, heads*dim).  DOT -> (nnz, heads); ADD / MUL -> (nnz, heads*dim); by edge id."""
     lib = _lib.get_lib()
     _need_cuda(u, v)
-    u = u.contiguous()
-    v = v.contiguous()
-    if u.dtype != v.dtype:
+    u = u.contiguous() if u is not None else None
+    v = v.contiguous() if v is not None else None
+    ref = u if u is not None else v
+    if u is not None and v is not None and u.dtype != v.dtype:
         raise DGLError("sddmm: dtype mismatch %s vs %s" % (u.dtype, v.dtype))
     width = heads if op == SDDMM_DOT else heads * dim
-    out = torch.empty((csr.nnz, width), dtype=u.dtype, device=u.device)
-    with torch.cuda.device(u.device):
+    out = torch.empty((csr.nnz, width), dtype=ref.dtype, device=ref.device)
+    with torch.cuda.device(ref.device):
         _lib.check_call(lib.dglb200_sddmm_csr(csr.n_rows, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices),
-                                              _ptr(csr.eids), op, _dtype_code(u), _ptr(u), _ptr(v),
+                                              _ptr(csr.eids), op, _dtype_code(ref), _ptr(u), _ptr(v),
                                               heads, dim, _ptr(out), _stream()))
     return out
 

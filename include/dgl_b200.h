@@ -41,7 +41,11 @@ enum { DGLB200_RED_SUM = 0, DGLB200_RED_MAX = 1 };
 /* storage type of features / edge data; accumulation is always fp32 */
 enum { DGLB200_F32 = 0, DGLB200_BF16 = 1 };
 /* u-op-v edge ops of the SDDMM */
-enum { DGLB200_SDDMM_DOT = 0, DGLB200_SDDMM_ADD = 1, DGLB200_SDDMM_MUL = 2 };
+enum {
+  DGLB200_SDDMM_DOT = 0, DGLB200_SDDMM_ADD = 1, DGLB200_SDDMM_MUL = 2,
+  DGLB200_SDDMM_COPY_U = 3, /* out[e] = u[src]: READ_ROW(nf, u) of _gen_send, runtime/scheduler.py:572-583 */
+  DGLB200_SDDMM_COPY_V = 4  /* out[e] = v[dst]: READ_ROW(nf, v); also d(loss)/d(w) of copy_edge->sum */
+};
 /* edge-softmax flavours of the fused GAT kernel */
 enum {
   DGLB200_SOFTMAX_STABLE = 0,  /* exp(s - rowmax) / sum */
@@ -175,6 +179,7 @@ int dglb200_spmm_csr_backward_x(int64_t n_rows, int64_t nnz,
  *   DOT: out[e(p), h]      = sum_d u[s, h, d] * v[r, h, d]          out is [nnz, heads]
  *   ADD: out[e(p), h, d]   = u[s, h, d] + v[r, h, d]                out is [nnz, heads*dim]
  *   MUL: out[e(p), h, d]   = u[s, h, d] * v[r, h, d]
+ *   COPY_U / COPY_V: out[e(p), h, d] = u[s, h, d]  /  v[r, h, d]   (the unused operand may be NULL)
  * DOT is d(loss)/d(w) of SRC_MUL_EDGE (u = x, v = dy) and the u.v attention score
  * the north-star names; ADD is the reference GAT example's a1[src] + a2[dst]
  * (examples/pytorch/gat/train.py:90-92; replaces READ_ROW x2 + EDGE_UDF of
