@@ -50,9 +50,10 @@ struct SpmmArgs {
   float* partial;
   int32_t* partial_arg;
   int64_t n_chunk_warps;   // leading warps of the grid that process slices
+  int slab_chunks;         // cap on the 16-byte chunks of a feature row per pass (0 = whole row)
 };
 
-constexpr int kSpmmThreads = 256;
+constexpr int kSpmmThreads = 128;  // measured: 128 > 256 > 512 on C2 at every slab width
 constexpr int kSpmmWarps = kSpmmThreads / 32;
 // One pipeline stage: the U edges of a step, their loaded rows and per-edge scalars.
 template <int U, int TILES, int VEC, bool MUL, bool MASKED>
@@ -341,7 +342,10 @@ int launch_shape(const SpmmArgs& a, cudaStream_t stream) {
   bool handled = false;
   const int rc = launch_tuned<T, VEC, MSG, RED>(a, stream, &handled);
   if (handled || rc != 0) return rc;
-  const int64_t chunks = ceil_div(a.feat, VEC);
+  int64_t chunks = ceil_div(a.feat, VEC);
+  // L2-residency slabbing (run_spmm): a narrower pass keeps one feature slab of every source row
+  // in the 126 MB L2 while all destination rows are visited; the slab index is blockIdx.y.
+  if (a.slab_chunks > 0 && VEC > 1 && a.slab_chunks < chunks) chunks = a.slab_chunks;
   if (chunks <= 4) return launch_one<T, VEC, 4, 1, MSG, RED>(a, stream);
   if (chunks <= 8) return launch_one<T, VEC, 8, 1, MSG, RED>(a, stream);
   if (chunks <= 16) return launch_one<T, VEC, 16, 1, MSG, RED>(a, stream);

@@ -232,7 +232,7 @@ def spmm_backward_x(csr_t, dy, w=None, w_width=1, arg=None, chunk=DEFAULT_CHUNK)
         w = w.contiguous()
     with torch.cuda.device(dy.device):
         _lib.check_call(lib.dglb200_spmm_csr_backward_x(
-            csr_t.n_rows, csr_t.nnz, _ptr(csr_t.indptr), _ptr(csr_t.indices), _ptr(csr_t.eids),
+            csr_t.n_rows, csr_t.n_cols, csr_t.nnz, _ptr(csr_t.indptr), _ptr(csr_t.indices), _ptr(csr_t.eids),
             _dtype_code(dy), _ptr(dy), feat, _ptr(w), w_width, _ptr(arg), _ptr(dx), plan_ref,
             _stream()))
     return dx

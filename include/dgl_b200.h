@@ -127,7 +127,10 @@ int dglb200_csr_row_ids(int64_t n_rows, int64_t nnz, const int64_t* indptr, int6
  *
  * `plan` (nullable) is the long-row split table made by dglb200_spmm_plan for this indptr;
  * without it every row is reduced by a single warp group (correct, slower on hub rows).
- * x_rows bounds-checks nothing at run time; it is recorded for error messages only.
+ * x_rows bounds-checks nothing at run time; it sizes the L2-residency slab choice: when the
+ * gathered operand (x_rows * feat) exceeds about half of the L2 and rows are re-used (mean degree
+ * >= 8) the feature dimension is processed in slabs narrow enough for one slab of every source
+ * row to stay L2-resident (results do not depend on the slab width).
  */
 typedef struct dglb200_spmm_plan_t {
   int32_t chunk;              /* edges per work item for long rows (multiple of 32) */
@@ -163,10 +166,11 @@ int dglb200_spmm_csr(int64_t n_rows, int64_t x_rows, int64_t nnz,
  * src (rows = source nodes, indices = dst, eids = edge id):
  *   dx[u, f] = sum_{p in row u} [arg == NULL or arg[indices[p], f] == e(p)] * wgt * dy[indices[p], f]
  *   wgt = 1, or w[e(p), f / (feat / w_width)] when w != NULL (src_mul_edge).
+ * dy_rows = number of rows of dy (destination nodes); it only steers the L2 slab choice.
  * Deterministic (no atomics).  This is what torch's sparse.mm backward provides in the
  * reference (call site backend/pytorch/tensor.py:146).
  */
-int dglb200_spmm_csr_backward_x(int64_t n_rows, int64_t nnz,
+int dglb200_spmm_csr_backward_x(int64_t n_rows, int64_t dy_rows, int64_t nnz,
                                 const int64_t* indptr, const int32_t* indices, const int32_t* eids,
                                 int dtype, const void* dy, int64_t feat,
                                 const void* w, int64_t w_width, const int32_t* arg,
