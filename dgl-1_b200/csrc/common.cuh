@@ -85,6 +85,15 @@ __device__ __forceinline__ int64_t ld_stream_i64(const int64_t* p) {
   return v;
 }
 
+// base + id * row_bytes as ONE instruction (IMAD.WIDE.U32 with a 64-bit addend).  Written in PTX
+// because the compiler otherwise splits a uniform base from the per-lane offset (3 instructions
+// per gathered row in the SpMM inner loop).
+__device__ __forceinline__ const char* row_ptr(const char* base, uint32_t id, uint32_t row_bytes) {
+  uint64_t r;
+  asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(id), "r"(row_bytes), "l"(base));
+  return reinterpret_cast<const char*>(r);
+}
+
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
 __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {

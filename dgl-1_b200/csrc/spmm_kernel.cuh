@@ -78,8 +78,10 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
   constexpr int kBudget = kMul ? 16 : 32;
   constexpr int U0 = kBudget / (TILES * VEC);
   constexpr int UA = U0 >= 4 ? 4 : (U0 >= 2 ? 2 : 1);
-  constexpr int U = UCAP > 0 ? (UCAP < G ? UCAP : G) : UA;  // UCAP > 0: tuning override
-  constexpr int SPI = G / U;  // steps served by one coalesced index load
+  constexpr int U1 = UCAP > 0 ? UCAP : UA;                 // UCAP > 0: tuning override
+  constexpr int U = U1 * 2 <= G ? U1 : G / 2;              // at least two steps per index block
+  constexpr int SPI = G / U;  // steps served by one coalesced index load (even)
+  static_assert(SPI >= 2 && SPI % 2 == 0, "pipeline needs an even number of steps per block");
   using Stage = SpmmStage<U, TILES, VEC, kMul, kMasked>;
 
   const int lane = threadIdx.x & 31;
@@ -120,14 +122,23 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
   }
 
   // ---- per-lane feature ownership --------------------------------------------------------
-  const T* __restrict__ x = static_cast<const T*>(a.x);
   const T* __restrict__ w = static_cast<const T*>(a.w);
   int64_t foff[TILES];
   bool fvalid[TILES];
+  // Byte bases of the gathered operands with this lane's feature offset folded in.  Lanes past
+  // the end of the row (fvalid false) read offset 0 instead: their values are never stored, and
+  // the hot loop then needs no per-lane predicate.  A row address is base + id * row_bytes:
+  // one IMAD.WIDE.U32 (ids and row_bytes are < 2^32).
+  const char* xb[TILES];   // x (or, for COPY_EDGE, the edge data) + feature offset
+  const char* wb[TILES];   // element-wise edge weights + feature offset
+  const uint32_t row_bytes = (uint32_t)(a.feat * (int64_t)sizeof(T));
 #pragma unroll
   for (int t = 0; t < TILES; ++t) {
     foff[t] = fbase + (int64_t)(t * G + gl) * VEC;
     fvalid[t] = foff[t] < a.feat;
+    const int64_t fo = fvalid[t] ? foff[t] : 0;
+    xb[t] = static_cast<const char*>(MSG == DGLB200_MSG_COPY_EDGE ? a.w : a.x) + fo * (int64_t)sizeof(T);
+    wb[t] = static_cast<const char*>(a.w) + fo * (int64_t)sizeof(T);
   }
   const bool w_scalar = kMul && a.w != nullptr && a.w_mode == kWScalar;
   const bool w_full = kMul && a.w != nullptr && a.w_mode == kWFull;
@@ -143,9 +154,16 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
       if constexpr (kMax) best[t][v] = -1;
     }
 
+  // Index blocks: G consecutive slots of the item, read coalesced by the group.  A block is FULL
+  // when every group of the warp has all of its G slots inside its item: those blocks run with
+  // no validity predicates at all.  The remaining (tail) blocks use predicated loads.
   const int len = (int)(end - start);
-  int steps = (len + U - 1) / U;
-  if (G < 32) steps = __reduce_max_sync(0xffffffffu, steps);
+  int nblk = (len + G - 1) / G;
+  int full_blk = len / G;
+  if (G < 32) {
+    nblk = __reduce_max_sync(0xffffffffu, nblk);
+    full_blk = __reduce_min_sync(0xffffffffu, full_blk);
+  }
 
   // coalesced read of G column ids (+ edge ids, scalar weights) of index block `it`
   auto load_idx = [&](int it, int32_t& s, int32_t& e, float& wsc) {
@@ -158,7 +176,8 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
     }
   };
   // issue every global load of one step; nothing here depends on another in-flight load
-  auto load_stage = [&](Stage& st, int32_t s, int32_t e, float wsc, int jj) {
+  auto load_stage = [&](auto full_tag, Stage& st, int32_t s, int32_t e, float wsc, int jj) {
+    constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
     for (int k = 0; k < U; ++k) {
       st.s[k] = __shfl_sync(0xffffffffu, s, jj + k, G);
@@ -167,42 +186,43 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
     }
 #pragma unroll
     for (int k = 0; k < U; ++k) {
+      const uint32_t gid = (uint32_t)(MSG == DGLB200_MSG_COPY_EDGE ? st.e[k] : st.s[k]);
 #pragma unroll
       for (int t = 0; t < TILES; ++t) {
-        const bool ok = st.s[k] >= 0 && fvalid[t];
+        const bool ok = FULL || (st.s[k] >= 0 && fvalid[t]);
+        if constexpr (!FULL) {
 #pragma unroll
-        for (int v = 0; v < VEC; ++v) st.xv[k][t][v] = kMax ? -INFINITY : 0.f;
+          for (int v = 0; v < VEC; ++v) st.xv[k][t][v] = kMax ? -INFINITY : 0.f;
+        }
         if (ok) {
-          if (MSG == DGLB200_MSG_COPY_EDGE)
-            Chunk<T, VEC>::load(w + (int64_t)st.e[k] * a.feat + foff[t], st.xv[k][t]);
-          else
-            Chunk<T, VEC>::load(x + (int64_t)st.s[k] * a.feat + foff[t], st.xv[k][t]);
+          Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(xb[t], gid, row_bytes)), st.xv[k][t]);
           if constexpr (kMul) {
             if (w_full) {
-              Chunk<T, VEC>::load(w + (int64_t)st.e[k] * a.feat + foff[t], st.wv[k][t]);
+              Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(wb[t], (uint32_t)st.e[k], row_bytes)),
+                                  st.wv[k][t]);
             } else if (w_grouped) {
 #pragma unroll
               for (int v = 0; v < VEC; ++v)
-                st.wv[k][t][v] =
-                    to_float(w[(int64_t)st.e[k] * a.w_width + (foff[t] + v) / a.w_group]);
+                st.wv[k][t][v] = fvalid[t] ? to_float(w[(int64_t)st.e[k] * a.w_width + (foff[t] + v) / a.w_group]) : 0.f;
             }
           }
           if constexpr (kMasked) {
 #pragma unroll
             for (int v = 0; v < VEC; ++v)
-              st.am[k][t][v] = a.arg ? a.arg[(int64_t)st.s[k] * a.feat + foff[t] + v] : st.e[k];
+              st.am[k][t][v] = (a.arg && fvalid[t]) ? a.arg[(int64_t)st.s[k] * a.feat + foff[t] + v] : st.e[k];
           }
         }
       }
     }
   };
   // fold one step into the accumulators, strictly in slot order
-  auto consume = [&](const Stage& st) {
+  auto consume = [&](auto full_tag, const Stage& st) {
+    constexpr bool FULL = decltype(full_tag)::value;
 #pragma unroll
     for (int k = 0; k < U; ++k) {
 #pragma unroll
       for (int t = 0; t < TILES; ++t) {
-        const bool ok = st.s[k] >= 0 && fvalid[t];
+        const bool ok = FULL || (st.s[k] >= 0 && fvalid[t]);
 #pragma unroll
         for (int v = 0; v < VEC; ++v) {
           float m = st.xv[k][t][v];
@@ -221,28 +241,37 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
       }
     }
   };
-
-  if (steps > 0) {
+  // Blocks [b0, b1): two-stage software pipeline (the loads of step q+1 are in flight while step
+  // q is accumulated), fully unrolled inside a block so both stages are fixed registers (SPI is
+  // even); the next block's indices are prefetched one block ahead.
+  auto run_blocks = [&](auto full_tag, int b0, int b1) {
+    if (b0 >= b1) return;
     int32_t sA, eA, sB, eB;
     float wA, wB;
-    load_idx(0, sA, eA, wA);
-    load_idx(1, sB, eB, wB);
-    Stage st0, st1;
-    load_stage(st0, sA, eA, wA, 0);
-    // two-stage software pipeline, unrolled by two so the stages are fixed registers
-    for (int q = 0; q < steps; q += 2) {
-      int qn = q + 1;
-      if (qn % SPI == 0) { sA = sB; eA = eB; wA = wB; load_idx(qn / SPI + 1, sB, eB, wB); }
-      if (qn < steps) load_stage(st1, sA, eA, wA, (qn % SPI) * U);
-      consume(st0);
-      if (qn < steps) {
-        qn = q + 2;
-        if (qn % SPI == 0) { sA = sB; eA = eB; wA = wB; load_idx(qn / SPI + 1, sB, eB, wB); }
-        if (qn < steps) load_stage(st0, sA, eA, wA, (qn % SPI) * U);
-        consume(st1);
+    Stage st[2];
+    load_idx(b0, sA, eA, wA);
+    load_idx(b0 + 1, sB, eB, wB);
+    load_stage(full_tag, st[0], sA, eA, wA, 0);
+    for (int b = b0; b < b1; ++b) {
+      // steps are taken in pairs so that the two stages are fixed registers; the pair loop is
+      // not unrolled (code size), the shuffle lane index is a runtime value
+#pragma unroll 1
+      for (int j = 0; j < SPI; j += 2) {
+        load_stage(full_tag, st[1], sA, eA, wA, (j + 1) * U);
+        consume(full_tag, st[0]);
+        if (j + 2 < SPI) {
+          load_stage(full_tag, st[0], sA, eA, wA, (j + 2) * U);
+        } else {
+          sA = sB; eA = eB; wA = wB;
+          load_idx(b + 2, sB, eB, wB);
+          if (b + 1 < b1) load_stage(full_tag, st[0], sA, eA, wA, 0);
+        }
+        consume(full_tag, st[1]);
       }
     }
-  }
+  };
+  run_blocks(std::true_type{}, 0, full_blk);
+  run_blocks(std::false_type{}, full_blk, nblk);
 
   // ---- epilogue ---------------------------------------------------------------------------
   if (out_row < 0) return;
@@ -323,10 +352,9 @@ int launch_tuned(const SpmmArgs& a, cudaStream_t stream, bool* handled) {
   if (u == UC && sc == G_ * TL && nt == NT_) \
     return launch_one<T, VEC, G_, TL, MSG, RED, UC, NT_>(a, stream);
 #define DGLB200_TUNED_U(G_, TL, NT_) \
-  DGLB200_TUNED(1, G_, TL, NT_) DGLB200_TUNED(2, G_, TL, NT_) DGLB200_TUNED(4, G_, TL, NT_) \
-  DGLB200_TUNED(8, G_, TL, NT_)
+  DGLB200_TUNED(2, G_, TL, NT_) DGLB200_TUNED(4, G_, TL, NT_)
 #define DGLB200_TUNED_NT(G_, TL) \
-  DGLB200_TUNED_U(G_, TL, 128) DGLB200_TUNED_U(G_, TL, 256) DGLB200_TUNED_U(G_, TL, 512)
+  DGLB200_TUNED_U(G_, TL, 128) DGLB200_TUNED_U(G_, TL, 256)
     DGLB200_TUNED_NT(16, 1) DGLB200_TUNED_NT(32, 1) DGLB200_TUNED_NT(32, 2)
 #undef DGLB200_TUNED_NT
 #undef DGLB200_TUNED_U
