@@ -199,15 +199,6 @@ class ClockSampler(object):
 # B200 arm
 # ---------------------------------------------------------------------------------------------
 
-def edge_balanced_bounds(indptr_in, indptr_out, parts):
-    """Row-block boundaries with (in + out) edges balanced across `parts` ranks."""
-    load = (indptr_in + indptr_out).to(torch.float64)
-    total = float(load[-1])
-    targets = torch.arange(1, parts, dtype=torch.float64, device=load.device) * (total / parts)
-    cuts = torch.searchsorted(load, targets).tolist()
-    return [0] + [int(c) for c in cuts] + [int(indptr_in.shape[0] - 1)]
-
-
 def run_b200(args):
     import torch.distributed as dist
     from dgl_b200 import ops, _lib
@@ -238,39 +229,32 @@ def run_b200(args):
     torch.cuda.synchronize()
     t_build = time.time() - t0
 
+    from dgl_b200.dist import RowPartition
+    part = RowPartition(csr_in, csr_out, rank=rank, world=world)
+    bounds, r0, r1, rows = part.bounds, part.r0, part.r1, part.rows
+    loc_in, loc_out = part.loc_in, part.loc_out
     if world > 1:
-        bounds = edge_balanced_bounds(csr_in.indptr, csr_out.indptr, world)
-        r0, r1 = bounds[rank], bounds[rank + 1]
-        loc_in = ops.csr_row_block(csr_in, r0, r1)
-        loc_out = ops.csr_row_block(csr_out, r0, r1)
         del csr_in, csr_out
         g.clear_cache()
         torch.cuda.empty_cache()
-    else:
-        bounds = [0, n]
-        r0, r1 = 0, n
-        loc_in, loc_out = csr_in, csr_out
-    rows = r1 - r0
     loc_in.plan()
     loc_out.plan()
 
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
-    x_full = torch.empty(n, feat, device=dev)
-    dy_full = torch.empty(n, feat, device=dev)
+    x_full = part.full_buffer("x", feat, torch.empty(0, device=dev))
+    dy_full = part.full_buffer("dy", feat, torch.empty(0, device=dev))
     x_full[r0:r1] = torch.randn(rows, feat, device=dev, generator=gen)
     dy_full[r0:r1] = torch.randn(rows, feat, device=dev, generator=gen)
+    x_loc, dy_loc = x_full[r0:r1], dy_full[r0:r1]       # this rank's blocks live inside the gather buffers
     y_loc = torch.empty(rows, feat, device=dev)
     dx_loc = torch.empty(rows, feat, device=dev)
-    x_views = [x_full[bounds[p]:bounds[p + 1]] for p in range(world)]
-    dy_views = [dy_full[bounds[p]:bounds[p + 1]] for p in range(world)]
 
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
     kern_events = []
 
     def step(record):
-        if world > 1:
-            dist.all_gather(x_views, x_views[rank])
+        part.all_gather_rows(x_loc, "x")          # halo exchange (no-op at world == 1)
         if record:
             a, b = ev(), ev()
             a.record()
@@ -278,8 +262,7 @@ def run_b200(args):
         if record:
             b.record()
             kern_events.append((a, b))
-        if world > 1:
-            dist.all_gather(dy_views, dy_views[rank])
+        part.all_gather_rows(dy_loc, "dy")
         if record:
             a, b = ev(), ev()
             a.record()
