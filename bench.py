@@ -229,10 +229,17 @@ def run_b200(args):
     torch.cuda.synchronize()
     t_build = time.time() - t0
 
-    from dgl_b200.dist import RowPartition
-    part = RowPartition(csr_in, csr_out, rank=rank, world=world)
+    from dgl_b200.dist import HaloPartition, RowPartition
+    exchange = args.exchange
+    if exchange == "auto":   # compacted halo pays when rows are referenced rarely (C5: mean degree 3)
+        exchange = "halo" if (world > 1 and e < 16 * n) else "allgather"
+    Part = HaloPartition if exchange == "halo" else RowPartition
+    part = Part(csr_in, csr_out, rank=rank, world=world)
     bounds, r0, r1, rows = part.bounds, part.r0, part.r1, part.rows
     loc_in, loc_out = part.loc_in, part.loc_out
+    check_ref = None
+    if args.check and world > 1:      # reference for --check: the un-remapped row block + a plain all-gather
+        check_ref = RowPartition(csr_in, csr_out, rank=rank, world=world)
     if world > 1:
         del csr_in, csr_out
         g.clear_cache()
@@ -242,11 +249,11 @@ def run_b200(args):
 
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
-    x_full = part.full_buffer("x", feat, torch.empty(0, device=dev))
-    dy_full = part.full_buffer("dy", feat, torch.empty(0, device=dev))
-    x_full[r0:r1] = torch.randn(rows, feat, device=dev, generator=gen)
-    dy_full[r0:r1] = torch.randn(rows, feat, device=dev, generator=gen)
-    x_loc, dy_loc = x_full[r0:r1], dy_full[r0:r1]       # this rank's blocks live inside the gather buffers
+    like = torch.empty(0, device=dev)
+    x_loc = part.local_view("x", feat, like)            # this rank's blocks live inside the exchange buffers
+    dy_loc = part.local_view("dy", feat, like)
+    x_loc.copy_(torch.randn(rows, feat, device=dev, generator=gen))
+    dy_loc.copy_(torch.randn(rows, feat, device=dev, generator=gen))
     y_loc = torch.empty(rows, feat, device=dev)
     dx_loc = torch.empty(rows, feat, device=dev)
 
@@ -254,7 +261,7 @@ def run_b200(args):
     kern_events = []
 
     def step(record):
-        part.all_gather_rows(x_loc, "x")          # halo exchange (no-op at world == 1)
+        x_full = part.exchange("x", x_loc)        # halo exchange (no-op at world == 1)
         if record:
             a, b = ev(), ev()
             a.record()
@@ -262,7 +269,7 @@ def run_b200(args):
         if record:
             b.record()
             kern_events.append((a, b))
-        part.all_gather_rows(dy_loc, "dy")
+        dy_full = part.exchange("dy", dy_loc)
         if record:
             a, b = ev(), ev()
             a.record()
@@ -318,7 +325,27 @@ def run_b200(args):
 
     # ---- e2e: host API with HOST feature buffers ---------------------------------------------
     e2e = None
-    if world == 1 and not args.no_e2e:
+    if check_ref is not None:
+        # multi-GPU parity: the exchange under test vs the full all-gather path, same local kernel
+        want_y = check_ref.forward(x_loc.clone())
+        want_dx = check_ref.backward(dy_loc.clone())
+        step(False)
+        torch.cuda.synchronize()
+        ok = torch.allclose(y_loc, want_y, rtol=1e-5, atol=1e-5 * float(want_y.abs().max())) and \
+            torch.allclose(dx_loc, want_dx, rtol=1e-5, atol=1e-5 * float(want_dx.abs().max()))
+        flag = torch.tensor([1 if ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) != 1:
+            raise SystemExit("rank %d: --check FAILED: exchange '%s' disagrees with the all-gather path" % (rank, exchange))
+        del want_y, want_dx
+        check_ref = None
+    xchg_bytes = part.exchange_bytes(feat)
+    del x_loc, dy_loc, y_loc, dx_loc
+    part._full.clear()
+    if exchange == "halo":
+        part.halo_in._buf = part.halo_out._buf = None
+    torch.cuda.empty_cache()
+    if world == 1 and not args.no_e2e and n * feat * 4 <= (8 << 30):
         from dgl_b200 import function as fn
         xh = torch.randn(n, feat).pin_memory()
         dyh = torch.randn(n, feat).pin_memory()
@@ -365,11 +392,14 @@ def run_b200(args):
             "config": {"workload": cfg["name"], "n": n, "e": e, "feat": feat,
                        "l2": "inputs_exceed_l2 (X %.0f MB + structure %.0f MB per SpMM; no flush)"
                              % (n * feat * 4 / 1e6, e * 4 / 1e6),
-                       "parallelism": "row-partition x%d + NCCL all-gather halo" % world,
+                       "parallelism": "row-partition x%d + NCCL %s" % (
+                           world, "compacted-halo all_to_all" if exchange == "halo" else "all-gather halo"),
+                       "exchange_bytes_per_rank_per_spmm": xchg_bytes,
                        "graph_build_s": round(t_build, 2)},
             "edge_feat_per_s": 2 * e * feat / (ms_step * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches), "clocks": clocks,
+            "checked": bool(args.check and world > 1),
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -383,6 +413,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c5", "tiny"])
+    ap.add_argument("--exchange", default="auto", choices=["auto", "allgather", "halo"])
+    ap.add_argument("--check", action="store_true", help="N>1: verify the exchange against the all-gather path")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

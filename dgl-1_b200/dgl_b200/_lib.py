@@ -70,6 +70,7 @@ SIGNATURES = {
     "dglb200_unique_workspace_bytes": (c_int, [c_i64, ctypes.POINTER(c_sz)]),
     "dglb200_unique_sorted": (c_int, [c_i64, c_i64, c_vp, c_vp, c_vp, ctypes.POINTER(c_i64),
                                       c_vp, c_sz, c_vp]),
+    "dglb200_gather_rows": (c_int, [c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "dglb200_register_packed_funcs": (c_int, [c_vp, c_int]),
 }
 

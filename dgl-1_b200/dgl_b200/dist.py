@@ -77,20 +77,129 @@ class RowPartition(object):
             return full
         if views[self.rank].data_ptr() != local.data_ptr():
             views[self.rank].copy_(local)
-        # uneven blocks: one broadcast per owner (what NCCL's uneven all_gather does internally;
-        # gloo has no uneven all_gather), issued together and awaited together
+        if dist.get_backend(self.group) == "nccl":
+            # uneven blocks: NCCL runs them as ONE grouped launch of per-owner broadcasts, all links
+            # busy in both directions at once
+            dist.all_gather(views, views[self.rank], group=self.group)
+            return full
+        # gloo (CPU tests) has no uneven all_gather: one broadcast per owner
         works = [dist.broadcast(views[p], src=self._global_rank(p), group=self.group, async_op=True)
                  for p in range(self.world) if views[p].numel() > 0]
         for w in works:
             w.wait()
         return full
 
+    # -- exchange interface (same on HaloPartition) --------------------------------------------
+    def local_view(self, key, feat, like):
+        """Where this rank's block of the 'x' / 'dy' operand lives inside the exchange buffer:
+        filling it in place saves the copy."""
+        return self.full_buffer(key, feat, like)[self.r0:self.r1]
+
+    def exchange(self, key, local):
+        """Make every source row the local SpMM needs available; returns the gather operand."""
+        return self.all_gather_rows(local, key)
+
+    def exchange_bytes(self, feat, elem=4):
+        """Bytes this rank receives per exchange."""
+        return (self.n - self.rows) * feat * elem if self.world > 1 else 0
+
     def forward(self, x_local, out=None):
         """y_local = (A x)[r0:r1] for update_all(copy_src, sum)."""
-        x_full = self.all_gather_rows(x_local, "x")
-        return self._spmm(self.loc_in, x_full, out)
+        return self._spmm(self.loc_in, self.exchange("x", x_local), out)
 
     def backward(self, dy_local, out=None):
         """dx_local = (A^T dy)[r0:r1]."""
-        dy_full = self.all_gather_rows(dy_local, "dy")
-        return self._spmm(self.loc_out, dy_full, out)
+        return self._spmm(self.loc_out, self.exchange("dy", dy_local), out)
+
+
+class HaloExchange(object):
+    """Compacted halo plan for one CSR row block (a full all-gather of X moves
+    n * feat per rank; only the DISTINCT remote rows a rank's edges reference are needed -
+    measured on C5 at 8 ranks: 9 % of the full volume, 2.0 GB instead of 23.5 GB per rank).
+
+    Plan time (one-off per graph and partition, integer plumbing):
+      * the sorted unique remote column ids of the block, split by owner       -> what I receive
+      * an all-to-all of those id lists                                         -> what I send
+      * the block's column ids remapped into the compact row space
+        [own rows | halo rows from owner 0 | owner 1 | ...]
+    Per call: pack the rows the others need (gather_rows kernel), one all_to_all_single straight
+    into the halo region of the compact feature buffer, then the local SpMM over the remapped CSR.
+    """
+
+    def __init__(self, csr_block, bounds, rank, world, group=None, gather_fn=None):
+        self.group, self.rank, self.world = group, rank, world
+        self.bounds = bounds
+        self.r0, self.r1 = bounds[rank], bounds[rank + 1]
+        self.rows = self.r1 - self.r0
+        self._gather = gather_fn or ops.gather_rows
+        dev = csr_block.indices.device
+        cols = csr_block.indices.long()
+        own = (cols >= self.r0) & (cols < self.r1)
+        halo_ids = torch.unique(cols[~own])                       # sorted ascending, own range absent
+        b = torch.tensor(bounds, dtype=torch.int64, device=dev)
+        cut = torch.searchsorted(halo_ids, b)
+        self.recv_counts = (cut[1:] - cut[:-1]).tolist()          # rows I need from every owner
+        assert self.recv_counts[rank] == 0
+        new_cols = torch.where(own, cols - self.r0, self.rows + torch.searchsorted(halo_ids, cols))
+        self.n_halo = int(halo_ids.numel())
+        self.csr = ops.CSR(csr_block.n_rows, self.rows + self.n_halo, csr_block.indptr,
+                           new_cols.to(torch.int32), csr_block.eids)
+        del cols, own, new_cols
+        # tell every owner which of its rows I need
+        rc = torch.tensor(self.recv_counts, dtype=torch.int64, device=dev)
+        sc = torch.empty_like(rc)
+        if world > 1:
+            dist.all_to_all_single(sc, rc, group=group)
+        else:
+            sc.copy_(rc)
+        self.send_counts = sc.tolist()
+        serve = torch.empty(int(sum(self.send_counts)), dtype=torch.int64, device=dev)
+        if world > 1:
+            dist.all_to_all_single(serve, halo_ids, output_split_sizes=self.send_counts,
+                                   input_split_sizes=self.recv_counts, group=group)
+        self.serve_local = (serve - self.r0).contiguous()        # my rows to pack, grouped by requester
+        self._buf = None
+
+    def buffer(self, feat, like):
+        """Compact feature buffer [rows + n_halo, feat]; rows [0, rows) are this rank's block."""
+        if (self._buf is None or self._buf.shape[1] != feat or self._buf.dtype != like.dtype or
+                self._buf.device != like.device):
+            self._buf = torch.empty((self.rows + self.n_halo, feat), dtype=like.dtype, device=like.device)
+        return self._buf
+
+    def exchange(self, x_local):
+        """Returns the compact buffer with own rows and freshly received halo rows."""
+        buf = self.buffer(x_local.shape[1], x_local)
+        own = buf[:self.rows]
+        if own.data_ptr() != x_local.data_ptr():
+            own.copy_(x_local)
+        if self.world > 1:
+            send = self._gather(own, self.serve_local)
+            dist.all_to_all_single(buf[self.rows:], send, output_split_sizes=self.recv_counts,
+                                   input_split_sizes=self.send_counts, group=self.group)
+        return buf
+
+    def halo_bytes(self, feat, elem=4):
+        return self.n_halo * feat * elem
+
+
+class HaloPartition(RowPartition):
+    """RowPartition whose exchange is the compacted halo instead of the full all-gather."""
+
+    def __init__(self, csr_in, csr_out, rank=None, world=None, group=None, spmm_fn=None, gather_fn=None):
+        super(HaloPartition, self).__init__(csr_in, csr_out, rank, world, group, spmm_fn)
+        self.halo_in = HaloExchange(self.loc_in, self.bounds, self.rank, self.world, group, gather_fn)
+        self.halo_out = HaloExchange(self.loc_out, self.bounds, self.rank, self.world, group, gather_fn)
+        self.loc_in, self.loc_out = self.halo_in.csr, self.halo_out.csr
+
+    def _halo(self, key):
+        return self.halo_in if key == "x" else self.halo_out
+
+    def local_view(self, key, feat, like):
+        return self._halo(key).buffer(feat, like)[:self.rows]
+
+    def exchange(self, key, local):
+        return self._halo(key).exchange(local)
+
+    def exchange_bytes(self, feat, elem=4):
+        return max(self.halo_in.n_halo, self.halo_out.n_halo) * feat * elem

@@ -349,3 +349,22 @@ def unique_sorted(ids, id_bound, want_inverse=True):
         _lib.check_call(lib.dglb200_unique_sorted(n, int(id_bound), _ptr(ids), _ptr(uniq), _ptr(inv),
                                                   counts, _ptr(ws), nbytes.value, _stream()))
     return uniq[:int(counts[0])], inv
+
+
+def gather_rows(x, idx, out=None):
+    """out[i] = x[idx[i]] (dglb200_gather_rows); idx int64 CUDA.  READ_ROW / halo packing."""
+    lib = _lib.get_lib()
+    _need_cuda(x, idx)
+    x = x.contiguous()
+    idx = idx.contiguous()
+    if idx.dtype != torch.int64:
+        raise DGLError("gather_rows: ids must be int64")
+    n_out = int(idx.shape[0])
+    if out is None:
+        out = torch.empty((n_out,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+    row_bytes = x.element_size() * (x.numel() // max(int(x.shape[0]), 1)) if x.shape[0] else x.element_size()
+    bad = torch.zeros(1, dtype=torch.int32, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check_call(lib.dglb200_gather_rows(n_out, _ptr(idx), int(x.shape[0]), _ptr(x), row_bytes,
+                                                _ptr(out), _ptr(bad), _stream()))
+    return out

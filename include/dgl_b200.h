@@ -262,6 +262,18 @@ int dglb200_unique_sorted(int64_t n, int64_t id_bound, const int64_t* ids,
                           int64_t* uniq, int64_t* inverse, int64_t* counts_host,
                           void* workspace, size_t workspace_bytes, void* stream);
 
+/* ---- row gather --------------------------------------------------------------------------- */
+
+/*
+ * out[i, :] = x[idx[i], :] for rows of row_bytes bytes (any dtype).  READ_ROW / F.gather_row of the
+ * reference (python/dgl/runtime/ir/executor.py:365-394; python/dgl/backend/pytorch/tensor.py:108-109)
+ * and the send-side packing of the multi-GPU halo exchange.  idx int64[n_out] on the device, values
+ * in [0, x_rows); an out-of-range id sets *bad_flag (device int32, caller-zeroed; nullable is NOT
+ * allowed) and leaves that output row untouched.  Does not sync.
+ */
+int dglb200_gather_rows(int64_t n_out, const int64_t* idx, int64_t x_rows, const void* x,
+                        int64_t row_bytes, void* out, int32_t* bad_flag, void* stream);
+
 /* ---- hook into the reference's PackedFunc registry ----------------------------------- */
 
 /*

@@ -38,15 +38,20 @@ def _oracle_block_spmm(csr, x, out):
     return torch.from_numpy(y)
 
 
-def _worker(rank, world, port, n, e, feat, q):
+def _worker(rank, world, port, n, e, feat, q, halo=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
-        from dgl_b200.dist import RowPartition
+        from dgl_b200.dist import HaloPartition, RowPartition
         src, dst = random_graph(n, e, 7, hubs=3, hub_deg=n // 2, zero_deg_frac=0.1)
-        part = RowPartition(_csr_cpu(src, dst, n, False), _csr_cpu(src, dst, n, True),
-                            spmm_fn=_oracle_block_spmm)
+        if halo:
+            part = HaloPartition(_csr_cpu(src, dst, n, False), _csr_cpu(src, dst, n, True),
+                                 spmm_fn=_oracle_block_spmm, gather_fn=lambda x, idx: x[idx])
+            assert part.halo_in.n_halo <= n - part.rows
+        else:
+            part = RowPartition(_csr_cpu(src, dst, n, False), _csr_cpu(src, dst, n, True),
+                                spmm_fn=_oracle_block_spmm)
         rng = np.random.RandomState(3)
         x = rng.randn(n, feat).astype(np.float32)
         dy = rng.randn(n, feat).astype(np.float32)
@@ -57,13 +62,13 @@ def _worker(rank, world, port, n, e, feat, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world", [2, 3])
-def test_row_partition_gloo(world):
+@pytest.mark.parametrize("world,halo", [(2, False), (3, False), (2, True), (3, True)])
+def test_row_partition_gloo(world, halo):
     n, e, feat = 300, 5000, 12
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, n, e, feat, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, e, feat, q, halo)) for r in range(world)]
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
