@@ -327,18 +327,28 @@ def run_b200(args):
     e2e = None
     if check_ref is not None:
         # multi-GPU parity: the exchange under test vs the full all-gather path, same local kernel
-        want_y = check_ref.forward(x_loc.clone())
-        want_dx = check_ref.backward(dy_loc.clone())
+        def same(a, b):      # chunked: the operands can be tens of GB
+            ok_, scale = True, float(b.abs().max()) + 1e-30
+            for s0 in range(0, a.shape[0], 1 << 20):
+                d = (a[s0:s0 + (1 << 20)] - b[s0:s0 + (1 << 20)]).abs_()
+                ok_ = ok_ and bool((d <= 1e-5 * scale + 1e-5 * b[s0:s0 + (1 << 20)].abs()).all())
+            return ok_
         step(False)
+        want = check_ref.forward(x_loc)
+        ok = same(y_loc, want)
+        del want
+        check_ref._full.clear()
+        want = check_ref.backward(dy_loc)
+        ok = same(dx_loc, want) and ok
+        del want
+        check_ref._full.clear()
         torch.cuda.synchronize()
-        ok = torch.allclose(y_loc, want_y, rtol=1e-5, atol=1e-5 * float(want_y.abs().max())) and \
-            torch.allclose(dx_loc, want_dx, rtol=1e-5, atol=1e-5 * float(want_dx.abs().max()))
         flag = torch.tensor([1 if ok else 0], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         if int(flag.item()) != 1:
             raise SystemExit("rank %d: --check FAILED: exchange '%s' disagrees with the all-gather path" % (rank, exchange))
-        del want_y, want_dx
         check_ref = None
+        torch.cuda.empty_cache()
     xchg_bytes = part.exchange_bytes(feat)
     del x_loc, dy_loc, y_loc, dx_loc
     part._full.clear()
