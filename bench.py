@@ -250,6 +250,8 @@ def run_b200(args):
     gen = torch.Generator(device=dev)
     gen.manual_seed(1234 + rank)
     like = torch.empty(0, device=dev)
+    if args.transport == "peer" and world > 1:
+        part.enable_peer_transport(feat, like)
     x_loc = part.local_view("x", feat, like)            # this rank's blocks live inside the exchange buffers
     dy_loc = part.local_view("dy", feat, like)
     x_loc.copy_(torch.randn(rows, feat, device=dev, generator=gen))
@@ -260,19 +262,31 @@ def run_b200(args):
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
     kern_events = []
 
+    xchg_events = []
+
     def step(record):
+        if record and world > 1:
+            xa = ev()
+            xa.record()
         x_full = part.exchange("x", x_loc)        # halo exchange (no-op at world == 1)
         if record:
             a, b = ev(), ev()
             a.record()
+            if world > 1:
+                xchg_events.append((xa, a))
         ops.spmm(loc_in, ops.MSG_COPY_SRC, ops.RED_SUM, x=x_full, out=y_loc)
         if record:
             b.record()
             kern_events.append((a, b))
+        if record and world > 1:
+            xa = ev()
+            xa.record()
         dy_full = part.exchange("dy", dy_loc)
         if record:
             a, b = ev(), ev()
             a.record()
+            if world > 1:
+                xchg_events.append((xa, a))
         ops.spmm(loc_out, ops.MSG_COPY_SRC, ops.RED_SUM, x=dy_full, out=dx_loc)
         if record:
             b.record()
@@ -308,6 +322,7 @@ def run_b200(args):
     # dominant kernel: the SpMM launches of this rank (forward and gradient are the same kernel)
     kms = [a.elapsed_time(b) for a, b in kern_events]
     k_avg_ms = sum(kms) / len(kms)
+    xchg_ms = (sum(a.elapsed_time(b) for a, b in xchg_events) / len(xchg_events)) if xchg_events else 0.0
     loc_e = (loc_in.nnz + loc_out.nnz) / 2.0
     alg_launch = graphs.spmm_alg_bytes(loc_e, rows, feat)
     peak, peak_kind = measured_peak()
@@ -402,9 +417,10 @@ def run_b200(args):
             "config": {"workload": cfg["name"], "n": n, "e": e, "feat": feat,
                        "l2": "inputs_exceed_l2 (X %.0f MB + structure %.0f MB per SpMM; no flush)"
                              % (n * feat * 4 / 1e6, e * 4 / 1e6),
-                       "parallelism": "row-partition x%d + NCCL %s" % (
-                           world, "compacted-halo all_to_all" if exchange == "halo" else "all-gather halo"),
-                       "exchange_bytes_per_rank_per_spmm": xchg_bytes,
+                       "parallelism": "row-partition x%d + %s %s" % (
+                           world, "NVLink peer-load" if (args.transport == "peer" and world > 1) else "NCCL",
+                           "compacted halo" if exchange == "halo" else "all-gather halo"),
+                       "exchange_bytes_per_rank_per_spmm": xchg_bytes, "exchange_ms_rank0": xchg_ms,
                        "graph_build_s": round(t_build, 2)},
             "edge_feat_per_s": 2 * e * feat / (ms_step * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
@@ -424,6 +440,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c5", "tiny"])
     ap.add_argument("--exchange", default="auto", choices=["auto", "allgather", "halo"])
+    ap.add_argument("--transport", default="nccl", choices=["nccl", "peer"],
+                    help="N>1 data path: NCCL collectives, or peer loads over NVLink from IPC-mapped buffers")
     ap.add_argument("--check", action="store_true", help="N>1: verify the exchange against the all-gather path")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

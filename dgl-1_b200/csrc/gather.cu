@@ -2,6 +2,10 @@
 // (python/dgl/runtime/ir/executor.py:365-394 -> F.gather_row, backend/pytorch/tensor.py:108-109)
 // and the send-side packing of the compacted halo exchange (dgl_b200/dist.py).  HBM-bound:
 // n_out * row_bytes read + written; 128-bit accesses, one group of lanes per row.
+#include <dlfcn.h>
+
+#include <cstring>
+
 #include "common.cuh"
 
 namespace dglb200 {
@@ -61,5 +65,49 @@ extern "C" int dglb200_gather_rows(int64_t n_out, const int64_t* idx, int64_t x_
   else
     gather_rows_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, xs, row_bytes, os, lanes, bad_flag);
   DGLB200_POST_LAUNCH("gather_rows_kernel");
+  return 0;
+}
+
+// ---- CUDA IPC: map a peer process's device allocation into this process, on the CURRENT device ----
+// (cudaIpcMemLazyEnablePeerAccess enables peer access from the current device to the exporter's
+// device).  Used by dgl_b200/dist.py for the NVLink peer-load exchange.
+extern "C" int dglb200_ipc_get_handle(const void* dev_ptr, void* handle64_out, int64_t* offset_out) {
+  clear_error();
+  DGLB200_REQUIRE(dev_ptr && handle64_out && offset_out, "ipc_get_handle: NULL pointer");
+  // base of the cudaMalloc allocation that contains dev_ptr (torch sub-allocates its blocks):
+  // cuMemGetAddressRange of the driver API, resolved at run time so that the library has no
+  // link-time dependency on libcuda
+  typedef int (*GetRange)(unsigned long long*, size_t*, unsigned long long);
+  static GetRange get_range = nullptr;
+  if (get_range == nullptr) {
+    void* drv = dlopen("libcuda.so.1", RTLD_NOW | RTLD_GLOBAL);
+    DGLB200_REQUIRE(drv != nullptr, "ipc_get_handle: cannot load libcuda.so.1");
+    get_range = reinterpret_cast<GetRange>(dlsym(drv, "cuMemGetAddressRange_v2"));
+    DGLB200_REQUIRE(get_range != nullptr, "ipc_get_handle: libcuda lacks cuMemGetAddressRange_v2");
+  }
+  unsigned long long base = 0;
+  size_t size = 0;
+  const int rc = get_range(&base, &size, (unsigned long long)(uintptr_t)dev_ptr);
+  DGLB200_REQUIRE(rc == 0, "ipc_get_handle: cuMemGetAddressRange failed (%d)", rc);
+  cudaIpcMemHandle_t h;
+  DGLB200_CUDA(cudaIpcGetMemHandle(&h, reinterpret_cast<void*>((uintptr_t)base)));
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(handle64_out, &h, 64);
+  *offset_out = (int64_t)((unsigned long long)(uintptr_t)dev_ptr - base);
+  return 0;
+}
+
+extern "C" int dglb200_ipc_open(const void* handle64, void** ptr_out) {
+  clear_error();
+  DGLB200_REQUIRE(handle64 && ptr_out, "ipc_open: NULL pointer");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, handle64, 64);
+  DGLB200_CUDA(cudaIpcOpenMemHandle(ptr_out, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+
+extern "C" int dglb200_ipc_close(void* ptr) {
+  clear_error();
+  DGLB200_CUDA(cudaIpcCloseMemHandle(ptr));
   return 0;
 }

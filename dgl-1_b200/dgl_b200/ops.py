@@ -352,19 +352,23 @@ def unique_sorted(ids, id_bound, want_inverse=True):
 
 
 def gather_rows(x, idx, out=None):
-    """out[i] = x[idx[i]] (dglb200_gather_rows); idx int64 CUDA.  READ_ROW / halo packing."""
+    """out[i] = x[idx[i]] (dglb200_gather_rows); idx int64 CUDA.  READ_ROW / halo packing.
+    The kernel runs on the device (and current stream) of `idx` / `out`; `x` may live on a PEER
+    device whose memory is mapped into this process (dist.share_with_peers): the rows are then
+    pulled over NVLink by the gathering GPU."""
     lib = _lib.get_lib()
     _need_cuda(x, idx)
-    x = x.contiguous()
+    if not x.is_contiguous():
+        raise DGLError("gather_rows: x must be contiguous")
     idx = idx.contiguous()
     if idx.dtype != torch.int64:
         raise DGLError("gather_rows: ids must be int64")
     n_out = int(idx.shape[0])
     if out is None:
-        out = torch.empty((n_out,) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+        out = torch.empty((n_out,) + tuple(x.shape[1:]), dtype=x.dtype, device=idx.device)
     row_bytes = x.element_size() * (x.numel() // max(int(x.shape[0]), 1)) if x.shape[0] else x.element_size()
-    bad = torch.zeros(1, dtype=torch.int32, device=x.device)
-    with torch.cuda.device(x.device):
+    bad = torch.zeros(1, dtype=torch.int32, device=idx.device)
+    with torch.cuda.device(idx.device):
         _lib.check_call(lib.dglb200_gather_rows(n_out, _ptr(idx), int(x.shape[0]), _ptr(x), row_bytes,
                                                 _ptr(out), _ptr(bad), _stream()))
     return out

@@ -274,6 +274,20 @@ int dglb200_unique_sorted(int64_t n, int64_t id_bound, const int64_t* ids,
 int dglb200_gather_rows(int64_t n_out, const int64_t* idx, int64_t x_rows, const void* x,
                         int64_t row_bytes, void* out, int32_t* bad_flag, void* stream);
 
+/* ---- CUDA IPC (multi-GPU peer-load exchange) ------------------------------------------------- */
+
+/*
+ * The reference has no multi-GPU layer.  These three calls let one process per
+ * GPU read another rank's feature block straight over NVLink: the owner exports the BASE of a
+ * cudaMalloc allocation (64-byte cudaIpcMemHandle_t), a peer maps it on ITS current device
+ * (peer access is enabled lazily by the driver) and passes the mapped pointer as `x` of
+ * dglb200_gather_rows / dglb200_spmm_csr.  dev_ptr may point inside an allocation (torch sub-allocates):
+ * the handle is that of the containing cudaMalloc block and *offset_out the byte offset of dev_ptr in it.
+ */
+int dglb200_ipc_get_handle(const void* dev_ptr, void* handle64_out, int64_t* offset_out);
+int dglb200_ipc_open(const void* handle64, void** ptr_out);
+int dglb200_ipc_close(void* ptr);
+
 /* ---- hook into the reference's PackedFunc registry ----------------------------------- */
 
 /*
