@@ -41,8 +41,8 @@ __global__ void plan_emit(const int32_t* is_long, const int32_t* long_pos, const
 // y[row, f] = ordered reduce of the row's slices.  One thread per (long row, feature).
 template <typename T, int RED>
 __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, int n_long,
-                           const float* partial, const int32_t* partial_arg, int64_t feat, T* y,
-                           int32_t* arg) {
+                           const float* partial, const int32_t* partial_arg, int64_t feat, int64_t y_ld,
+                           T* y, int32_t* arg) {
   const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int lr = blockIdx.y;
   if (f >= feat || lr >= n_long) return;
@@ -60,8 +60,8 @@ __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, i
   }
   const int64_t row = long_rows[lr];
   if (RED == DGLB200_RED_MAX && arg) arg[row * feat + f] = best;
-  if (sizeof(T) == 4) reinterpret_cast<float*>(y)[row * feat + f] = acc;
-  else reinterpret_cast<__nv_bfloat16*>(y)[row * feat + f] = __float2bfloat16_rn(acc);
+  if (sizeof(T) == 4) reinterpret_cast<float*>(y)[row * y_ld + f] = acc;
+  else reinterpret_cast<__nv_bfloat16*>(y)[row * y_ld + f] = __float2bfloat16_rn(acc);
 }
 
 SpmmTuning& spmm_tuning() {
@@ -128,7 +128,10 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
                     "spmm: MAX with arg over a plan needs plan->partial_arg");
   }
   const int full_vec = dtype == DGLB200_F32 ? 4 : 8;
-  bool vec = a.feat % full_vec == 0 && aligned16(a.x) && aligned16(a.y);
+  if (a.x_ld == 0) a.x_ld = a.feat;
+  if (a.y_ld == 0) a.y_ld = a.feat;
+  bool vec = a.feat % full_vec == 0 && aligned16(a.x) && aligned16(a.y) && a.x_ld % full_vec == 0 &&
+             a.y_ld % full_vec == 0;
   if (a.w != nullptr && (a.w_mode == kWFull || msg == DGLB200_MSG_COPY_EDGE)) vec = vec && aligned16(a.w);
   a.slab_chunks = 0;
   if (vec && msg != DGLB200_MSG_COPY_EDGE && x_rows > 0)
@@ -145,7 +148,7 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
       grid.y = (unsigned)n;
 #define FIX(T, R)                                                                          \
   spmm_fixup<T, R><<<grid, 128, 0, stream>>>(a.long_rows + base, a.chunk_ptr + base, n,    \
-                                             a.partial, a.partial_arg, a.feat,             \
+                                             a.partial, a.partial_arg, a.feat, a.y_ld,     \
                                              static_cast<T*>(a.y), a.arg)
       if (dtype == DGLB200_F32) {
         if (red == DGLB200_RED_SUM) FIX(float, DGLB200_RED_SUM); else FIX(float, DGLB200_RED_MAX);
@@ -233,7 +236,18 @@ int dglb200_spmm_csr(int64_t n_rows, int64_t x_rows, int64_t nnz, const int64_t*
                      const int32_t* indices, const int32_t* eids, int msg_op, int reduce_op,
                      int dtype, const void* x, int64_t feat, const void* w, int64_t w_width,
                      void* y, int32_t* arg, const dglb200_spmm_plan_t* plan, void* stream) {
+  return dglb200_spmm_csr_strided(n_rows, x_rows, nnz, indptr, indices, eids, msg_op, reduce_op, dtype,
+                                  x, feat, feat, w, w_width, y, feat, arg, plan, stream);
+}
+
+int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz, const int64_t* indptr,
+                             const int32_t* indices, const int32_t* eids, int msg_op, int reduce_op,
+                             int dtype, const void* x, int64_t x_ld, int64_t feat, const void* w,
+                             int64_t w_width, void* y, int64_t y_ld, int32_t* arg,
+                             const dglb200_spmm_plan_t* plan, void* stream) {
   clear_error();
+  DGLB200_REQUIRE(x_ld >= feat && y_ld >= feat, "spmm_csr: leading dimensions (%lld, %lld) < feat %lld",
+                  (long long)x_ld, (long long)y_ld, (long long)feat);
   DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && feat >= 1, "spmm_csr: bad sizes n_rows=%lld nnz=%lld feat=%lld",
                   (long long)n_rows, (long long)nnz, (long long)feat);
   DGLB200_REQUIRE(n_rows < (1ll << 31) && nnz < (1ll << 31) && x_rows < (1ll << 31),
@@ -249,7 +263,7 @@ int dglb200_spmm_csr(int64_t n_rows, int64_t x_rows, int64_t nnz, const int64_t*
                   "spmm_csr: indices / x is NULL");
   SpmmArgs a{};
   a.n_rows = n_rows; a.indptr = indptr; a.indices = indices; a.eids = eids;
-  a.x = x; a.w = w; a.y = y; a.arg = arg; a.feat = feat;
+  a.x = x; a.w = w; a.y = y; a.arg = arg; a.feat = feat; a.x_ld = x_ld; a.y_ld = y_ld;
   a.w_width = 1; a.w_group = feat; a.w_mode = kWScalar;
   if (msg_op != DGLB200_MSG_COPY_SRC) {
     DGLB200_REQUIRE(nnz == 0 || w != nullptr, "spmm_csr: edge data w is NULL");

@@ -51,6 +51,8 @@ struct SpmmArgs {
   int32_t* partial_arg;
   int64_t n_chunk_warps;   // leading warps of the grid that process slices
   int slab_chunks;         // cap on the 16-byte chunks of a feature row per pass (0 = whole row)
+  int64_t x_ld;            // leading dimension (elements) of x rows; == feat when dense
+  int64_t y_ld;            // leading dimension (elements) of y rows
 };
 
 constexpr int kSpmmThreads = 128;  // measured: 128 > 256 > 512 on C2 at every slab width
@@ -131,7 +133,9 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
   // one IMAD.WIDE.U32 (ids and row_bytes are < 2^32).
   const char* xb[TILES];   // x (or, for COPY_EDGE, the edge data) + feature offset
   const char* wb[TILES];   // element-wise edge weights + feature offset
-  const uint32_t row_bytes = (uint32_t)(a.feat * (int64_t)sizeof(T));
+  const uint32_t w_row_bytes = (uint32_t)(a.feat * (int64_t)sizeof(T));   // edge-data rows are dense
+  const uint32_t row_bytes =
+      MSG == DGLB200_MSG_COPY_EDGE ? w_row_bytes : (uint32_t)(a.x_ld * (int64_t)sizeof(T));
 #pragma unroll
   for (int t = 0; t < TILES; ++t) {
     foff[t] = fbase + (int64_t)(t * G + gl) * VEC;
@@ -198,7 +202,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
           Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(xb[t], gid, row_bytes)), st.xv[k][t]);
           if constexpr (kMul) {
             if (w_full) {
-              Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(wb[t], (uint32_t)st.e[k], row_bytes)),
+              Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(wb[t], (uint32_t)st.e[k], w_row_bytes)),
                                   st.wv[k][t]);
             } else if (w_grouped) {
 #pragma unroll
@@ -305,7 +309,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
           for (int v = 0; v < VEC; ++v) da[v] = best[t][v];
         }
       }
-      Chunk<T, VEC>::store(y + out_row * a.feat + foff[t], acc[t]);
+      Chunk<T, VEC>::store(y + out_row * a.y_ld + foff[t], acc[t]);
     }
   }
 }

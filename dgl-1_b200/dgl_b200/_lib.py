@@ -52,6 +52,9 @@ SIGNATURES = {
     "dglb200_spmm_csr": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_int, c_int,
                                  c_vp, c_i64, c_vp, c_i64, c_vp, c_vp,
                                  ctypes.POINTER(SpmmPlanStruct), c_vp]),
+    "dglb200_spmm_csr_strided": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_int, c_int,
+                                         c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
+                                         ctypes.POINTER(SpmmPlanStruct), c_vp]),
     "dglb200_spmm_csr_backward_x": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_vp, c_i64,
                                             c_vp, c_i64, c_vp, c_vp,
                                             ctypes.POINTER(SpmmPlanStruct), c_vp]),

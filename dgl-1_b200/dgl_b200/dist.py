@@ -112,6 +112,7 @@ class RowPartition(object):
         self._full = {}
         self._peer_full = {}      # key -> every rank's full buffer mapped here (transport "peer")
         self._barrier = None
+        self._comm = None
 
     def enable_peer_transport(self, feat, like, keys=("x", "dy")):
         """Exchange by PEER LOADS over NVLink instead of NCCL: every rank's gather buffer is mapped
@@ -178,75 +179,161 @@ class RowPartition(object):
         """Make every source row the local SpMM needs available; returns the gather operand."""
         return self.all_gather_rows(local, key)
 
+    def operand(self, key, feat, like):
+        """The gather operand as the last exchange left it (benchmark kernel-only timing)."""
+        return self.full_buffer(key, feat, like)
+
     def exchange_bytes(self, feat, elem=4):
         """Bytes this rank receives per exchange."""
         return (self.n - self.rows) * feat * elem if self.world > 1 else 0
 
+    SLAB = 64     # elements; the SpMM's own L2-residency slab width at C2 (spmm.cu pick_slab_chunks)
+
+    def _aggregate(self, key, local, csr, out):
+        """Exchange + SpMM.  With the peer transport the feature dimension is pipelined in slabs:
+        slab s+1 is copied out of the owners' memory (NVLink) on a side stream while the SpMM runs
+        over slab s (dglb200_spmm_csr_strided on column blocks of the gather buffer)."""
+        feat = local.shape[1]
+        if key not in self._peer_full or feat <= self.SLAB or feat % self.SLAB:
+            return self._spmm(csr, self.exchange(key, local), out)
+        full = self.full_buffer(key, feat, local)
+        views = self.views(full)
+        if views[self.rank].data_ptr() != local.data_ptr():
+            views[self.rank].copy_(local)
+        if out is None:
+            out = torch.empty((csr.n_rows, feat), dtype=local.dtype, device=local.device)
+        if self._comm is None:
+            self._comm = torch.cuda.Stream(device=local.device)
+        cur = torch.cuda.current_stream(local.device)
+        peers = self._peer_full[key]
+        self._barrier()                                           # every owner's block is written
+        self._comm.wait_stream(cur)
+        events = []
+        with torch.cuda.stream(self._comm):
+            for s0 in range(0, feat, self.SLAB):
+                for j in range(1, self.world):
+                    q = (self.rank + j) % self.world
+                    b0, b1 = self.bounds[q], self.bounds[q + 1]
+                    if b1 > b0:
+                        full[b0:b1, s0:s0 + self.SLAB].copy_(peers[q][b0:b1, s0:s0 + self.SLAB], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self._comm)
+                events.append(ev)
+        for i, s0 in enumerate(range(0, feat, self.SLAB)):
+            cur.wait_event(events[i])
+            self._spmm(csr, full[:, s0:s0 + self.SLAB], out[:, s0:s0 + self.SLAB])
+        self._barrier()                                           # nobody overwrites a block still being read
+        return out
+
     def forward(self, x_local, out=None):
         """y_local = (A x)[r0:r1] for update_all(copy_src, sum)."""
-        return self._spmm(self.loc_in, self.exchange("x", x_local), out)
+        return self._aggregate("x", x_local, self.loc_in, out)
 
     def backward(self, dy_local, out=None):
         """dx_local = (A^T dy)[r0:r1]."""
-        return self._spmm(self.loc_out, self.exchange("dy", dy_local), out)
+        return self._aggregate("dy", dy_local, self.loc_out, out)
 
 
 class HaloExchange(object):
-    """Compacted halo plan for one CSR row block (a full all-gather of X moves
-    n * feat per rank; only the DISTINCT remote rows a rank's edges reference are needed -
+    """Compacted, pipelined halo plan for one CSR row block (a full all-gather of X
+    moves n * feat per rank; only the DISTINCT remote rows a rank's edges reference are needed -
     measured on C5 at 8 ranks: 9 % of the full volume, 2.0 GB instead of 23.5 GB per rank).
 
     Plan time (one-off per graph and partition, integer plumbing):
-      * the sorted unique remote column ids of the block, split by owner       -> what I receive
-      * an all-to-all of those id lists                                         -> what I send
-      * the block's column ids remapped into the compact row space
-        [own rows | halo rows from owner 0 | owner 1 | ...]
-    Per call: pack the rows the others need (gather_rows kernel), one all_to_all_single straight
-    into the halo region of the compact feature buffer, then the local SpMM over the remapped CSR.
+      * the block's rows are cut into `chunks` edge-balanced row chunks; chunk k's halo is the set
+        of remote column ids it references that no earlier chunk referenced
+      * the compact row space is [own rows | halo of chunk 0 (by owner, ascending id) | chunk 1 ..]
+        and the block's column ids are remapped into it
+      * an all-to-all of the id lists tells every owner which rows to serve, per chunk
+    Per call, for k = 0..chunks-1 on a side stream: fetch chunk k's halo rows (NCCL: pack with the
+    gather kernel + all_to_all_single; peer transport: the gather kernel pulls them straight out of
+    the owners' memory over NVLink); the SpMM over chunk k's rows starts as soon as its halo has
+    landed, while chunk k+1's halo is in flight.
     """
 
-    def __init__(self, csr_block, bounds, rank, world, group=None, gather_fn=None):
+    def __init__(self, csr_block, bounds, rank, world, group=None, gather_fn=None, chunks=1):
         self.group, self.rank, self.world = group, rank, world
         self.bounds = bounds
         self.r0, self.r1 = bounds[rank], bounds[rank + 1]
         self.rows = self.r1 - self.r0
         self._gather = gather_fn or ops.gather_rows
         dev = csr_block.indices.device
+        self.chunks = max(1, int(chunks)) if world > 1 else 1
+        # edge-balanced row chunks of the block
+        ip = csr_block.indptr
+        tgt = torch.arange(1, self.chunks, dtype=torch.float64, device=dev) * (float(ip[-1]) / self.chunks)
+        cuts = torch.searchsorted(ip.to(torch.float64), tgt).clamp_(max=self.rows).tolist()
+        self.row_cuts = [0] + [int(c) for c in cuts] + [self.rows]
+        for i in range(1, len(self.row_cuts)):
+            self.row_cuts[i] = max(self.row_cuts[i], self.row_cuts[i - 1])
         cols = csr_block.indices.long()
         own = (cols >= self.r0) & (cols < self.r1)
-        halo_ids = torch.unique(cols[~own])                       # sorted ascending, own range absent
-        b = torch.tensor(bounds, dtype=torch.int64, device=dev)
-        cut = torch.searchsorted(halo_ids, b)
-        self.recv_counts = (cut[1:] - cut[:-1]).tolist()          # rows I need from every owner
-        assert self.recv_counts[rank] == 0
-        new_cols = torch.where(own, cols - self.r0, self.rows + torch.searchsorted(halo_ids, cols))
+        halo_ids = torch.unique(cols[~own])                       # H: sorted ascending, own range absent
+        # first chunk that references every halo id
+        first = torch.full((halo_ids.numel(),), self.chunks, dtype=torch.int64, device=dev)
+        for k in range(self.chunks):
+            lo, hi = int(ip[self.row_cuts[k]]), int(ip[self.row_cuts[k + 1]])
+            ck = cols[lo:hi]
+            ck = ck[(ck < self.r0) | (ck >= self.r1)]
+            hk = torch.searchsorted(halo_ids, torch.unique(ck))
+            first[hk] = torch.minimum(first[hk], torch.full_like(hk, k))
+            del ck, hk
+        order = torch.sort(first, stable=True)[1]                 # layout: (chunk, id) == (chunk, owner, id)
+        pos = torch.empty_like(order)
+        pos[order] = torch.arange(order.numel(), device=dev)
+        layout_ids = halo_ids[order]                              # global ids in layout order
+        per_chunk = torch.bincount(first, minlength=self.chunks).tolist()
         self.n_halo = int(halo_ids.numel())
+        new_cols = torch.where(own, cols - self.r0,
+                               self.rows + pos[torch.searchsorted(halo_ids, cols).clamp_(max=max(self.n_halo - 1, 0))]
+                               if self.n_halo else cols - self.r0)
         self.csr = ops.CSR(csr_block.n_rows, self.rows + self.n_halo, csr_block.indptr,
                            new_cols.to(torch.int32), csr_block.eids)
-        del cols, own, new_cols
-        # tell every owner which of its rows I need
-        rc = torch.tensor(self.recv_counts, dtype=torch.int64, device=dev)
-        sc = torch.empty_like(rc)
-        if world > 1:
-            dist.all_to_all_single(sc, rc, group=group)
-        else:
-            sc.copy_(rc)
-        self.send_counts = sc.tolist()
-        serve = torch.empty(int(sum(self.send_counts)), dtype=torch.int64, device=dev)
-        if world > 1:
-            dist.all_to_all_single(serve, halo_ids, output_split_sizes=self.send_counts,
-                                   input_split_sizes=self.recv_counts, group=group)
-        self.serve_local = (serve - self.r0).contiguous()        # my rows to pack, grouped by requester
+        del cols, own, new_cols, pos, order, first
+        # per (chunk, owner): receive counts, and the ids as LOCAL row ids of their owner
+        b = torch.tensor(bounds, dtype=torch.int64, device=dev)
+        self.chunk_start, self.recv_counts, self.need_local = [], [], []
+        off = 0
+        for k in range(self.chunks):
+            ids_k = layout_ids[off:off + per_chunk[k]]
+            cut = torch.searchsorted(ids_k, b)
+            cnt = (cut[1:] - cut[:-1]).tolist()
+            self.chunk_start.append(self.rows + off)
+            self.recv_counts.append(cnt)
+            owner_of = torch.repeat_interleave(torch.arange(world, device=dev), torch.tensor(cnt, device=dev))
+            local_k = ids_k - b[owner_of]
+            self.need_local.append([local_k[int(cut[q]):int(cut[q + 1])].contiguous() for q in range(world)])
+            off += per_chunk[k]
+        # tell every owner which of its rows I need, per chunk
+        self.send_counts, self.serve_local = [], []
+        for k in range(self.chunks):
+            rc = torch.tensor(self.recv_counts[k], dtype=torch.int64, device=dev)
+            sc = torch.empty_like(rc)
+            if world > 1:
+                dist.all_to_all_single(sc, rc, group=group)
+            else:
+                sc.copy_(rc)
+            sc = sc.tolist()
+            need_cat = torch.cat(self.need_local[k]) if world > 1 else torch.empty(0, dtype=torch.int64, device=dev)
+            serve = torch.empty(int(sum(sc)), dtype=torch.int64, device=dev)
+            if world > 1:
+                dist.all_to_all_single(serve, need_cat, output_split_sizes=sc,
+                                       input_split_sizes=self.recv_counts[k], group=group)
+            self.send_counts.append(sc)
+            self.serve_local.append(serve.contiguous())           # already local ids of THIS rank
+        self.chunk_csr = None
         self._buf = None
         self._peer_buf = None
         self._barrier = None
-        # for the peer transport: the rows I need, as LOCAL row ids of their owners, per owner
-        self.need_local = []
-        off = 0
-        for q in range(world):
-            ids = halo_ids[off:off + self.recv_counts[q]] - bounds[q]
-            self.need_local.append(ids.contiguous())
-            off += self.recv_counts[q]
+        self._comm = None
+
+    # -- buffers / transports -----------------------------------------------------------------
+    def buffer(self, feat, like):
+        """Compact feature buffer [rows + n_halo, feat]; rows [0, rows) are this rank's block."""
+        if (self._buf is None or self._buf.shape[1] != feat or self._buf.dtype != like.dtype or
+                self._buf.device != like.device):
+            self._buf = torch.empty((self.rows + self.n_halo, feat), dtype=like.dtype, device=like.device)
+        return self._buf
 
     def enable_peer_transport(self, feat, like):
         """Pull the halo rows straight out of their owners' memory with the gather kernel (peer
@@ -257,47 +344,99 @@ class HaloExchange(object):
         self._peer_buf = share_with_peers(buf, self.rank, self.world, self.group)
         self._barrier = StreamBarrier(like.device, self.group)
 
-    def buffer(self, feat, like):
-        """Compact feature buffer [rows + n_halo, feat]; rows [0, rows) are this rank's block."""
-        if (self._buf is None or self._buf.shape[1] != feat or self._buf.dtype != like.dtype or
-                self._buf.device != like.device):
-            self._buf = torch.empty((self.rows + self.n_halo, feat), dtype=like.dtype, device=like.device)
-        return self._buf
-
-    def exchange(self, x_local):
-        """Returns the compact buffer with own rows and freshly received halo rows."""
-        buf = self.buffer(x_local.shape[1], x_local)
-        own = buf[:self.rows]
-        if own.data_ptr() != x_local.data_ptr():
-            own.copy_(x_local)
-        if self._peer_buf is not None:
-            self._barrier()
-            for k in range(1, self.world):
-                q = (self.rank + k) % self.world
-                start = self.rows + sum(self.recv_counts[:q])
-                cnt = self.recv_counts[q]
-                if cnt:
-                    rows_q = self.bounds[q + 1] - self.bounds[q]
-                    self._gather(self._peer_buf[q][:rows_q], self.need_local[q], out=buf[start:start + cnt])
-            self._barrier()
-            return buf
-        if self.world > 1:
-            send = self._gather(own, self.serve_local)
-            dist.all_to_all_single(buf[self.rows:], send, output_split_sizes=self.recv_counts,
-                                   input_split_sizes=self.send_counts, group=self.group)
-        return buf
+    def row_chunks(self):
+        """The remapped CSR cut into the plan's row chunks (views; each with its own long-row plan)."""
+        if self.chunk_csr is None:
+            self.chunk_csr = [ops.csr_row_block(self.csr, self.row_cuts[k], self.row_cuts[k + 1])
+                              for k in range(self.chunks)]
+        return self.chunk_csr
 
     def halo_bytes(self, feat, elem=4):
         return self.n_halo * feat * elem
 
+    # -- data path ---------------------------------------------------------------------------
+    def _fetch_chunk(self, k, buf):
+        """Bring chunk k's halo rows into buf (current stream)."""
+        start = self.chunk_start[k]
+        cnts = self.recv_counts[k]
+        if self._peer_buf is not None:
+            off = start
+            offs = []
+            for q in range(self.world):
+                offs.append(off)
+                off += cnts[q]
+            for j in range(1, self.world):                        # start at a different owner on every rank
+                q = (self.rank + j) % self.world
+                if cnts[q]:
+                    rows_q = self.bounds[q + 1] - self.bounds[q]
+                    self._gather(self._peer_buf[q][:rows_q], self.need_local[k][q], out=buf[offs[q]:offs[q] + cnts[q]])
+            return
+        send = self._gather(buf[:self.rows], self.serve_local[k])
+        dist.all_to_all_single(buf[start:start + sum(cnts)], send, output_split_sizes=cnts,
+                               input_split_sizes=self.send_counts[k], group=self.group)
+
+    def exchange(self, x_local):
+        """Unpipelined: returns the compact buffer with own rows and every halo row."""
+        buf = self.buffer(x_local.shape[1], x_local)
+        own = buf[:self.rows]
+        if own.data_ptr() != x_local.data_ptr():
+            own.copy_(x_local)
+        if self.world == 1:
+            return buf
+        if self._barrier is not None:
+            self._barrier()
+        for k in range(self.chunks):
+            self._fetch_chunk(k, buf)
+        if self._barrier is not None:
+            self._barrier()
+        return buf
+
+    def aggregate(self, x_local, spmm_fn, out):
+        """Pipelined exchange + SpMM: y[rows of chunk k] is computed while chunk k+1's halo is in
+        flight on the side stream.  `out` [rows, feat] must be given."""
+        if self.world == 1 or self.chunks == 1:
+            return spmm_fn(self.csr, self.exchange(x_local), out)
+        buf = self.buffer(x_local.shape[1], x_local)
+        own = buf[:self.rows]
+        if own.data_ptr() != x_local.data_ptr():
+            own.copy_(x_local)
+        if not x_local.is_cuda:                                   # CPU (gloo tests): same schedule, no streams
+            for k, csr_k in enumerate(self.row_chunks()):
+                self._fetch_chunk(k, buf)
+                if csr_k.n_rows:
+                    out[self.row_cuts[k]:self.row_cuts[k + 1]] = spmm_fn(csr_k, buf, None)
+            return out
+        if self._comm is None:
+            self._comm = torch.cuda.Stream(device=x_local.device)
+        cur = torch.cuda.current_stream(x_local.device)
+        if self._barrier is not None:
+            self._barrier()                                       # every owner's rows are written
+        self._comm.wait_stream(cur)
+        events = []
+        with torch.cuda.stream(self._comm):
+            for k in range(self.chunks):
+                self._fetch_chunk(k, buf)
+                ev = torch.cuda.Event()
+                ev.record(self._comm)
+                events.append(ev)
+        for k, csr_k in enumerate(self.row_chunks()):
+            cur.wait_event(events[k])
+            if csr_k.n_rows:
+                spmm_fn(csr_k, buf, out[self.row_cuts[k]:self.row_cuts[k + 1]])
+        if self._barrier is not None:
+            self._barrier()                                       # nobody overwrites rows still being read
+        return out
+
 
 class HaloPartition(RowPartition):
-    """RowPartition whose exchange is the compacted halo instead of the full all-gather."""
+    """RowPartition whose exchange is the compacted (and, with chunks > 1, pipelined) halo instead
+    of the full all-gather."""
 
-    def __init__(self, csr_in, csr_out, rank=None, world=None, group=None, spmm_fn=None, gather_fn=None):
+    def __init__(self, csr_in, csr_out, rank=None, world=None, group=None, spmm_fn=None, gather_fn=None,
+                 chunks=1):
         super(HaloPartition, self).__init__(csr_in, csr_out, rank, world, group, spmm_fn)
-        self.halo_in = HaloExchange(self.loc_in, self.bounds, self.rank, self.world, group, gather_fn)
-        self.halo_out = HaloExchange(self.loc_out, self.bounds, self.rank, self.world, group, gather_fn)
+        self.halo_in = HaloExchange(self.loc_in, self.bounds, self.rank, self.world, group, gather_fn, chunks)
+        self.halo_out = HaloExchange(self.loc_out, self.bounds, self.rank, self.world, group, gather_fn, chunks)
         self.loc_in, self.loc_out = self.halo_in.csr, self.halo_out.csr
 
     def _halo(self, key):
@@ -313,5 +452,18 @@ class HaloPartition(RowPartition):
     def exchange(self, key, local):
         return self._halo(key).exchange(local)
 
+    def operand(self, key, feat, like):
+        return self._halo(key).buffer(feat, like)
+
     def exchange_bytes(self, feat, elem=4):
         return max(self.halo_in.n_halo, self.halo_out.n_halo) * feat * elem
+
+    def forward(self, x_local, out=None):
+        if out is None:
+            out = torch.empty((self.rows, x_local.shape[1]), dtype=x_local.dtype, device=x_local.device)
+        return self.halo_in.aggregate(x_local, self._spmm, out)
+
+    def backward(self, dy_local, out=None):
+        if out is None:
+            out = torch.empty((self.rows, dy_local.shape[1]), dtype=dy_local.dtype, device=dy_local.device)
+        return self.halo_out.aggregate(dy_local, self._spmm, out)

@@ -197,25 +197,33 @@ def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chun
     else:
         feat = int(x.shape[1])
     dt = _dtype_code(ref)
+
+    def rows_ok(t):    # row-major with unit inner stride (a column block of a wider matrix is fine)
+        return t.dim() == 2 and t.stride(1) == 1 and t.stride(0) >= t.shape[1]
     if x is not None:
-        x = x.contiguous()
+        if not rows_ok(x):
+            x = x.contiguous()
         if x.shape[0] != csr.n_cols:
             raise DGLError("spmm: x has %d rows, CSR has %d columns" % (x.shape[0], csr.n_cols))
     if w is not None:
         w = w.contiguous()
         if w.dtype != ref.dtype:
             raise DGLError("spmm: edge data dtype %s != feature dtype %s" % (w.dtype, ref.dtype))
+    if out is not None and not rows_ok(out):
+        raise DGLError("spmm: `out` must be row-major with unit inner stride")
     y = out if out is not None else torch.empty((csr.n_rows, feat), dtype=ref.dtype, device=ref.device)
     arg = None
     if reduce_op == RED_MAX and want_arg:
         arg = torch.empty((csr.n_rows, feat), dtype=torch.int32, device=ref.device)
     plan = csr.plan(chunk).struct(feat, arg is not None) if chunk else None
     plan_ref = ctypes.byref(plan) if plan is not None else None
+    x_ld = int(x.stride(0)) if (x is not None and x.shape[0] > 1) else feat
+    y_ld = int(y.stride(0)) if y.shape[0] > 1 else feat
     with torch.cuda.device(ref.device):
-        _lib.check_call(lib.dglb200_spmm_csr(
+        _lib.check_call(lib.dglb200_spmm_csr_strided(
             csr.n_rows, csr.n_cols, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids),
-            msg_op, reduce_op, dt, _ptr(x), feat, _ptr(w), w_width, _ptr(y), _ptr(arg),
-            plan_ref, _stream()))
+            msg_op, reduce_op, dt, _ptr(x), max(x_ld, feat), feat, _ptr(w), w_width, _ptr(y),
+            max(y_ld, feat), _ptr(arg), plan_ref, _stream()))
     return y, arg
 
 

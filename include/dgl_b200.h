@@ -162,6 +162,19 @@ int dglb200_spmm_csr(int64_t n_rows, int64_t x_rows, int64_t nnz,
                      const dglb200_spmm_plan_t* plan, void* stream);
 
 /*
+ * Same, for operands that are column blocks of wider row-major matrices: x rows are x_ld elements
+ * apart, y rows y_ld (>= feat).  Used to pipeline a feature-slab exchange with the SpMM over that
+ * slab (dgl_b200/dist.py); arg, w and the plan's partial buffers stay dense in feat.
+ */
+int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz,
+                             const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                             int msg_op, int reduce_op, int dtype,
+                             const void* x, int64_t x_ld, int64_t feat,
+                             const void* w, int64_t w_width,
+                             void* y, int64_t y_ld, int32_t* arg,
+                             const dglb200_spmm_plan_t* plan, void* stream);
+
+/*
  * Gradient of MAX wrt x (and of SUM, with arg == NULL) in gather form over the CSR keyed by
  * src (rows = source nodes, indices = dst, eids = edge id):
  *   dx[u, f] = sum_{p in row u} [arg == NULL or arg[indices[p], f] == e(p)] * wgt * dy[indices[p], f]

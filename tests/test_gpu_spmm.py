@@ -203,3 +203,34 @@ def test_determinism_and_large():
     A = sp.csr_matrix((np.ones(len(src), np.float32), (dst, src)), shape=(n, n))
     want = (A.astype(np.float64) @ x.astype(np.float64)).astype(np.float32)
     _close(y1, want, RTOL_F32)
+
+
+@pytest.mark.parametrize("feat,slab", [(256, 64), (128, 32), (96, 24), (12, 5)])
+def test_strided_column_blocks(feat, slab):
+    """dglb200_spmm_csr_strided: x and y are column blocks of wider row-major matrices (the
+    feature-slab pipeline of dgl_b200/dist.py); results equal the dense call bit for bit."""
+    from dgl_b200 import ops
+    n = 500
+    src, dst = random_graph(n, 9000, 21 + feat, hubs=2, hub_deg=900, zero_deg_frac=0.1)
+    csr = _csr(src, dst, n)
+    x = torch.from_numpy(np.random.RandomState(feat).randn(n, feat).astype(np.float32)).cuda()
+    dense, _ = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=x)
+    y = torch.full((n, feat), float("nan"), device="cuda")
+    for s0 in range(0, feat, slab):
+        s1 = min(feat, s0 + slab)
+        ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=x[:, s0:s1], out=y[:, s0:s1])
+    assert torch.equal(y, dense)
+    want = oracle.update_all(src, dst, n, "copy_src", "sum", x=x.cpu().numpy())
+    _close(y, want, RTOL_F32)
+
+
+def test_gather_rows():
+    from dgl_b200 import ops
+    rng = np.random.RandomState(0)
+    for shape in ((1000, 128), (1000, 7), (300, 4, 6), (50,)):
+        x = torch.from_numpy(rng.randn(*shape).astype(np.float32)).cuda()
+        idx = torch.from_numpy(rng.randint(0, shape[0], size=777)).cuda()
+        assert torch.equal(ops.gather_rows(x, idx), x[idx])
+    xb = torch.randn(64, 40, device="cuda").bfloat16()
+    idx = torch.randint(0, 64, (100,), device="cuda")
+    assert torch.equal(ops.gather_rows(xb, idx), xb[idx])

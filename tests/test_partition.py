@@ -38,7 +38,7 @@ def _oracle_block_spmm(csr, x, out):
     return torch.from_numpy(y)
 
 
-def _worker(rank, world, port, n, e, feat, q, halo=False):
+def _worker(rank, world, port, n, e, feat, q, halo=False, chunks=1):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -47,7 +47,7 @@ def _worker(rank, world, port, n, e, feat, q, halo=False):
         src, dst = random_graph(n, e, 7, hubs=3, hub_deg=n // 2, zero_deg_frac=0.1)
         if halo:
             part = HaloPartition(_csr_cpu(src, dst, n, False), _csr_cpu(src, dst, n, True),
-                                 spmm_fn=_oracle_block_spmm, gather_fn=lambda x, idx: x[idx])
+                                 spmm_fn=_oracle_block_spmm, gather_fn=lambda x, idx: x[idx], chunks=chunks)
             assert part.halo_in.n_halo <= n - part.rows
         else:
             part = RowPartition(_csr_cpu(src, dst, n, False), _csr_cpu(src, dst, n, True),
@@ -62,13 +62,14 @@ def _worker(rank, world, port, n, e, feat, q, halo=False):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,halo", [(2, False), (3, False), (2, True), (3, True)])
-def test_row_partition_gloo(world, halo):
+@pytest.mark.parametrize("world,halo,chunks", [(2, False, 1), (3, False, 1), (2, True, 1), (3, True, 1),
+                                               (2, True, 3), (3, True, 4)])
+def test_row_partition_gloo(world, halo, chunks):
     n, e, feat = 300, 5000, 12
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, n, e, feat, q, halo)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, n, e, feat, q, halo, chunks)) for r in range(world)]
     for p in procs:
         p.start()
     res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
