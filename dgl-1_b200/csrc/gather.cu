@@ -5,35 +5,51 @@
 #include <dlfcn.h>
 
 #include <cstring>
+#include <type_traits>
 
 #include "common.cuh"
 
 namespace dglb200 {
 
-template <int BYTES_PER_LANE>
+// Units of work are (row, 16-byte lane) pairs, walked with a grid-stride loop, four independent
+// loads in flight per thread.  `max_ctas` bounds the grid: a pull over NVLink needs bytes in
+// flight (~1 MB for 700 GB/s at ~1.5 us), not SMs, so a small persistent grid saturates the link
+// and leaves the SMs to the SpMM that runs concurrently on another stream.
+template <int UNIT>
 __global__ void __launch_bounds__(256)
 gather_rows_kernel(int64_t n_out, const int64_t* __restrict__ idx, int64_t x_rows,
-                   const char* __restrict__ x, int64_t row_bytes, char* __restrict__ out,
-                   int lanes_per_row, int32_t* __restrict__ bad) {
-  const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const int64_t row = tid / lanes_per_row;
-  const int lane = (int)(tid % lanes_per_row);
-  if (row >= n_out) return;
-  const int64_t s = idx[row];
-  if (s < 0 || s >= x_rows) {
-    if (lane == 0) atomicExch(bad, 1);
-    return;
-  }
-  const char* src = x + s * row_bytes;
-  char* dst = out + row * row_bytes;
-  for (int64_t b = (int64_t)lane * BYTES_PER_LANE; b < row_bytes; b += (int64_t)lanes_per_row * BYTES_PER_LANE) {
-    if (BYTES_PER_LANE == 16) {
-      *reinterpret_cast<uint4*>(dst + b) = __ldg(reinterpret_cast<const uint4*>(src + b));
-    } else if (BYTES_PER_LANE == 4) {
-      *reinterpret_cast<uint32_t*>(dst + b) = __ldg(reinterpret_cast<const uint32_t*>(src + b));
-    } else {
-      dst[b] = src[b];
+                   const char* __restrict__ x, int64_t x_ld_bytes, int64_t row_bytes,
+                   char* __restrict__ out, int64_t out_ld_bytes, int32_t* __restrict__ bad) {
+  using V = typename std::conditional<UNIT == 16, uint4,
+                                      typename std::conditional<UNIT == 4, uint32_t, uint8_t>::type>::type;
+  const int64_t lanes = row_bytes / UNIT;
+  const int64_t total = n_out * lanes;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  constexpr int K = 4;
+  for (int64_t u0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; u0 < total; u0 += stride * K) {
+    V v[K];
+    int64_t dst_off[K];
+    bool ok[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const int64_t u = u0 + (int64_t)k * stride;
+      ok[k] = u < total;
+      if (ok[k]) {
+        const int64_t row = u / lanes;
+        const int64_t lane = u - row * lanes;
+        const int64_t s = idx ? idx[row] : row;
+        if (s < 0 || s >= x_rows) {
+          atomicExch(bad, 1);
+          ok[k] = false;
+        } else {
+          v[k] = *reinterpret_cast<const V*>(x + s * x_ld_bytes + lane * UNIT);
+          dst_off[k] = row * out_ld_bytes + lane * UNIT;
+        }
+      }
     }
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+      if (ok[k]) *reinterpret_cast<V*>(out + dst_off[k]) = v[k];
   }
 }
 
@@ -41,31 +57,40 @@ gather_rows_kernel(int64_t n_out, const int64_t* __restrict__ idx, int64_t x_row
 
 using namespace dglb200;
 
-extern "C" int dglb200_gather_rows(int64_t n_out, const int64_t* idx, int64_t x_rows, const void* x,
-                                   int64_t row_bytes, void* out, int32_t* bad_flag, void* stream_) {
+extern "C" int dglb200_gather_rows_strided(int64_t n_out, const int64_t* idx, int64_t x_rows,
+                                           const void* x, int64_t x_ld_bytes, int64_t row_bytes,
+                                           void* out, int64_t out_ld_bytes, int32_t* bad_flag,
+                                           int max_ctas, void* stream_) {
   clear_error();
   DGLB200_REQUIRE(n_out >= 0 && x_rows >= 0 && row_bytes >= 1, "gather_rows: bad sizes");
+  DGLB200_REQUIRE(x_ld_bytes >= row_bytes && out_ld_bytes >= row_bytes, "gather_rows: leading dimension < row");
   if (n_out == 0) return 0;
-  DGLB200_REQUIRE(idx && x && out, "gather_rows: NULL pointer");
+  DGLB200_REQUIRE(x && out && bad_flag, "gather_rows: NULL pointer");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  auto al = [](const void* p, int a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0; };
-  const int unit = (row_bytes % 16 == 0 && al(x, 16) && al(out, 16)) ? 16
-                   : (row_bytes % 4 == 0 && al(x, 4) && al(out, 4)) ? 4 : 1;
-  int lanes = 1;
-  while (lanes < 32 && (int64_t)lanes * unit < row_bytes) lanes <<= 1;
-  const int64_t threads = n_out * lanes;
-  const int64_t blocks = ceil_div(threads, 256);
+  auto al = [](const void* p, int64_t ld, int a) { return (reinterpret_cast<uintptr_t>(p) % a) == 0 && ld % a == 0; };
+  const int unit = (row_bytes % 16 == 0 && al(x, x_ld_bytes, 16) && al(out, out_ld_bytes, 16)) ? 16
+                   : (row_bytes % 4 == 0 && al(x, x_ld_bytes, 4) && al(out, out_ld_bytes, 4)) ? 4 : 1;
+  const int64_t total = n_out * (row_bytes / unit);
+  int64_t blocks = ceil_div(total, 256 * 4);
+  if (max_ctas > 0 && blocks > max_ctas) blocks = max_ctas;
   DGLB200_REQUIRE(blocks < (1ll << 31), "gather_rows: grid too large");
   const char* xs = static_cast<const char*>(x);
   char* os = static_cast<char*>(out);
   if (unit == 16)
-    gather_rows_kernel<16><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, xs, row_bytes, os, lanes, bad_flag);
+    gather_rows_kernel<16><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, xs, x_ld_bytes, row_bytes, os, out_ld_bytes, bad_flag);
   else if (unit == 4)
-    gather_rows_kernel<4><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, xs, row_bytes, os, lanes, bad_flag);
+    gather_rows_kernel<4><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, xs, x_ld_bytes, row_bytes, os, out_ld_bytes, bad_flag);
   else
-    gather_rows_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, xs, row_bytes, os, lanes, bad_flag);
+    gather_rows_kernel<1><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, xs, x_ld_bytes, row_bytes, os, out_ld_bytes, bad_flag);
   DGLB200_POST_LAUNCH("gather_rows_kernel");
   return 0;
+}
+
+extern "C" int dglb200_gather_rows(int64_t n_out, const int64_t* idx, int64_t x_rows, const void* x,
+                                   int64_t row_bytes, void* out, int32_t* bad_flag, void* stream_) {
+  DGLB200_REQUIRE(idx != nullptr, "gather_rows: idx is NULL");
+  return dglb200_gather_rows_strided(n_out, idx, x_rows, x, row_bytes, row_bytes, out, row_bytes, bad_flag, 0,
+                                     stream_);
 }
 
 // ---- CUDA IPC: map a peer process's device allocation into this process, on the CURRENT device ----

@@ -16,6 +16,11 @@ import torch.distributed as dist
 from . import ops
 
 
+# CTAs of a peer pull (dglb200_gather_rows_strided max_ctas): enough bytes in flight to fill the
+# NVLink (4 x 16 B x 256 threads x 96 CTAs = 1.5 MB) while the concurrent SpMM keeps the SMs
+PULL_CTAS = 96
+
+
 def edge_balanced_bounds(indptr_in, indptr_out, parts):
     """Row-block boundaries [0 = b_0 <= ... <= b_parts = n] such that every block holds about
     the same number of in + out edges (forward and gradient work)."""
@@ -215,7 +220,8 @@ class RowPartition(object):
                     q = (self.rank + j) % self.world
                     b0, b1 = self.bounds[q], self.bounds[q + 1]
                     if b1 > b0:
-                        full[b0:b1, s0:s0 + self.SLAB].copy_(peers[q][b0:b1, s0:s0 + self.SLAB], non_blocking=True)
+                        ops.gather_rows(peers[q][b0:b1, s0:s0 + self.SLAB], None,
+                                        out=full[b0:b1, s0:s0 + self.SLAB], max_ctas=PULL_CTAS)
                 ev = torch.cuda.Event()
                 ev.record(self._comm)
                 events.append(ev)
@@ -369,7 +375,8 @@ class HaloExchange(object):
                 q = (self.rank + j) % self.world
                 if cnts[q]:
                     rows_q = self.bounds[q + 1] - self.bounds[q]
-                    self._gather(self._peer_buf[q][:rows_q], self.need_local[k][q], out=buf[offs[q]:offs[q] + cnts[q]])
+                    self._gather(self._peer_buf[q][:rows_q], self.need_local[k][q],
+                                 out=buf[offs[q]:offs[q] + cnts[q]], max_ctas=PULL_CTAS)
             return
         send = self._gather(buf[:self.rows], self.serve_local[k])
         dist.all_to_all_single(buf[start:start + sum(cnts)], send, output_split_sizes=cnts,

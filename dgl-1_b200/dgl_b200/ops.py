@@ -359,24 +359,49 @@ def unique_sorted(ids, id_bound, want_inverse=True):
     return uniq[:int(counts[0])], inv
 
 
-def gather_rows(x, idx, out=None):
-    """out[i] = x[idx[i]] (dglb200_gather_rows); idx int64 CUDA.  READ_ROW / halo packing.
-    The kernel runs on the device (and current stream) of `idx` / `out`; `x` may live on a PEER
-    device whose memory is mapped into this process (dist.share_with_peers): the rows are then
-    pulled over NVLink by the gathering GPU."""
+_BAD_FLAGS = {}
+
+
+def gather_rows(x, idx, out=None, max_ctas=0):
+    """out[i] = x[idx[i]] (idx int64 CUDA), or out[i] = x[i] when idx is None (strided block
+    copy).  x / out may be column blocks of wider row-major matrices.  The kernel runs on the
+    device (and current stream) of `out`; `x` may alias a PEER GPU's memory mapped into this
+    process (dist.share_with_peers): the rows are then pulled over NVLink by the gathering GPU.
+    max_ctas > 0 bounds the grid so that a concurrent SpMM keeps the SMs."""
     lib = _lib.get_lib()
-    _need_cuda(x, idx)
-    if not x.is_contiguous():
-        raise DGLError("gather_rows: x must be contiguous")
-    idx = idx.contiguous()
-    if idx.dtype != torch.int64:
-        raise DGLError("gather_rows: ids must be int64")
-    n_out = int(idx.shape[0])
+    _need_cuda(x, idx, out)
+    tail = tuple(x.shape[1:])
+    if x.dim() == 1:
+        x = x.reshape(-1, 1)
+    if x.dim() > 2:
+        if not x.is_contiguous():
+            raise DGLError("gather_rows: N-d x must be contiguous")
+        x2 = x.reshape(x.shape[0], -1)
+    else:
+        x2 = x
+    if x2.stride(1) != 1 and x2.shape[1] > 1:
+        raise DGLError("gather_rows: x must have unit inner stride")
+    n_out = int(idx.shape[0]) if idx is not None else int(x2.shape[0])
+    if idx is not None:
+        idx = idx.contiguous()
+        if idx.dtype != torch.int64:
+            raise DGLError("gather_rows: ids must be int64")
+    dev = out.device if out is not None else (idx.device if idx is not None else x.device)
+    ret = out
     if out is None:
-        out = torch.empty((n_out,) + tuple(x.shape[1:]), dtype=x.dtype, device=idx.device)
-    row_bytes = x.element_size() * (x.numel() // max(int(x.shape[0]), 1)) if x.shape[0] else x.element_size()
-    bad = torch.zeros(1, dtype=torch.int32, device=idx.device)
-    with torch.cuda.device(idx.device):
-        _lib.check_call(lib.dglb200_gather_rows(n_out, _ptr(idx), int(x.shape[0]), _ptr(x), row_bytes,
-                                                _ptr(out), _ptr(bad), _stream()))
-    return out
+        ret = torch.empty((n_out,) + tail, dtype=x.dtype, device=dev)
+    o2 = ret.reshape(n_out, -1) if ret.is_contiguous() else ret
+    if o2.dim() != 2 or (o2.stride(1) != 1 and o2.shape[1] > 1):
+        raise DGLError("gather_rows: out must be 2-D with unit inner stride")
+    es = x2.element_size()
+    row_bytes = int(x2.shape[1]) * es
+    x_ld = int(x2.stride(0)) * es if x2.shape[0] > 1 else row_bytes
+    o_ld = int(o2.stride(0)) * es if n_out > 1 else row_bytes
+    bad = _BAD_FLAGS.get(dev)
+    if bad is None:
+        bad = _BAD_FLAGS[dev] = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_gather_rows_strided(n_out, _ptr(idx), int(x2.shape[0]), _ptr(x2), max(x_ld, row_bytes),
+                                                        row_bytes, _ptr(o2), max(o_ld, row_bytes), _ptr(bad),
+                                                        int(max_ctas), _stream()))
+    return ret

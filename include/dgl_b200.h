@@ -287,6 +287,17 @@ int dglb200_unique_sorted(int64_t n, int64_t id_bound, const int64_t* ids,
 int dglb200_gather_rows(int64_t n_out, const int64_t* idx, int64_t x_rows, const void* x,
                         int64_t row_bytes, void* out, int32_t* bad_flag, void* stream);
 
+/*
+ * General form: x rows x_ld_bytes apart, out rows out_ld_bytes apart, row_bytes copied per row;
+ * idx == NULL copies row i to row i (a strided 2-D block copy).  max_ctas > 0 bounds the grid
+ * (grid-stride loop): pulls from a peer GPU over NVLink need bytes in flight, not SMs, and must
+ * leave the SMs to the SpMM running concurrently on another stream.
+ */
+int dglb200_gather_rows_strided(int64_t n_out, const int64_t* idx, int64_t x_rows,
+                                const void* x, int64_t x_ld_bytes, int64_t row_bytes,
+                                void* out, int64_t out_ld_bytes, int32_t* bad_flag,
+                                int max_ctas, void* stream);
+
 /* ---- CUDA IPC (multi-GPU peer-load exchange) ------------------------------------------------- */
 
 /*
