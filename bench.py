@@ -442,7 +442,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=["c2", "c5", "tiny"])
     ap.add_argument("--exchange", default="auto", choices=["auto", "allgather", "halo"])
-    ap.add_argument("--transport", default="nccl", choices=["nccl", "peer"],
+    ap.add_argument("--transport", default="peer", choices=["nccl", "peer"],
                     help="N>1 data path: NCCL collectives, or peer loads over NVLink from IPC-mapped buffers")
     ap.add_argument("--chunks", type=int, default=4, help="row chunks of the pipelined halo exchange")
     ap.add_argument("--check", action="store_true", help="N>1: verify the exchange against the all-gather path")

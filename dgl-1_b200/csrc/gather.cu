@@ -53,9 +53,87 @@ gather_rows_kernel(int64_t n_out, const int64_t* __restrict__ idx, int64_t x_row
   }
 }
 
+// Multi-source form: output row i comes from source `seg` with seg_ptr[seg] <= i < seg_ptr[seg+1],
+// row idx[i] of that source.  One launch pulls a halo chunk from ALL owners at once (every NVLink
+// peer busy simultaneously, no per-owner launch tails).
+constexpr int kMaxSources = 16;
+struct MultiSrc {
+  const char* base[kMaxSources];
+  int64_t rows[kMaxSources];
+  int64_t seg_ptr[kMaxSources + 1];
+  int n_src;
+};
+
+__global__ void __launch_bounds__(256)
+gather_rows_multi_kernel(const MultiSrc ms, const int64_t* __restrict__ idx, int64_t row_bytes,
+                         char* __restrict__ out, int32_t* __restrict__ bad) {
+  const int64_t lanes = row_bytes / 16;
+  const int64_t total = ms.seg_ptr[ms.n_src] * lanes;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  constexpr int K = 4;
+  for (int64_t u0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; u0 < total; u0 += stride * K) {
+    uint4 v[K];
+    int64_t dst_off[K];
+    bool ok[K];
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const int64_t u = u0 + (int64_t)k * stride;
+      ok[k] = u < total;
+      if (ok[k]) {
+        const int64_t row = u / lanes;
+        const int64_t lane = u - row * lanes;
+        int seg = 0;
+#pragma unroll
+        for (int q = 1; q < kMaxSources; ++q)
+          if (q < ms.n_src && row >= ms.seg_ptr[q]) seg = q;
+        const int64_t s = idx[row];
+        if (s < 0 || s >= ms.rows[seg]) {
+          atomicExch(bad, 1);
+          ok[k] = false;
+        } else {
+          v[k] = *reinterpret_cast<const uint4*>(ms.base[seg] + s * row_bytes + lane * 16);
+          dst_off[k] = row * row_bytes + lane * 16;
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < K; ++k)
+      if (ok[k]) *reinterpret_cast<uint4*>(out + dst_off[k]) = v[k];
+  }
+}
+
 }  // namespace dglb200
 
 using namespace dglb200;
+
+extern "C" int dglb200_gather_rows_multi(int n_src, const void* const* src_base_host,
+                                         const int64_t* src_rows_host, const int64_t* seg_ptr_host,
+                                         const int64_t* idx, int64_t row_bytes, void* out,
+                                         int32_t* bad_flag, int max_ctas, void* stream_) {
+  clear_error();
+  DGLB200_REQUIRE(n_src >= 1 && n_src <= kMaxSources, "gather_rows_multi: n_src %d out of range", n_src);
+  DGLB200_REQUIRE(src_base_host && src_rows_host && seg_ptr_host, "gather_rows_multi: NULL table");
+  DGLB200_REQUIRE(row_bytes >= 16 && row_bytes % 16 == 0, "gather_rows_multi: rows must be multiples of 16 bytes");
+  MultiSrc ms;
+  ms.n_src = n_src;
+  for (int q = 0; q < kMaxSources; ++q) {
+    ms.base[q] = q < n_src ? static_cast<const char*>(src_base_host[q]) : nullptr;
+    ms.rows[q] = q < n_src ? src_rows_host[q] : 0;
+  }
+  for (int q = 0; q <= kMaxSources; ++q) ms.seg_ptr[q] = seg_ptr_host[q <= n_src ? q : n_src];
+  const int64_t n_out = ms.seg_ptr[n_src];
+  if (n_out == 0) return 0;
+  DGLB200_REQUIRE(idx && out && bad_flag, "gather_rows_multi: NULL pointer");
+  DGLB200_REQUIRE((reinterpret_cast<uintptr_t>(out) & 15) == 0, "gather_rows_multi: out must be 16-byte aligned");
+  const int64_t total = n_out * (row_bytes / 16);
+  int64_t blocks = ceil_div(total, 256 * 4);
+  if (max_ctas > 0 && blocks > max_ctas) blocks = max_ctas;
+  DGLB200_REQUIRE(blocks < (1ll << 31), "gather_rows_multi: grid too large");
+  gather_rows_multi_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      ms, idx, row_bytes, static_cast<char*>(out), bad_flag);
+  DGLB200_POST_LAUNCH("gather_rows_multi_kernel");
+  return 0;
+}
 
 extern "C" int dglb200_gather_rows_strided(int64_t n_out, const int64_t* idx, int64_t x_rows,
                                            const void* x, int64_t x_ld_bytes, int64_t row_bytes,

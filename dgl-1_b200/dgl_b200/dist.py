@@ -18,7 +18,7 @@ from . import ops
 
 # CTAs of a peer pull (dglb200_gather_rows_strided max_ctas): enough bytes in flight to fill the
 # NVLink (4 x 16 B x 256 threads x 384 CTAs = 6 MB; measured on C5: 96 CTAs 290 GB/s, 192: 545, 384: 660 = full grid) while the concurrent SpMM keeps the SMs
-PULL_CTAS = 384
+PULL_CTAS = 256
 COMM_PRIORITY = -1      # side stream of the pulls: higher priority than the compute stream
 
 
@@ -316,7 +316,7 @@ class HaloExchange(object):
             self.need_local.append([local_k[int(cut[q]):int(cut[q + 1])].contiguous() for q in range(world)])
             off += per_chunk[k]
         # tell every owner which of its rows I need, per chunk
-        self.send_counts, self.serve_local = [], []
+        self.send_counts, self.serve_local, self.need_cat = [], [], []
         for k in range(self.chunks):
             rc = torch.tensor(self.recv_counts[k], dtype=torch.int64, device=dev)
             sc = torch.empty_like(rc)
@@ -331,6 +331,7 @@ class HaloExchange(object):
                 dist.all_to_all_single(serve, need_cat, output_split_sizes=sc,
                                        input_split_sizes=self.recv_counts[k], group=group)
             self.send_counts.append(sc)
+            self.need_cat.append(need_cat.contiguous())
             self.serve_local.append(serve.contiguous())           # already local ids of THIS rank
         self.chunk_csr = None
         self._buf = None
@@ -371,17 +372,14 @@ class HaloExchange(object):
         start = self.chunk_start[k]
         cnts = self.recv_counts[k]
         if self._peer_buf is not None:
-            off = start
-            offs = []
+            # one launch pulls this chunk's rows from every owner at once (NVLink peer loads)
+            seg = [0]
             for q in range(self.world):
-                offs.append(off)
-                off += cnts[q]
-            for j in range(1, self.world):                        # start at a different owner on every rank
-                q = (self.rank + j) % self.world
-                if cnts[q]:
-                    rows_q = self.bounds[q + 1] - self.bounds[q]
-                    self._gather(self._peer_buf[q][:rows_q], self.need_local[k][q],
-                                 out=buf[offs[q]:offs[q] + cnts[q]], max_ctas=PULL_CTAS)
+                seg.append(seg[-1] + cnts[q])
+            if seg[-1]:
+                srcs = [self._peer_buf[q][:self.bounds[q + 1] - self.bounds[q]] if q != self.rank else None
+                        for q in range(self.world)]
+                ops.gather_rows_multi(srcs, seg, self.need_cat[k], buf[start:start + seg[-1]], max_ctas=PULL_CTAS)
             return
         send = self._gather(buf[:self.rows], self.serve_local[k])
         dist.all_to_all_single(buf[start:start + sum(cnts)], send, output_split_sizes=cnts,

@@ -405,3 +405,27 @@ def gather_rows(x, idx, out=None, max_ctas=0):
                                                         row_bytes, _ptr(o2), max(o_ld, row_bytes), _ptr(bad),
                                                         int(max_ctas), _stream()))
     return ret
+
+
+def gather_rows_multi(sources, seg_ptr, idx, out, max_ctas=0):
+    """out[i] = sources[q][idx[i]] for seg_ptr[q] <= i < seg_ptr[q+1] (dglb200_gather_rows_multi):
+    one launch that pulls from several (peer) tensors at once.  sources: dense 2-D tensors of equal
+    width; seg_ptr: python list of len(sources)+1 offsets; idx int64 CUDA; out dense 2-D."""
+    lib = _lib.get_lib()
+    _need_cuda(idx, out)
+    n_src = len(sources)
+    es = out.element_size()
+    row_bytes = int(out.shape[1]) * es
+    base = (ctypes.c_void_p * n_src)(*[s.data_ptr() if s is not None else 0 for s in sources])
+    rows = (ctypes.c_int64 * n_src)(*[int(s.shape[0]) if s is not None else 0 for s in sources])
+    seg = (ctypes.c_int64 * (n_src + 1))(*[int(v) for v in seg_ptr])
+    dev = out.device
+    bad = _BAD_FLAGS.get(dev)
+    if bad is None:
+        bad = _BAD_FLAGS[dev] = torch.zeros(1, dtype=torch.int32, device=dev)
+    if not out.is_contiguous() or not idx.is_contiguous():
+        raise DGLError("gather_rows_multi: out and idx must be contiguous")
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_gather_rows_multi(n_src, base, rows, seg, _ptr(idx), row_bytes, _ptr(out),
+                                                      _ptr(bad), int(max_ctas), _stream()))
+    return out

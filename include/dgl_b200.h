@@ -298,6 +298,16 @@ int dglb200_gather_rows_strided(int64_t n_out, const int64_t* idx, int64_t x_row
                                 void* out, int64_t out_ld_bytes, int32_t* bad_flag,
                                 int max_ctas, void* stream);
 
+/*
+ * Multi-source form (one launch pulls a halo chunk from every owner at once): output row i, with
+ * seg_ptr[q] <= i < seg_ptr[q+1], is row idx[i] of source q (src_base[q], src_rows[q] rows of
+ * row_bytes bytes, dense).  The three tables are HOST arrays (n_src <= 16 entries, seg_ptr n_src+1);
+ * idx / out / bad_flag are device pointers.  row_bytes must be a multiple of 16.
+ */
+int dglb200_gather_rows_multi(int n_src, const void* const* src_base_host, const int64_t* src_rows_host,
+                              const int64_t* seg_ptr_host, const int64_t* idx, int64_t row_bytes,
+                              void* out, int32_t* bad_flag, int max_ctas, void* stream);
+
 /* ---- CUDA IPC (multi-GPU peer-load exchange) ------------------------------------------------- */
 
 /*

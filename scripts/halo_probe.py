@@ -72,15 +72,15 @@ def spmm_chunks():
 
 res = {}
 res["barrier_x2"] = timed(lambda: (h._barrier(), h._barrier()))
-for ctas in (0, 384):
+for ctas in (0, 256):
     bdist.PULL_CTAS = ctas
     res["fetch_ctas%d" % ctas] = timed(fetch_all)
 res["spmm_whole"] = timed(lambda: ops.spmm(h.csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=buf, out=y))
 res["spmm_chunks"] = timed(spmm_chunks)
-for prio in (0, -1):
+for prio in (-1,):
     bdist.COMM_PRIORITY = prio
     h._comm = None
-    for ctas in (0, 192, 384):
+    for ctas in (0, 128, 256, 512):
         bdist.PULL_CTAS = ctas
         res["pipelined_prio%d_ctas%d" % (prio, ctas)] = timed(lambda: h.aggregate(x_loc, part._spmm, y))
 sizes = [sum(c) * feat * 4 / 1e9 for c in h.recv_counts]
