@@ -444,7 +444,8 @@ def main():
     ap.add_argument("--exchange", default="auto", choices=["auto", "allgather", "halo"])
     ap.add_argument("--transport", default="peer", choices=["nccl", "peer"],
                     help="N>1 data path: NCCL collectives, or peer loads over NVLink from IPC-mapped buffers")
-    ap.add_argument("--chunks", type=int, default=4, help="row chunks of the pipelined halo exchange")
+    ap.add_argument("--chunks", type=int, default=1,
+                    help="row chunks of the pipelined halo exchange (1 = unpipelined; measured faster)")
     ap.add_argument("--check", action="store_true", help="N>1: verify the exchange against the all-gather path")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

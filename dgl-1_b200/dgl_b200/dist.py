@@ -16,9 +16,12 @@ import torch.distributed as dist
 from . import ops
 
 
-# CTAs of a peer pull (dglb200_gather_rows_strided max_ctas): enough bytes in flight to fill the
-# NVLink (4 x 16 B x 256 threads x 384 CTAs = 6 MB; measured on C5: 96 CTAs 290 GB/s, 192: 545, 384: 660 = full grid) while the concurrent SpMM keeps the SMs
-PULL_CTAS = 256
+# CTAs of a peer pull (max_ctas of the gather kernels; 0 = full grid).  Measured on C5: a pull needs
+# the whole GPU's bytes in flight to fill the NVLink (2 ranks: 96 CTAs 290 GB/s, 192: 545, 384 and
+# full grid: 660 GB/s; 8 ranks all-to-all: full grid 450 GB/s, 256 CTAs 260 GB/s), so bounding the grid
+# to co-schedule the SpMM loses more than the overlap wins: the pipelined paths below (row chunks /
+# feature slabs on a side stream) are kept selectable but are OFF by default
+PULL_CTAS = 0
 COMM_PRIORITY = -1      # side stream of the pulls: higher priority than the compute stream
 
 
@@ -197,14 +200,15 @@ class RowPartition(object):
         """Bytes this rank receives per exchange."""
         return (self.n - self.rows) * feat * elem if self.world > 1 else 0
 
-    SLAB = 64     # elements; the SpMM's own L2-residency slab width at C2 (spmm.cu pick_slab_chunks)
+    SLAB = 0      # feature-slab pipeline width in elements (64 = the SpMM's L2 slab at C2); 0 = off:
+                  # measured at 8 ranks on C2: 2.63 ms/step pipelined vs 2.48 ms/step plain
 
     def _aggregate(self, key, local, csr, out):
         """Exchange + SpMM.  With the peer transport the feature dimension is pipelined in slabs:
         slab s+1 is copied out of the owners' memory (NVLink) on a side stream while the SpMM runs
         over slab s (dglb200_spmm_csr_strided on column blocks of the gather buffer)."""
         feat = local.shape[1]
-        if key not in self._peer_full or feat <= self.SLAB or feat % self.SLAB:
+        if key not in self._peer_full or self.SLAB <= 0 or feat <= self.SLAB or feat % self.SLAB:
             return self._spmm(csr, self.exchange(key, local), out)
         full = self.full_buffer(key, feat, local)
         views = self.views(full)
