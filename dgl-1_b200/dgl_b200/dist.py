@@ -10,6 +10,8 @@ Gradient: all-gather the dY blocks, then the local transposed SpMM over the rank
 Only torch.distributed is used for the exchange (NCCL on GPUs, gloo in the CPU tests); the
 local compute is `ops.spmm` (libdgl_b200.so) unless a test injects a checker.
 """
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -22,6 +24,11 @@ from . import ops
 # to co-schedule the SpMM loses more than the overlap wins: the pipelined paths below (row chunks /
 # feature slabs on a side stream) are kept selectable but are OFF by default
 PULL_CTAS = 0
+# weight of a row relative to an edge in the partition balance (2 SpMMs per step write every row once)
+ROW_WEIGHT = float(os.environ.get("DGL_B200_ROW_WEIGHT", "2.0"))
+# halo pull: one fused launch over all owners ("fused") or one launch per owner in a rotating order
+# so that every owner serves exactly one puller at a time ("perpeer")
+PULL_MODE = os.environ.get("DGL_B200_PULL", "fused")
 COMM_PRIORITY = -1      # side stream of the pulls: higher priority than the compute stream
 
 
@@ -33,7 +40,7 @@ def edge_balanced_bounds(indptr_in, indptr_out, parts):
     C5: 11.5 ms vs 16.4 ms per SpMM at 2 ranks)."""
     n = int(indptr_in.shape[0] - 1)
     rows = torch.arange(n + 1, dtype=torch.float64, device=indptr_in.device)
-    load = (indptr_in + indptr_out).to(torch.float64) + 2.0 * rows
+    load = (indptr_in + indptr_out).to(torch.float64) + ROW_WEIGHT * rows
     total = float(load[-1])
     if parts == 1 or total == 0:
         step = (n + parts - 1) // parts
@@ -380,7 +387,13 @@ class HaloExchange(object):
             seg = [0]
             for q in range(self.world):
                 seg.append(seg[-1] + cnts[q])
-            if seg[-1]:
+            if seg[-1] and PULL_MODE == "perpeer":
+                for j in range(1, self.world):
+                    q = (self.rank + j) % self.world
+                    if cnts[q]:
+                        ops.gather_rows(self._peer_buf[q][:self.bounds[q + 1] - self.bounds[q]], self.need_local[k][q],
+                                        out=buf[start + seg[q]:start + seg[q + 1]], max_ctas=PULL_CTAS)
+            elif seg[-1]:
                 srcs = [self._peer_buf[q][:self.bounds[q + 1] - self.bounds[q]] if q != self.rank else None
                         for q in range(self.world)]
                 ops.gather_rows_multi(srcs, seg, self.need_cat[k], buf[start:start + seg[-1]], max_ctas=PULL_CTAS)
