@@ -1,0 +1,158 @@
+"""Per-config kernel timings for the BASELINE.json configs that are not bench.py's line
+(C1 Cora-shaped GCN, C3 PubMed-shaped GAT, C4 AIFB-shaped R-GCN) plus the structure kernels at C2
+size (CSR build, degree bucketing, unique).  One JSON line per measurement -> gpurun_out/configs.jsonl.
+
+Small configs are L2-resident and launch-latency-bound: the number of record is
+microseconds per op; the roofline fraction is informational.  Timing: CUDA events on the launching
+stream, 5 warm-ups, median of 20; small working sets stay in L2 on purpose (that IS their regime),
+the C2-size structure kernels stream far more than the 126 MB L2.
+"""
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for p in (ROOT, os.path.join(ROOT, "dgl-1_b200")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+from benchmarks import graphs  # noqa: E402
+from dgl_b200 import ops  # noqa: E402
+
+PEAK = 6540.5
+DEV = torch.device("cuda")
+
+
+def timeit(fn, warm=5, iters=20):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+OUT = []
+
+
+def report(config, op, ms, alg_bytes, **extra):
+    rec = dict(config=config, op=op, us=round(ms * 1e3, 2), alg_bytes=int(alg_bytes),
+               alg_GBps=round(alg_bytes / ms / 1e6, 1), frac_of_hbm_peak=round(alg_bytes / ms / 1e6 / PEAK, 4))
+    rec.update(extra)
+    OUT.append(rec)
+    print(json.dumps(rec), flush=True)
+
+
+def csr_of(src, dst, n):
+    return ops.csr_build(dst, src, n, n), ops.csr_build(src, dst, n, n)
+
+
+def c1():
+    c = graphs.C1_CORA
+    n = c["n"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], DEV, self_loops=True)
+    cin, cout = csr_of(src, dst, n)
+    e = cin.nnz
+    for feat in (c["hidden"], c["classes"], c["feat_in"]):
+        x = torch.randn(n, feat, device=DEV)
+        ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_SRC, ops.RED_SUM, x=x))
+        report("C1", "spmm copy_src->sum F=%d" % feat, ms, graphs.spmm_alg_bytes(e, n, feat), n=n, e=e)
+        ms = timeit(lambda: ops.spmm_backward_x(cout, x))
+        report("C1", "spmm gradient F=%d" % feat, ms, graphs.spmm_alg_bytes(e, n, feat), n=n, e=e)
+    ms = timeit(lambda: csr_of(src, dst, n))
+    report("C1", "csr_build in+out", ms, 2 * e * 24, n=n, e=e)
+
+
+def c3():
+    c = graphs.C3_PUBMED
+    n, heads, hid = c["n"], c["heads"], c["hidden"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], DEV, self_loops=True)
+    cin, cout = csr_of(src, dst, n)
+    e = cin.nnz
+    ft = torch.randn(n, heads, hid, device=DEV)
+    a1 = torch.randn(n, heads, device=DEV)
+    a2 = torch.randn(n, heads, device=DEV)
+    fused_bytes = e * (heads * hid * 4 + heads * 4 + 4) + n * heads * (hid + 2) * 4
+    ms = timeit(lambda: ops.gat_aggregate(cin, a1, a2, ft, 0.2, flavour=ops.SOFTMAX_GAT_EXAMPLE, want_edge=False))
+    report("C3", "fused GAT aggregation (example flavour)", ms, fused_bytes, n=n, e=e)
+    ms = timeit(lambda: ops.gat_aggregate(cin, a1, a2, ft, 0.2, flavour=ops.SOFTMAX_STABLE, want_edge=False))
+    report("C3", "fused GAT aggregation (stable softmax)", ms, fused_bytes, n=n, e=e)
+
+    def unfused():
+        s = ops.sddmm(cin, ops.SDDMM_ADD, a1, a2, heads, 1)
+        alpha = ops.edge_softmax(cin, s)
+        return ops.spmm(cin, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=ft.reshape(n, -1), w=alpha, w_width=heads)
+    ms = timeit(unfused)
+    report("C3", "sddmm(add) + edge_softmax + spmm(src_mul_edge) [3 kernels]", ms, fused_bytes + 4 * e * heads * 4, n=n, e=e)
+    u = torch.randn(n, heads * hid, device=DEV)
+    ms = timeit(lambda: ops.sddmm(cin, ops.SDDMM_DOT, u, u, heads, hid))
+    report("C3", "sddmm u.v H=8 D=8", ms, e * (2 * heads * hid * 4 + 4 + heads * 4), n=n, e=e)
+
+
+def c4():
+    c = graphs.C4_AIFB
+    n, hid = c["n"], c["hidden"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], DEV)
+    cin, _ = csr_of(src, dst, n)
+    e = cin.nnz
+    x = torch.randn(n, hid, device=DEV)
+    w = torch.rand(e, device=DEV)
+    ms = timeit(lambda: ops.spmm(cin, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w.reshape(-1, 1), w_width=1))
+    report("C4", "spmm src_mul_edge(scalar norm)->sum F=16, all relations in one launch", ms,
+           graphs.spmm_alg_bytes(e, n, hid, weights=True), n=n, e=e)
+    m = torch.randn(e, hid, device=DEV)
+    ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_EDGE, ops.RED_SUM, w=m))
+    report("C4", "spmm copy_edge->sum F=16 (typed messages)", ms, e * (hid * 4 + 4) + n * hid * 4, n=n, e=e)
+    ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_SRC, ops.RED_MAX, x=x, want_arg=True))
+    report("C4", "spmm copy_src->max + argmax F=16", ms, graphs.spmm_alg_bytes(e, n, hid) + n * hid * 4, n=n, e=e)
+
+
+def c2_structure():
+    c = graphs.C2_REDDIT
+    n, e = c["n"], c["e"]
+    src, dst = graphs.powerlaw_symmetric(n, e, c["seed"], DEV)
+    ms = timeit(lambda: ops.csr_build(dst, src, n, n), warm=2, iters=5)
+    report("C2", "csr_build (in-edge CSR from 114.6M-edge COO)", ms, e * (16 + 8) + 3 * 3 * e * 8, n=n, e=e)
+    mids = torch.arange(e, device=DEV)
+    recv = torch.arange(n, device=DEV)
+    ms = timeit(lambda: ops.degree_bucketing(mids, dst, recv, n), warm=1, iters=3)
+    report("C2", "degree_bucketing (114.6M messages, 233K nodes)", ms, e * 8 * 6, n=n, e=e)
+    ms = timeit(lambda: ops.unique_sorted(dst, n), warm=1, iters=3)
+    report("C2", "unique_sorted + inverse (114.6M ids)", ms, e * 8 * 5, n=n, e=e)
+    cin = ops.csr_build(dst, src, n, n)
+    del src, dst
+    for dt, b in ((torch.float32, 4), (torch.bfloat16, 2)):
+        x = torch.randn(n, 256, device=DEV).to(dt)
+        ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_SRC, ops.RED_SUM, x=x), warm=3, iters=10)
+        report("C2", "spmm copy_src->sum F=256 %s" % str(dt).split(".")[-1], ms,
+               graphs.spmm_alg_bytes(e, n, 256, elem=b), n=n, e=e)
+    x = torch.randn(n, 256, device=DEV)
+    w = torch.rand(e, 1, device=DEV)
+    ms = timeit(lambda: ops.spmm(cin, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w, w_width=1), warm=3, iters=10)
+    report("C2", "spmm src_mul_edge(scalar)->sum F=256 f32", ms, graphs.spmm_alg_bytes(e, n, 256, weights=True), n=n, e=e)
+    ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_SRC, ops.RED_MAX, x=x, want_arg=True), warm=3, iters=10)
+    report("C2", "spmm copy_src->max+argmax F=256 f32", ms, graphs.spmm_alg_bytes(e, n, 256) + n * 256 * 4, n=n, e=e)
+    for feat in (602, 41):
+        x = torch.randn(n, feat, device=DEV)
+        ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_SRC, ops.RED_SUM, x=x), warm=2, iters=5)
+        report("C2", "spmm copy_src->sum F=%d f32" % feat, ms, graphs.spmm_alg_bytes(e, n, feat), n=n, e=e)
+
+
+if __name__ == "__main__":
+    c1()
+    c3()
+    c4()
+    c2_structure()
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", "configs.jsonl"), "w") as f:
+        for r in OUT:
+            f.write(json.dumps(r) + "\n")
