@@ -81,7 +81,7 @@ def make_edges(cfg, device, e=None, scale_deg=1.0):
 # reference arm / cpu_baseline: torch.sparse.mm on the uncoalesced COO, CPU
 # ---------------------------------------------------------------------------------------------
 
-def cpu_reference(cfg, steps, warmup, budget_s=25.0):
+def cpu_reference(cfg, steps, warmup, budget_s=25.0, gcn=False):
     """Times fwd+bwd of th.sparse.mm on a bounded sample (same N and F, E/k edges of the same
     generator) sized so that steps+warmup passes take about `budget_s` seconds."""
     from oracle import oracle
@@ -115,7 +115,8 @@ def cpu_reference(cfg, steps, warmup, budget_s=25.0):
     ts = one_pass(src, dst, total)[warmup:] or [t_probe]
     t = sum(ts) / len(ts)
     alg = 2 * graphs.spmm_alg_bytes(e_s, n, feat)
-    return dict(value=alg / t / 1e9, unit=UNIT, cores=cores, kind="port",
+    gcn = gcn_epoch_cpu(src, dst, n, cfg) if (gcn and cfg["kind"] == "powerlaw") else None
+    return dict(gcn_epoch=gcn, value=alg / t / 1e9, unit=UNIT, cores=cores, kind="port",
                 sample="th.sparse.mm(COO)+autograd bwd, fp32, N=%d F=%d, E=%d of %d edges (1/%.1f), "
                        "%d timed passes, %.3f s/pass" % (n, feat, e_s, cfg["e"], cfg["e"] / e_s,
                                                          len(ts), t),
@@ -127,7 +128,7 @@ def run_reference(args):
     if rank != 0:
         return
     cfg = workload_cfg(args.workload)
-    r = cpu_reference(cfg, args.steps, args.warmup, budget_s=60.0)
+    r = cpu_reference(cfg, args.steps, args.warmup, budget_s=60.0, gcn=not args.no_gcn)
     line = {
         "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT,
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
@@ -137,9 +138,83 @@ def run_reference(args):
                    "sample_edges": r["sample_edges"]},
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "edge_feat_per_s": r["edge_feat_per_s"], "gpu_launches": 0,
+        "edge_feat_per_s": r["edge_feat_per_s"], "gpu_launches": 0, "gcn_epoch": r["gcn_epoch"],
     }
     print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------
+# GCN epoch (BASELINE.json metric, second half): the reference's examples/pytorch/gcn/gcn_spmv.py
+# model - per layer dropout, h @ W, * norm, update_all(copy_src, sum), * norm, + bias, activation -
+# two layers feat_in -> hidden -> classes, cross-entropy, Adam; one epoch = forward + backward +
+# optimizer step over the full graph.  Dense GEMMs are torch (cuBLAS / MKL) in both arms; the
+# aggregation is this engine's update_all in the B200 arm and th.sparse.mm in the reference arm.
+# ---------------------------------------------------------------------------------------------
+
+class GCNModel(object):
+    def __init__(self, feat_in, hidden, classes, device, dropout=0.5):
+        gen = torch.Generator().manual_seed(7)          # same weights on every rank
+        def uni(*shape):
+            stdv = 1.0 / (shape[-1] ** 0.5)             # reset_parameters of the example (gcn_spmv.py:35-39)
+            return ((torch.rand(*shape, generator=gen) * 2 - 1) * stdv).to(device).requires_grad_(True)
+        self.w1, self.b1 = uni(feat_in, hidden), uni(hidden)
+        self.w2, self.b2 = uni(hidden, classes), uni(classes)
+        self.params = [self.w1, self.b1, self.w2, self.b2]
+        self.dropout = dropout
+        self.opt = torch.optim.Adam(self.params, lr=1e-2, weight_decay=5e-4)
+
+    def forward(self, x, norm, aggregate):
+        drop = torch.nn.functional.dropout
+        h = torch.mm(drop(x, self.dropout), self.w1) * norm
+        h = torch.relu(aggregate(h, "h") * norm + self.b1)
+        h = torch.mm(drop(h, self.dropout), self.w2) * norm
+        return aggregate(h, "c") * norm + self.b2
+
+    def epoch(self, x, labels, norm, aggregate, n_total, allreduce=None):
+        logits = self.forward(x, norm, aggregate)
+        loss = torch.nn.functional.cross_entropy(logits, labels, reduction="sum") / n_total
+        self.opt.zero_grad(set_to_none=True)
+        loss.backward()
+        if allreduce is not None:                       # data-parallel: sum the per-rank weight gradients
+            flat = torch.cat([p.grad.reshape(-1) for p in self.params])
+            allreduce(flat)
+            o = 0
+            for p in self.params:
+                p.grad.copy_(flat[o:o + p.numel()].view_as(p))
+                o += p.numel()
+        self.opt.step()
+        return loss
+
+
+def gcn_dims(cfg):
+    c = graphs.C2_REDDIT
+    return c["feat_in"], cfg["feat"], c["classes"]
+
+
+def gcn_epoch_cpu(src, dst, n, cfg, epochs=2, warm=1):
+    """Reference arm: the same model with th.sparse.mm on the uncoalesced COO (CPU)."""
+    from oracle import oracle
+    feat_in, hidden, classes = gcn_dims(cfg)
+    e = src.shape[0]
+    idx, _ = oracle.get_adj_coo(src.numpy(), dst.numpy())
+    adj = torch.sparse_coo_tensor(torch.from_numpy(idx).view(2, e), torch.ones(e), (n, n))
+    deg = torch.bincount(dst, minlength=n).float()
+    norm = deg.pow(-0.5)
+    norm[torch.isinf(norm)] = 0
+    norm = norm.unsqueeze(1)
+    x = torch.randn(n, feat_in)
+    labels = torch.randint(0, classes, (n,))
+    model = GCNModel(feat_in, hidden, classes, "cpu")
+    agg = lambda h, tag: torch.sparse.mm(adj, h)  # noqa: E731
+    ts = []
+    for i in range(warm + epochs):
+        t0 = time.perf_counter()
+        model.epoch(x, labels, norm, agg, n)
+        ts.append(time.perf_counter() - t0)
+    ts = ts[warm:]
+    t = sum(ts) / len(ts)
+    return {"ms": t * 1e3, "edges": int(e), "edges_per_s": e / t, "epochs": len(ts),
+            "model": "GCN %d-%d-%d, dropout 0.5, Adam" % (feat_in, hidden, classes)}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -439,6 +514,55 @@ def run_b200(args):
     elif world > 1:
         e2e = None
 
+    # ---- GCN epoch (second half of BASELINE.json's metric) ------------------------------------
+    gcn = None
+    if not args.no_gcn and cfg["kind"] == "powerlaw" and exchange != "halo":
+        from dgl_b200 import function as fn
+        from dgl_b200 import dist as b200dist
+        feat_in, hidden, classes = gcn_dims(cfg)
+        deg = (loc_in.indptr[1:] - loc_in.indptr[:-1]).float()
+        norm = deg.pow(-0.5)
+        norm[torch.isinf(norm)] = 0
+        norm = norm.unsqueeze(1)
+        xg = torch.randn(rows, feat_in, device=dev, generator=gen)
+        labels = torch.randint(0, classes, (rows,), device=dev, generator=gen)
+        model = GCNModel(feat_in, hidden, classes, dev)
+        if world == 1:
+            g.set_csr(loc_in, loc_out)
+
+            def agg(h, tag):                     # the call a reference user makes (gcn_spmv.py:52-54)
+                g.ndata["h"] = h
+                g.update_all(fn.copy_src("h", "m"), fn.sum("m", "h"))
+                return g.ndata.pop("h")
+            allreduce = None
+        else:
+            if args.transport == "peer":
+                part.enable_peer_transport(hidden, like, keys=("xh", "dyh"))
+                part.enable_peer_transport(classes, like, keys=("xc", "dyc"))
+            agg = lambda h, tag: b200dist.aggregate(part, h, tag)  # noqa: E731
+            allreduce = lambda t: dist.all_reduce(t)  # noqa: E731
+        for _ in range(3):
+            model.epoch(xg, labels, norm, agg, n, allreduce)
+        barrier()
+        k = max(3, min(args.steps, 10))
+        l1 = _lib.launch_count()
+        a, b = ev(), ev()
+        a.record()
+        for _ in range(k):
+            loss = model.epoch(xg, labels, norm, agg, n, allreduce)
+        b.record()
+        barrier()
+        ms = a.elapsed_time(b) / k
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        gcn = {"ms": ms, "edges": int(e), "edges_per_s": e / (ms * 1e-3), "epochs": k,
+               "model": "GCN %d-%d-%d, dropout 0.5, Adam" % (feat_in, hidden, classes),
+               "loss": float(loss.item()), "engine_launches_per_epoch": (_lib.launch_count() - l1) / k}
+        del xg, labels, model
+        torch.cuda.empty_cache()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_reference(cfg, 2, 1, budget_s=20.0)
@@ -460,7 +584,7 @@ def run_b200(args):
                        "graph_build_s": round(t_build, 2)},
             "edge_feat_per_s": 2 * e * feat / (ms_step * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
-            "gpu_launches": int(launches), "clocks": clocks,
+            "gpu_launches": int(launches), "clocks": clocks, "gcn_epoch": gcn,
             "checked": bool(args.check and world > 1),
         }
         print(json.dumps(line), flush=True)
@@ -483,6 +607,7 @@ def main():
     ap.add_argument("--check", action="store_true", help="N>1: verify the exchange against the all-gather path")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-gcn", action="store_true", help="skip the GCN-epoch measurement")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

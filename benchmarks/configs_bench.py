@@ -139,6 +139,8 @@ def c2_structure():
     w = torch.rand(e, 1, device=DEV)
     ms = timeit(lambda: ops.spmm(cin, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w, w_width=1), warm=3, iters=10)
     report("C2", "spmm src_mul_edge(scalar)->sum F=256 f32", ms, graphs.spmm_alg_bytes(e, n, 256, weights=True), n=n, e=e)
+    ms = timeit(lambda: ops.edge_scalars_to_slots(cin, w), warm=3, iters=10)
+    report("C2", "edge_scalars_to_slots (w[eid] -> slot order)", ms, e * 12, n=n, e=e)
     ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_SRC, ops.RED_MAX, x=x, want_arg=True), warm=3, iters=10)
     report("C2", "spmm copy_src->max+argmax F=256 f32", ms, graphs.spmm_alg_bytes(e, n, 256) + n * 256 * 4, n=n, e=e)
     for feat in (602, 41):
@@ -148,10 +150,9 @@ def c2_structure():
 
 
 if __name__ == "__main__":
-    c1()
-    c3()
-    c4()
-    c2_structure()
+    sections = dict(c1=c1, c3=c3, c4=c4, c2=c2_structure)
+    for name in (sys.argv[1:] or list(sections)):
+        sections[name]()
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
     with open(os.path.join(ROOT, "gpurun_out", "configs.jsonl"), "w") as f:
         for r in OUT:

@@ -64,6 +64,37 @@ __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, i
   else reinterpret_cast<__nv_bfloat16*>(y)[row * y_ld + f] = __float2bfloat16_rn(acc);
 }
 
+// out[p] = w[eids[p]]: edge-id-ordered scalars -> CSR slot order (see dglb200_edge_scalars_to_slots).
+// Four independent gathers in flight per thread; the id read and the store are coalesced.
+template <typename T>
+__global__ void __launch_bounds__(256)
+edge_scalars_to_slots_kernel(int64_t nnz, const int32_t* __restrict__ eids, int64_t n_edges,
+                             const T* __restrict__ w, T* __restrict__ out, int32_t* __restrict__ bad) {
+  constexpr int K = 4;
+  const int64_t base = ((int64_t)blockIdx.x * K) * blockDim.x + threadIdx.x;
+  int32_t e[K];
+  T v[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int64_t p = base + (int64_t)k * blockDim.x;
+    e[k] = p < nnz ? ld_stream_i32(eids + p) : -1;
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int64_t p = base + (int64_t)k * blockDim.x;
+    if (p < nnz && (e[k] < 0 || e[k] >= n_edges)) {
+      if (bad != nullptr) atomicExch(bad, 1);
+      e[k] = -1;
+    }
+    if (e[k] >= 0) v[k] = w[e[k]];
+  }
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    const int64_t p = base + (int64_t)k * blockDim.x;
+    if (e[k] >= 0) out[p] = v[k];
+  }
+}
+
 SpmmTuning& spmm_tuning() {
   static SpmmTuning t;
   return t;
@@ -130,8 +161,16 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
   const int full_vec = dtype == DGLB200_F32 ? 4 : 8;
   if (a.x_ld == 0) a.x_ld = a.feat;
   if (a.y_ld == 0) a.y_ld = a.feat;
-  bool vec = a.feat % full_vec == 0 && aligned16(a.x) && aligned16(a.y) && a.x_ld % full_vec == 0 &&
-             a.y_ld % full_vec == 0;
+  // Vector (16-byte) path: gathered rows must start 16-byte aligned.  A feature width that is not
+  // a multiple of the vector still qualifies for copy_src / scalar-weight messages when the rows of
+  // x are padded (x_ld a multiple of the vector: the ragged last chunk reads the row's own padding);
+  // its outputs are then stored element-wise.  ops.spmm pads 602-wide rows to 604 this way.
+  const bool x_ok = aligned16(a.x) && a.x_ld % full_vec == 0;
+  a.y_vec = aligned16(a.y) && a.y_ld % full_vec == 0;
+  const bool ragged = a.feat % full_vec != 0;
+  const bool ragged_ok = msg == DGLB200_MSG_COPY_SRC ||
+                         (msg == DGLB200_MSG_SRC_MUL_EDGE && a.w_mode == kWScalar);
+  bool vec = ragged ? (ragged_ok && x_ok && a.x_ld >= a.feat + 1) : (x_ok && a.y_vec);
   if (a.w != nullptr && (a.w_mode == kWFull || msg == DGLB200_MSG_COPY_EDGE)) vec = vec && aligned16(a.w);
   a.slab_chunks = 0;
   if (vec && msg != DGLB200_MSG_COPY_EDGE && x_rows > 0)
@@ -282,6 +321,25 @@ int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz, const 
   }
   if (reduce_op != DGLB200_RED_MAX) a.arg = nullptr;
   return run_spmm(a, msg_op, reduce_op, dtype, plan, x_rows, nnz, static_cast<cudaStream_t>(stream));
+}
+
+int dglb200_edge_scalars_to_slots(int64_t nnz, const int32_t* eids, int64_t n_edges, int dtype,
+                                  const void* w, void* out, int32_t* bad_flag, void* stream_) {
+  clear_error();
+  DGLB200_REQUIRE(nnz >= 0 && nnz < (1ll << 31) && n_edges >= 0, "edge_scalars_to_slots: bad sizes");
+  DGLB200_REQUIRE(dtype == DGLB200_F32 || dtype == DGLB200_BF16, "edge_scalars_to_slots: unknown dtype %d", dtype);
+  if (nnz == 0) return 0;
+  DGLB200_REQUIRE(eids && w && out, "edge_scalars_to_slots: NULL pointer");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const unsigned blocks = (unsigned)ceil_div(nnz, 256 * 4);
+  if (dtype == DGLB200_F32)
+    edge_scalars_to_slots_kernel<float><<<blocks, 256, 0, stream>>>(
+        nnz, eids, n_edges, static_cast<const float*>(w), static_cast<float*>(out), bad_flag);
+  else
+    edge_scalars_to_slots_kernel<uint16_t><<<blocks, 256, 0, stream>>>(
+        nnz, eids, n_edges, static_cast<const uint16_t*>(w), static_cast<uint16_t*>(out), bad_flag);
+  DGLB200_POST_LAUNCH("edge_scalars_to_slots_kernel");
+  return 0;
 }
 
 int dglb200_spmm_csr_backward_x(int64_t n_rows, int64_t dy_rows, int64_t nnz, const int64_t* indptr,

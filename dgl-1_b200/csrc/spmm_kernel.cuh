@@ -23,6 +23,10 @@
 
 #include "common.cuh"
 
+#ifndef DGLB200_PACKED_ADD
+#define DGLB200_PACKED_ADD 1   // add.f32x2 (sm_100) in the copy->sum accumulate
+#endif
+
 namespace dglb200 {
 
 enum { kMsgMasked = 3 };  // internal: backward of MAX (gather form)
@@ -53,6 +57,7 @@ struct SpmmArgs {
   int slab_chunks;         // cap on the 16-byte chunks of a feature row per pass (0 = whole row)
   int64_t x_ld;            // leading dimension (elements) of x rows; == feat when dense
   int64_t y_ld;            // leading dimension (elements) of y rows
+  int y_vec;               // y rows take 16-byte stores (base and y_ld aligned)
 };
 
 constexpr int kSpmmThreads = 128;  // measured: 128 > 256 > 512 on C2 at every slab width
@@ -68,23 +73,33 @@ struct SpmmStage {
   float ws[U];    // scalar edge weight
 };
 
-template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads>
+// WS: the edge weight is one scalar per edge, known at compile time (src_mul_edge with w_width == 1:
+// the GCN-norm / R-GCN / single-head GAT case).  That variant carries no per-element weight
+// registers and no edge ids through the pipeline: 72 registers instead of 138, i.e. 7 CTAs per SM
+// instead of 3 (measured at C2: 31.7 ms -> see DESIGN.md section 6).
+template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads,
+          bool WS = false>
 __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
   constexpr int RPW = 32 / G;  // items per warp
   constexpr bool kMul = (MSG == DGLB200_MSG_SRC_MUL_EDGE || MSG == kMsgMasked);
+  constexpr bool kMulVec = kMul && !WS;   // element-wise / grouped weights (or decided at run time)
   constexpr bool kMasked = (MSG == kMsgMasked);
   constexpr bool kMax = (RED == DGLB200_RED_MAX);
   constexpr bool kNeedE = (MSG != DGLB200_MSG_COPY_SRC) || kMax;
   constexpr bool kNeedX = (MSG != DGLB200_MSG_COPY_EDGE);
+  constexpr bool kPackedAdd = !kMax && !kMul && (VEC % 2 == 0) && DGLB200_PACKED_ADD;
+  constexpr bool kPackedFma = !kMax && WS && !kMasked && (VEC % 2 == 0) && DGLB200_PACKED_ADD;
+  // edge ids ride through the pipeline only when a stage consumes them
+  constexpr bool kStageE = (MSG == DGLB200_MSG_COPY_EDGE) || kMax || kMasked || kMulVec;
   // register budget per stage: 32 loaded floats for plain gathers, 16 when weights/masks ride along
-  constexpr int kBudget = kMul ? 16 : 32;
+  constexpr int kBudget = kMulVec ? 16 : 32;
   constexpr int U0 = kBudget / (TILES * VEC);
   constexpr int UA = U0 >= 4 ? 4 : (U0 >= 2 ? 2 : 1);
   constexpr int U1 = UCAP > 0 ? UCAP : UA;                 // UCAP > 0: tuning override
   constexpr int U = U1 * 2 <= G ? U1 : G / 2;              // at least two steps per index block
   constexpr int SPI = G / U;  // steps served by one coalesced index load (even)
   static_assert(SPI >= 2 && SPI % 2 == 0, "pipeline needs an even number of steps per block");
-  using Stage = SpmmStage<U, TILES, VEC, kMul, kMasked>;
+  using Stage = SpmmStage<U, TILES, VEC, kMulVec, kMasked>;
 
   const int lane = threadIdx.x & 31;
   const int gl = lane % G;     // lane inside the group
@@ -144,9 +159,9 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
     xb[t] = static_cast<const char*>(MSG == DGLB200_MSG_COPY_EDGE ? a.w : a.x) + fo * (int64_t)sizeof(T);
     wb[t] = static_cast<const char*>(a.w) + fo * (int64_t)sizeof(T);
   }
-  const bool w_scalar = kMul && a.w != nullptr && a.w_mode == kWScalar;
-  const bool w_full = kMul && a.w != nullptr && a.w_mode == kWFull;
-  const bool w_grouped = kMul && a.w != nullptr && a.w_mode == kWGrouped;
+  const bool w_scalar = kMul && a.w != nullptr && (WS || a.w_mode == kWScalar);
+  const bool w_full = kMulVec && a.w != nullptr && a.w_mode == kWFull;
+  const bool w_grouped = kMulVec && a.w != nullptr && a.w_mode == kWGrouped;
 
   float acc[TILES][VEC];
   int32_t best[kMax ? TILES : 1][kMax ? VEC : 1];
@@ -185,7 +200,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
 #pragma unroll
     for (int k = 0; k < U; ++k) {
       st.s[k] = __shfl_sync(0xffffffffu, s, jj + k, G);
-      if (kNeedE) st.e[k] = __shfl_sync(0xffffffffu, e, jj + k, G);
+      if (kStageE) st.e[k] = __shfl_sync(0xffffffffu, e, jj + k, G);
       if (kMul) st.ws[k] = __shfl_sync(0xffffffffu, wsc, jj + k, G);
     }
 #pragma unroll
@@ -200,7 +215,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
         }
         if (ok) {
           Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(xb[t], gid, row_bytes)), st.xv[k][t]);
-          if constexpr (kMul) {
+          if constexpr (kMulVec) {
             if (w_full) {
               Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(wb[t], (uint32_t)st.e[k], w_row_bytes)),
                                   st.wv[k][t]);
@@ -226,19 +241,47 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
     for (int k = 0; k < U; ++k) {
 #pragma unroll
       for (int t = 0; t < TILES; ++t) {
+        if constexpr (kPackedAdd) {
+          // copy_src -> sum: the hot loop is issue-bound (SHFL + address + LDG.128 + 4 FADD per
+          // edge-lane); sm_100's packed add.f32x2 halves the FADD count.  Same rounding (rn), same
+          // order: results are bit-identical to the scalar form.  Tail lanes hold zeros.
+#pragma unroll
+          for (int v = 0; v < VEC; v += 2) {
+            const float2 r = __fadd2_rn(make_float2(acc[t][v], acc[t][v + 1]),
+                                        make_float2(st.xv[k][t][v], st.xv[k][t][v + 1]));
+            acc[t][v] = r.x;
+            acc[t][v + 1] = r.y;
+          }
+          continue;
+        }
+        if constexpr (kPackedFma) {
+          // scalar-weighted sum: acc += x * w as fma.rn.f32x2 (the scalar form contracts to the
+          // same FFMA, so the bits do not change)
+          const float2 wk = make_float2(st.ws[k], st.ws[k]);
+#pragma unroll
+          for (int v = 0; v < VEC; v += 2) {
+            const float2 r = __ffma2_rn(make_float2(st.xv[k][t][v], st.xv[k][t][v + 1]), wk,
+                                        make_float2(acc[t][v], acc[t][v + 1]));
+            acc[t][v] = r.x;
+            acc[t][v + 1] = r.y;
+          }
+          continue;
+        }
         const bool ok = FULL || (st.s[k] >= 0 && fvalid[t]);
 #pragma unroll
         for (int v = 0; v < VEC; ++v) {
           float m = st.xv[k][t][v];
           if constexpr (kMul) {
             if (w_scalar) m *= st.ws[k];
-            else if (w_full || w_grouped) m *= (ok ? st.wv[k][t][v] : 0.f);
+            if constexpr (kMulVec) {
+              if (w_full || w_grouped) m *= (ok ? st.wv[k][t][v] : 0.f);
+            }
             if (kMasked && ok && st.am[k][t][v] != st.e[k]) m = 0.f;
           }
           if (!kMax) {
             acc[t][v] += m;
-          } else if (ok && (best[t][v] < 0 || m > acc[t][v])) {  // strict '>': earliest slot wins ties
-            acc[t][v] = m;
+          } else if (ok && m > acc[t][v]) {  // strict '>': earliest slot wins ties; acc starts at -inf,
+            acc[t][v] = m;                   // an all -inf row is settled in the epilogue
             best[t][v] = st.e[k];
           }
         }
@@ -279,18 +322,36 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
 
   // ---- epilogue ---------------------------------------------------------------------------
   if (out_row < 0) return;
+  if constexpr (kMax) {
+    // No message beat -inf: an empty item yields 0 (the reference leaves zero-degree rows at the
+    // frame initializer's 0), a non-empty one is all -inf and its argmax is the first slot.
+    const int32_t first_e = len > 0 ? (a.eids ? a.eids[start] : (int32_t)start) : -1;
+#pragma unroll
+    for (int t = 0; t < TILES; ++t)
+#pragma unroll
+      for (int v = 0; v < VEC; ++v)
+        if (best[t][v] < 0) {
+          best[t][v] = first_e;
+          if (len == 0 && !to_partial) acc[t][v] = 0.f;
+        }
+  }
+  // A ragged last chunk (feat not a multiple of VEC, x rows padded up to x_ld) and outputs whose
+  // rows are not 16-byte aligned are stored element by element.
   if (to_partial) {
 #pragma unroll
     for (int t = 0; t < TILES; ++t) {
       if (!fvalid[t]) continue;
+      const int nv = (int)min((int64_t)VEC, a.feat - foff[t]);
       float* dst = a.partial + out_row * a.feat + foff[t];
 #pragma unroll
-      for (int v = 0; v < VEC; ++v) dst[v] = acc[t][v];
+      for (int v = 0; v < VEC; ++v)
+        if (v < nv) dst[v] = acc[t][v];
       if constexpr (kMax) {
         if (a.partial_arg != nullptr) {
           int32_t* da = a.partial_arg + out_row * a.feat + foff[t];
 #pragma unroll
-          for (int v = 0; v < VEC; ++v) da[v] = best[t][v];
+          for (int v = 0; v < VEC; ++v)
+            if (v < nv) da[v] = best[t][v];
         }
       }
     }
@@ -299,24 +360,33 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
 #pragma unroll
     for (int t = 0; t < TILES; ++t) {
       if (!fvalid[t]) continue;
+      const int nv = (int)min((int64_t)VEC, a.feat - foff[t]);
       if constexpr (kMax) {
-#pragma unroll
-        for (int v = 0; v < VEC; ++v)
-          if (best[t][v] < 0) acc[t][v] = 0.f;
         if (a.arg != nullptr) {
           int32_t* da = a.arg + out_row * a.feat + foff[t];
 #pragma unroll
-          for (int v = 0; v < VEC; ++v) da[v] = best[t][v];
+          for (int v = 0; v < VEC; ++v)
+            if (v < nv) da[v] = best[t][v];
         }
       }
-      Chunk<T, VEC>::store(y + out_row * a.y_ld + foff[t], acc[t]);
+      if (VEC == 1 || (nv == VEC && a.y_vec)) {
+        Chunk<T, VEC>::store(y + out_row * a.y_ld + foff[t], acc[t]);
+      } else {
+#pragma unroll
+        for (int v = 0; v < VEC; ++v)
+          if (v < nv) {
+            const float one[1] = {acc[t][v]};
+            Chunk<T, 1>::store(y + out_row * a.y_ld + foff[t] + v, one);
+          }
+      }
     }
   }
 }
 
 // ---- dispatch over (G, TILES, MSG, RED) for one storage type -----------------------------------
 
-template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads>
+template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads,
+          bool WS = false>
 int launch_one(const SpmmArgs& a, cudaStream_t stream) {
   constexpr int RPW = 32 / G;
   SpmmArgs args = a;
@@ -328,7 +398,7 @@ int launch_one(const SpmmArgs& a, cudaStream_t stream) {
                   (long long)blocks, (long long)slabs);
   if (blocks == 0) return 0;
   dim3 grid((unsigned)blocks, (unsigned)slabs);
-  spmm_kernel<T, VEC, G, TILES, MSG, RED, UCAP, NT><<<grid, NT, 0, stream>>>(args);
+  spmm_kernel<T, VEC, G, TILES, MSG, RED, UCAP, NT, WS><<<grid, NT, 0, stream>>>(args);
   DGLB200_POST_LAUNCH("spmm_kernel");
   return 0;
 }
@@ -369,7 +439,7 @@ int launch_tuned(const SpmmArgs& a, cudaStream_t stream, bool* handled) {
   return 0;
 }
 
-template <typename T, int VEC, int MSG, int RED>
+template <typename T, int VEC, int MSG, int RED, bool WS = false>
 int launch_shape(const SpmmArgs& a, cudaStream_t stream) {
   bool handled = false;
   const int rc = launch_tuned<T, VEC, MSG, RED>(a, stream, &handled);
@@ -378,14 +448,14 @@ int launch_shape(const SpmmArgs& a, cudaStream_t stream) {
   // L2-residency slabbing (run_spmm): a narrower pass keeps one feature slab of every source row
   // in the 126 MB L2 while all destination rows are visited; the slab index is blockIdx.y.
   if (a.slab_chunks > 0 && VEC > 1 && a.slab_chunks < chunks) chunks = a.slab_chunks;
-  if (chunks <= 4) return launch_one<T, VEC, 4, 1, MSG, RED>(a, stream);
-  if (chunks <= 8) return launch_one<T, VEC, 8, 1, MSG, RED>(a, stream);
-  if (chunks <= 16) return launch_one<T, VEC, 16, 1, MSG, RED>(a, stream);
-  if (chunks <= 32) return launch_one<T, VEC, 32, 1, MSG, RED>(a, stream);
+  if (chunks <= 4) return launch_one<T, VEC, 4, 1, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
+  if (chunks <= 8) return launch_one<T, VEC, 8, 1, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
+  if (chunks <= 16) return launch_one<T, VEC, 16, 1, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
+  if (chunks <= 32) return launch_one<T, VEC, 32, 1, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
   if (VEC * sizeof(T) == 16 && sizeof(T) == 2)  // bf16 vector path: 8 accumulators per tile
-    return launch_one<T, VEC, 32, (VEC == 1 ? 4 : 2), MSG, RED>(a, stream);
-  if (chunks <= 64 || VEC != 1) return launch_one<T, VEC, 32, 2, MSG, RED>(a, stream);
-  return launch_one<T, VEC, 32, 4, MSG, RED>(a, stream);
+    return launch_one<T, VEC, 32, (VEC == 1 ? 4 : 2), MSG, RED, 0, kSpmmThreads, WS>(a, stream);
+  if (chunks <= 64 || VEC != 1) return launch_one<T, VEC, 32, 2, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
+  return launch_one<T, VEC, 32, 4, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
 }
 
 template <typename T, int VEC>
@@ -393,14 +463,18 @@ int launch_ops(const SpmmArgs& a, int msg, int red, cudaStream_t stream) {
   if (red == DGLB200_RED_SUM) {
     switch (msg) {
       case DGLB200_MSG_COPY_SRC: return launch_shape<T, VEC, DGLB200_MSG_COPY_SRC, DGLB200_RED_SUM>(a, stream);
-      case DGLB200_MSG_SRC_MUL_EDGE: return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_SUM>(a, stream);
+      case DGLB200_MSG_SRC_MUL_EDGE:
+        if (a.w_mode == kWScalar) return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_SUM, true>(a, stream);
+        return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_SUM>(a, stream);
       case DGLB200_MSG_COPY_EDGE: return launch_shape<T, VEC, DGLB200_MSG_COPY_EDGE, DGLB200_RED_SUM>(a, stream);
       case kMsgMasked: return launch_shape<T, VEC, kMsgMasked, DGLB200_RED_SUM>(a, stream);
     }
   } else if (red == DGLB200_RED_MAX) {
     switch (msg) {
       case DGLB200_MSG_COPY_SRC: return launch_shape<T, VEC, DGLB200_MSG_COPY_SRC, DGLB200_RED_MAX>(a, stream);
-      case DGLB200_MSG_SRC_MUL_EDGE: return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_MAX>(a, stream);
+      case DGLB200_MSG_SRC_MUL_EDGE:
+        if (a.w_mode == kWScalar) return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_MAX, true>(a, stream);
+        return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_MAX>(a, stream);
       case DGLB200_MSG_COPY_EDGE: return launch_shape<T, VEC, DGLB200_MSG_COPY_EDGE, DGLB200_RED_MAX>(a, stream);
     }
   }

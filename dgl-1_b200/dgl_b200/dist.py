@@ -247,13 +247,34 @@ class RowPartition(object):
         self._barrier()                                           # nobody overwrites a block still being read
         return out
 
-    def forward(self, x_local, out=None):
-        """y_local = (A x)[r0:r1] for update_all(copy_src, sum)."""
-        return self._aggregate("x", x_local, self.loc_in, out)
+    def forward(self, x_local, out=None, key="x"):
+        """y_local = (A x)[r0:r1] for update_all(copy_src, sum).  `key` names the gather buffer: a
+        model that aggregates at several widths uses one key per width (no reallocation)."""
+        return self._aggregate(key, x_local, self.loc_in, out)
 
-    def backward(self, dy_local, out=None):
+    def backward(self, dy_local, out=None, key="dy"):
         """dx_local = (A^T dy)[r0:r1]."""
-        return self._aggregate("dy", dy_local, self.loc_out, out)
+        return self._aggregate(key, dy_local, self.loc_out, out)
+
+
+class _PartitionAggregate(torch.autograd.Function):
+    """Differentiable update_all(copy_src, sum) over a row partition: forward = exchange + SpMM over
+    the in-edge row block, backward = exchange of dy + SpMM over the out-edge row block (what torch
+    autograd does for th.sparse.mm in the reference, python/dgl/backend/pytorch/tensor.py:143-146)."""
+
+    @staticmethod
+    def forward(ctx, part, x_local, tag):
+        ctx.part, ctx.tag = part, tag
+        return part.forward(x_local.contiguous(), key="x" + tag)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return None, ctx.part.backward(dy.contiguous(), key="dy" + ctx.tag), None
+
+
+def aggregate(part, x_local, tag=""):
+    """update_all(copy_src, sum) on this rank's rows of a RowPartition, with autograd."""
+    return _PartitionAggregate.apply(part, x_local, tag)
 
 
 class HaloExchange(object):
@@ -469,7 +490,7 @@ class HaloPartition(RowPartition):
         self.loc_in, self.loc_out = self.halo_in.csr, self.halo_out.csr
 
     def _halo(self, key):
-        return self.halo_in if key == "x" else self.halo_out
+        return self.halo_in if key.startswith("x") else self.halo_out
 
     def enable_peer_transport(self, feat, like, keys=("x", "dy")):
         for key in keys:
@@ -487,12 +508,12 @@ class HaloPartition(RowPartition):
     def exchange_bytes(self, feat, elem=4):
         return max(self.halo_in.n_halo, self.halo_out.n_halo) * feat * elem
 
-    def forward(self, x_local, out=None):
+    def forward(self, x_local, out=None, key="x"):
         if out is None:
             out = torch.empty((self.rows, x_local.shape[1]), dtype=x_local.dtype, device=x_local.device)
         return self.halo_in.aggregate(x_local, self._spmm, out)
 
-    def backward(self, dy_local, out=None):
+    def backward(self, dy_local, out=None, key="dy"):
         if out is None:
             out = torch.empty((self.rows, dy_local.shape[1]), dtype=dy_local.dtype, device=dy_local.device)
         return self.halo_out.aggregate(dy_local, self._spmm, out)

@@ -182,6 +182,43 @@ def _flatten(t, n):
     return t.reshape(n, -1)
 
 
+def _pad_rows(x, multiple):
+    """Row-major copy of x whose leading dimension is rounded up to `multiple` elements (zero pad);
+    returns the (rows, feat) view into it."""
+    rows, feat = x.shape
+    ld = (feat + multiple - 1) // multiple * multiple
+    buf = torch.zeros((rows, ld), dtype=x.dtype, device=x.device)
+    buf[:, :feat].copy_(x)
+    return buf[:, :feat]
+
+
+SLOT_ORDER_MIN_NNZ = 1 << 22   # below this the per-slot w[eid] gather stays in L2 and costs nothing
+
+
+def edge_scalars_to_slots(csr, w):
+    """w (E,) or (E, 1) in edge-id order -> (nnz,) in the slot order of `csr`
+    (dglb200_edge_scalars_to_slots).  Identity when the CSR carries no edge ids."""
+    lib = _lib.get_lib()
+    _need_cuda(w, csr.indptr)
+    flat = w.contiguous().reshape(-1)
+    if csr.eids is None:
+        return flat
+    out = torch.empty((csr.nnz,), dtype=w.dtype, device=w.device)
+    with torch.cuda.device(w.device):
+        _lib.check_call(lib.dglb200_edge_scalars_to_slots(
+            csr.nnz, _ptr(csr.eids), flat.numel(), _dtype_code(w), _ptr(flat), _ptr(out), None, _stream()))
+    return out
+
+
+def _slot_ordered_scalar(csr, w, w_width, need_eids):
+    """(w, eids) to hand to the kernel: large graphs with a scalar weight per edge get the weights
+    permuted to slot order once (coalesced reads in every feature slab afterwards)."""
+    if (w is None or w_width != 1 or need_eids or csr.eids is None or csr.nnz < SLOT_ORDER_MIN_NNZ
+            or w.numel() != w.shape[0]):
+        return w, csr.eids
+    return edge_scalars_to_slots(csr, w), None
+
+
 def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chunk=DEFAULT_CHUNK,
          out=None):
     """y[r] = reduce over row r of msg(x[indices], w[eids]); 2-D (rows, feat) tensors.
@@ -209,6 +246,13 @@ def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chun
         w = w.contiguous()
         if w.dtype != ref.dtype:
             raise DGLError("spmm: edge data dtype %s != feature dtype %s" % (w.dtype, ref.dtype))
+    # ragged widths (602 = Reddit's input features): pad the gathered rows to a 16-byte multiple so
+    # the kernel keeps its 128-bit loads; one n x feat copy against nnz x feat gathered elements
+    vec = 16 // ref.element_size()
+    if (x is not None and feat % vec != 0 and feat > 2 * vec and csr.nnz >= 4 * csr.n_cols
+            and (msg_op == MSG_COPY_SRC or (msg_op == MSG_SRC_MUL_EDGE and w_width == 1))
+            and (x.stride(0) % vec != 0 or x.data_ptr() % 16 != 0)):
+        x = _pad_rows(x, vec)
     if out is not None and not rows_ok(out):
         raise DGLError("spmm: `out` must be row-major with unit inner stride")
     y = out if out is not None else torch.empty((csr.n_rows, feat), dtype=ref.dtype, device=ref.device)
@@ -219,9 +263,12 @@ def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chun
     plan_ref = ctypes.byref(plan) if plan is not None else None
     x_ld = int(x.stride(0)) if (x is not None and x.shape[0] > 1) else feat
     y_ld = int(y.stride(0)) if y.shape[0] > 1 else feat
+    eids = csr.eids
+    if msg_op == MSG_SRC_MUL_EDGE:
+        w, eids = _slot_ordered_scalar(csr, w, w_width, need_eids=arg is not None)
     with torch.cuda.device(ref.device):
         _lib.check_call(lib.dglb200_spmm_csr_strided(
-            csr.n_rows, csr.n_cols, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids),
+            csr.n_rows, csr.n_cols, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices), _ptr(eids),
             msg_op, reduce_op, dt, _ptr(x), max(x_ld, feat), feat, _ptr(w), w_width, _ptr(y),
             max(y_ld, feat), _ptr(arg), plan_ref, _stream()))
     return y, arg
@@ -231,16 +278,23 @@ def spmm_backward_x(csr_t, dy, w=None, w_width=1, arg=None, chunk=DEFAULT_CHUNK)
     """dx over the CSR keyed by source (see dglb200_spmm_csr_backward_x)."""
     lib = _lib.get_lib()
     _need_cuda(dy, w, arg)
-    dy = dy.contiguous()
     feat = int(dy.shape[1])
+    if arg is None and feat % (16 // dy.element_size()) != 0:
+        # the unmasked gradient IS the forward op over the transposed CSR; ragged widths take the
+        # row-padding route of spmm()
+        msg = MSG_COPY_SRC if w is None else MSG_SRC_MUL_EDGE
+        return spmm(csr_t, msg, RED_SUM, x=dy, w=w, w_width=w_width, chunk=chunk)[0]
+    dy = dy.contiguous()
     dx = torch.empty((csr_t.n_rows, feat), dtype=dy.dtype, device=dy.device)
     plan = csr_t.plan(chunk).struct(feat, False) if chunk else None
     plan_ref = ctypes.byref(plan) if plan is not None else None
+    eids = csr_t.eids
     if w is not None:
         w = w.contiguous()
+        w, eids = _slot_ordered_scalar(csr_t, w, w_width, need_eids=arg is not None)
     with torch.cuda.device(dy.device):
         _lib.check_call(lib.dglb200_spmm_csr_backward_x(
-            csr_t.n_rows, csr_t.n_cols, csr_t.nnz, _ptr(csr_t.indptr), _ptr(csr_t.indices), _ptr(csr_t.eids),
+            csr_t.n_rows, csr_t.n_cols, csr_t.nnz, _ptr(csr_t.indptr), _ptr(csr_t.indices), _ptr(eids),
             _dtype_code(dy), _ptr(dy), feat, _ptr(w), w_width, _ptr(arg), _ptr(dx), plan_ref,
             _stream()))
     return dx

@@ -234,3 +234,87 @@ def test_gather_rows():
     xb = torch.randn(64, 40, device="cuda").bfloat16()
     idx = torch.randint(0, 64, (100,), device="cuda")
     assert torch.equal(ops.gather_rows(xb, idx), xb[idx])
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_slot_ordered_scalar_weights(dtype, monkeypatch):
+    """dglb200_edge_scalars_to_slots + eids == NULL: the large-graph form of SPMV_WITH_DATA.
+    The permutation is bit-exact; forward and dx equal the edge-id-indexed form bit for bit."""
+    from dgl_b200 import ops
+    n, feat = 500, 64
+    src, dst = random_graph(n, 9000, 11, hubs=2, hub_deg=900, zero_deg_frac=0.1)
+    csr, csr_t = _csr(src, dst, n), _csr(src, dst, n, transpose=True)
+    rs = np.random.RandomState(3)
+    x = torch.from_numpy(rs.randn(n, feat).astype(np.float32)).cuda().to(dtype)
+    w = torch.from_numpy(rs.rand(len(src), 1).astype(np.float32)).cuda().to(dtype)
+    ws = ops.edge_scalars_to_slots(csr, w)
+    assert torch.equal(ws, w.reshape(-1)[csr.eids.long()])
+    y0, _ = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w, w_width=1)
+    dx0 = ops.spmm_backward_x(csr_t, x, w=w, w_width=1)
+    monkeypatch.setattr(ops, "SLOT_ORDER_MIN_NNZ", 0)
+    y1, _ = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w, w_width=1)
+    dx1 = ops.spmm_backward_x(csr_t, x, w=w, w_width=1)
+    assert torch.equal(y0, y1) and torch.equal(dx0, dx1)
+    if dtype == torch.float32:
+        want = oracle.update_all(src, dst, n, "src_mul_edge", "sum", x=x.cpu().numpy(), w=w.cpu().numpy())
+        _close(y1, want, RTOL_F32)
+    # MAX with argmax keeps the edge-id form (ids are an output)
+    y2, a2 = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_MAX, x=x, w=w, w_width=1, want_arg=True)
+    monkeypatch.setattr(ops, "SLOT_ORDER_MIN_NNZ", 1 << 22)
+    y3, a3 = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_MAX, x=x, w=w, w_width=1, want_arg=True)
+    assert torch.equal(y2, y3) and torch.equal(a2, a3)
+
+
+@pytest.mark.parametrize("feat", [4, 6, 64])
+def test_max_with_minus_inf_messages(feat):
+    """Rows whose messages are all -inf keep -inf with the first edge as argmax; zero-degree rows
+    stay 0 / -1; mixed rows pick the first finite maximum (long-row slices included)."""
+    from dgl_b200 import ops
+    n = 120
+    src, dst = random_graph(n, 1500, 77 + feat, hubs=2, hub_deg=300, zero_deg_frac=0.2)
+    rng = np.random.RandomState(feat)
+    x = rng.randint(-2, 3, size=(n, feat)).astype(np.float32)
+    x[rng.rand(n) < 0.6] = -np.inf          # most sources send -inf on every feature
+    x[rng.rand(n, feat) < 0.2] = -np.inf
+    want, warg = oracle.reduce_max(dst, oracle.message("copy_src", src, x), n)
+    csr = _csr(src, dst, n)
+    for chunk in (0, 32):
+        y, arg = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_MAX, x=torch.from_numpy(x).cuda(),
+                          want_arg=True, chunk=chunk)
+        assert np.array_equal(y.cpu().numpy(), want)
+        assert np.array_equal(arg.cpu().numpy().astype(np.int64), warg)
+
+
+@pytest.mark.parametrize("feat", [41, 602, 90])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_ragged_width_takes_padded_vector_path(feat, dtype):
+    """feat not a multiple of the 16-byte vector: ops.spmm pads the gathered rows (x_ld) and the
+    kernel stores the ragged last chunk element-wise; a strided out block next to live data must
+    not be clobbered."""
+    from dgl_b200 import ops
+    n = 300
+    src, dst = random_graph(n, 5000, feat, hubs=2, hub_deg=600, zero_deg_frac=0.1)
+    rs = np.random.RandomState(feat)
+    x = rs.randn(n, feat).astype(np.float32)
+    w = rs.rand(len(src), 1).astype(np.float32)
+    csr = _csr(src, dst, n)
+    xt, wt = torch.from_numpy(x).cuda().to(dtype), torch.from_numpy(w).cuda().to(dtype)
+    rtol = RTOL_F32 if dtype == torch.float32 else RTOL_BF16
+    xr, wr = xt.float().cpu().numpy(), wt.float().cpu().numpy()
+    for msg, code, ww in (("copy_src", ops.MSG_COPY_SRC, None), ("src_mul_edge", ops.MSG_SRC_MUL_EDGE, wt)):
+        want = oracle.update_all(src, dst, n, msg, "sum", x=xr, w=wr if ww is not None else None)
+        for chunk in (0, 64):
+            y, _ = ops.spmm(csr, code, ops.RED_SUM, x=xt, w=ww, w_width=1, chunk=chunk)
+            _close(y, want, rtol)
+        big = torch.full((n, feat + 7), 7.0, dtype=dtype, device="cuda")
+        ops.spmm(csr, code, ops.RED_SUM, x=xt, w=ww, w_width=1, out=big[:, 3:3 + feat])
+        _close(big[:, 3:3 + feat], want, rtol)
+        assert bool((big[:, :3] == 7).all()) and bool((big[:, 3 + feat:] == 7).all())
+    if dtype == torch.float32:
+        m = oracle.message("copy_src", src, x)
+        want, warg = oracle.reduce_max(dst, m, n)
+        y, arg = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_MAX, x=xt, want_arg=True, chunk=64)
+        assert np.array_equal(y.cpu().numpy(), want)
+        assert np.array_equal(arg.cpu().numpy().astype(np.int64), warg)
+        dx = ops.spmm_backward_x(_csr(src, dst, n, transpose=True), xt, w=wt, w_width=1)
+        _close(dx, oracle.spmm_grad(src, dst, n, x, w), rtol)

@@ -105,3 +105,53 @@ def test_bounds_degenerate_cases():
     ip = torch.tensor([0, 100, 100, 100, 100], dtype=torch.int64)      # one hub row
     b = edge_balanced_bounds(ip, ip, 2)
     assert b[0] == 0 and b[-1] == 4 and b == sorted(b)
+
+
+def _worker_autograd(rank, world, port, n, e, feat, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from dgl_b200 import dist as b200dist
+        src, dst = random_graph(n, e, 9, hubs=2, hub_deg=n // 3, zero_deg_frac=0.1)
+        part = b200dist.RowPartition(_csr_cpu(src, dst, n, False), _csr_cpu(src, dst, n, True),
+                                     spmm_fn=_oracle_block_spmm)
+        rng = np.random.RandomState(5)
+        x = rng.randn(n, feat).astype(np.float32)
+        c = rng.randn(n, 5).astype(np.float32)
+        xl = torch.from_numpy(x[part.r0:part.r1].copy()).requires_grad_(True)
+        y = b200dist.aggregate(part, xl, "wide")                 # two widths, one buffer key each
+        z = b200dist.aggregate(part, (2 * y)[:, :5], "narrow")
+        (z * torch.from_numpy(c[part.r0:part.r1])).sum().backward()
+        assert set(part._full) == {"xwide", "dywide", "xnarrow", "dynarrow"}
+        q.put((rank, z.detach().numpy(), xl.grad.numpy()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_partition_autograd_two_widths_gloo():
+    """dist.aggregate (what a row-partitioned GCN epoch calls twice per layer): forward values and
+    the gradient through two chained aggregations of different widths, world_size 2."""
+    world, n, e, feat = 2, 200, 3000, 8
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_autograd, args=(r, world, port, n, e, feat, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted([q.get(timeout=120) for _ in range(world)], key=lambda t: t[0])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    src, dst = random_graph(n, e, 9, hubs=2, hub_deg=n // 3, zero_deg_frac=0.1)
+    rng = np.random.RandomState(5)
+    x = rng.randn(n, feat).astype(np.float32)
+    c = rng.randn(n, 5).astype(np.float32)
+    y = oracle.update_all(src, dst, n, "copy_src", "sum", x=x)
+    z = oracle.update_all(src, dst, n, "copy_src", "sum", x=np.ascontiguousarray(2 * y[:, :5]))
+    want_dx = np.zeros_like(x)
+    want_dx[:, :5] = oracle.spmm_grad(src, dst, n, 2 * oracle.spmm_grad(src, dst, n, c))
+    got_z = np.concatenate([r[1] for r in res])
+    got_dx = np.concatenate([r[2] for r in res])
+    np.testing.assert_allclose(got_z, z, rtol=1e-5, atol=1e-5 * np.abs(z).max())
+    np.testing.assert_allclose(got_dx, want_dx, rtol=1e-5, atol=1e-5 * np.abs(want_dx).max())
