@@ -139,8 +139,13 @@ def c2_structure():
     w = torch.rand(e, 1, device=DEV)
     ms = timeit(lambda: ops.spmm(cin, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w, w_width=1), warm=3, iters=10)
     report("C2", "spmm src_mul_edge(scalar)->sum F=256 f32", ms, graphs.spmm_alg_bytes(e, n, 256, weights=True), n=n, e=e)
-    ms = timeit(lambda: ops.edge_scalars_to_slots(cin, w), warm=3, iters=10)
-    report("C2", "edge_scalars_to_slots (w[eid] -> slot order)", ms, e * 12, n=n, e=e)
+    wh = torch.rand(e, 8, device=DEV)
+    ms = timeit(lambda: ops.spmm(cin, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=wh, w_width=8), warm=3, iters=10)
+    report("C2", "spmm src_mul_edge(8 heads x 32)->sum F=256 f32", ms,
+           graphs.spmm_alg_bytes(e, n, 256) + e * (8 * 4 + 4), n=n, e=e)
+    del wh
+    ms = timeit(lambda: ops.edge_data_to_slots(cin, w), warm=3, iters=10)
+    report("C2", "edge_data_to_slots (w[eid] -> slot order)", ms, e * 12, n=n, e=e)
     ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_SRC, ops.RED_MAX, x=x, want_arg=True), warm=3, iters=10)
     report("C2", "spmm copy_src->max+argmax F=256 f32", ms, graphs.spmm_alg_bytes(e, n, 256) + n * 256 * 4, n=n, e=e)
     for feat in (602, 41):

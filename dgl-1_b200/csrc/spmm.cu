@@ -64,34 +64,39 @@ __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, i
   else reinterpret_cast<__nv_bfloat16*>(y)[row * y_ld + f] = __float2bfloat16_rn(acc);
 }
 
-// out[p] = w[eids[p]]: edge-id-ordered scalars -> CSR slot order (see dglb200_edge_scalars_to_slots).
-// Four independent gathers in flight per thread; the id read and the store are coalesced.
-template <typename T>
+// out[p, :] = w[eids[p], :]: edge-id-ordered edge data -> CSR slot order (see
+// dglb200_edge_data_to_slots).  One thread per (slot, UNIT-byte element); four independent gathers
+// in flight per thread; id reads (L1-broadcast across a row's elements) and stores are coalesced.
+template <typename V>
 __global__ void __launch_bounds__(256)
-edge_scalars_to_slots_kernel(int64_t nnz, const int32_t* __restrict__ eids, int64_t n_edges,
-                             const T* __restrict__ w, T* __restrict__ out, int32_t* __restrict__ bad) {
+edge_data_to_slots_kernel(int64_t nnz, const int32_t* __restrict__ eids, int64_t n_edges, int units,
+                          const V* __restrict__ w, V* __restrict__ out, int32_t* __restrict__ bad) {
   constexpr int K = 4;
+  const int64_t total = nnz * units;
   const int64_t base = ((int64_t)blockIdx.x * K) * blockDim.x + threadIdx.x;
-  int32_t e[K];
-  T v[K];
+  int64_t srcoff[K];
+  V v[K];
 #pragma unroll
   for (int k = 0; k < K; ++k) {
-    const int64_t p = base + (int64_t)k * blockDim.x;
-    e[k] = p < nnz ? ld_stream_i32(eids + p) : -1;
-  }
-#pragma unroll
-  for (int k = 0; k < K; ++k) {
-    const int64_t p = base + (int64_t)k * blockDim.x;
-    if (p < nnz && (e[k] < 0 || e[k] >= n_edges)) {
-      if (bad != nullptr) atomicExch(bad, 1);
-      e[k] = -1;
+    const int64_t i = base + (int64_t)k * blockDim.x;
+    srcoff[k] = -1;
+    if (i < total) {
+      const int64_t p = i / units;
+      const int32_t e = __ldg(eids + p);
+      if (e < 0 || e >= n_edges) {
+        if (bad != nullptr) atomicExch(bad, 1);
+      } else {
+        srcoff[k] = (int64_t)e * units + (i - p * units);
+      }
     }
-    if (e[k] >= 0) v[k] = w[e[k]];
   }
 #pragma unroll
+  for (int k = 0; k < K; ++k)
+    if (srcoff[k] >= 0) v[k] = w[srcoff[k]];
+#pragma unroll
   for (int k = 0; k < K; ++k) {
-    const int64_t p = base + (int64_t)k * blockDim.x;
-    if (e[k] >= 0) out[p] = v[k];
+    const int64_t i = base + (int64_t)k * blockDim.x;
+    if (srcoff[k] >= 0) out[i] = v[k];
   }
 }
 
@@ -175,6 +180,20 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
   a.slab_chunks = 0;
   if (vec && msg != DGLB200_MSG_COPY_EDGE && x_rows > 0)
     a.slab_chunks = pick_slab_chunks(x_rows, nnz, (size_t)a.feat * (dtype == DGLB200_F32 ? 4 : 2));
+  // Per-head weights (E, H) on H x D features: when the passes can be cut so that none straddles
+  // two heads (a power-of-two number of 16-byte chunks dividing D), the scalar-weight kernel runs
+  // with w[e, head of the pass]; otherwise the per-chunk / generic variants take over.
+  a.w_slab_scalar = 0;
+  if (vec && msg == DGLB200_MSG_SRC_MUL_EDGE && a.w_mode == kWGrouped && a.w_group % full_vec == 0) {
+    const int64_t head_chunks = a.w_group / full_vec;
+    const int cap = a.slab_chunks > 0 ? a.slab_chunks : 64;
+    int p = 64;
+    while (p >= 4 && (p > cap || head_chunks % p != 0)) p >>= 1;
+    if (p >= 4) {
+      a.slab_chunks = p;
+      a.w_slab_scalar = 1;
+    }
+  }
   int rc = dtype == DGLB200_F32 ? launch_spmm_f32(a, msg, red, vec, stream)
                                 : launch_spmm_bf16(a, msg, red, vec, stream);
   if (rc != 0) return rc;
@@ -323,22 +342,27 @@ int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz, const 
   return run_spmm(a, msg_op, reduce_op, dtype, plan, x_rows, nnz, static_cast<cudaStream_t>(stream));
 }
 
-int dglb200_edge_scalars_to_slots(int64_t nnz, const int32_t* eids, int64_t n_edges, int dtype,
-                                  const void* w, void* out, int32_t* bad_flag, void* stream_) {
+int dglb200_edge_data_to_slots(int64_t nnz, const int32_t* eids, int64_t n_edges, int64_t row_bytes,
+                               const void* w, void* out, int32_t* bad_flag, void* stream_) {
   clear_error();
-  DGLB200_REQUIRE(nnz >= 0 && nnz < (1ll << 31) && n_edges >= 0, "edge_scalars_to_slots: bad sizes");
-  DGLB200_REQUIRE(dtype == DGLB200_F32 || dtype == DGLB200_BF16, "edge_scalars_to_slots: unknown dtype %d", dtype);
+  DGLB200_REQUIRE(nnz >= 0 && nnz < (1ll << 31) && n_edges >= 0, "edge_data_to_slots: bad sizes");
+  DGLB200_REQUIRE(row_bytes >= 2 && row_bytes % 2 == 0 && row_bytes <= 4096,
+                  "edge_data_to_slots: row_bytes %lld must be even and in [2, 4096]", (long long)row_bytes);
   if (nnz == 0) return 0;
-  DGLB200_REQUIRE(eids && w && out, "edge_scalars_to_slots: NULL pointer");
+  DGLB200_REQUIRE(eids && w && out, "edge_data_to_slots: NULL pointer");
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
-  const unsigned blocks = (unsigned)ceil_div(nnz, 256 * 4);
-  if (dtype == DGLB200_F32)
-    edge_scalars_to_slots_kernel<float><<<blocks, 256, 0, stream>>>(
-        nnz, eids, n_edges, static_cast<const float*>(w), static_cast<float*>(out), bad_flag);
+  const bool u4 = row_bytes % 4 == 0 && (reinterpret_cast<uintptr_t>(w) & 3) == 0 &&
+                  (reinterpret_cast<uintptr_t>(out) & 3) == 0;
+  const int units = (int)(row_bytes / (u4 ? 4 : 2));
+  const int64_t blocks = ceil_div(nnz * units, 256 * 4);
+  DGLB200_REQUIRE(blocks < (1ll << 31), "edge_data_to_slots: grid too large");
+  if (u4)
+    edge_data_to_slots_kernel<uint32_t><<<(unsigned)blocks, 256, 0, stream>>>(
+        nnz, eids, n_edges, units, static_cast<const uint32_t*>(w), static_cast<uint32_t*>(out), bad_flag);
   else
-    edge_scalars_to_slots_kernel<uint16_t><<<blocks, 256, 0, stream>>>(
-        nnz, eids, n_edges, static_cast<const uint16_t*>(w), static_cast<uint16_t*>(out), bad_flag);
-  DGLB200_POST_LAUNCH("edge_scalars_to_slots_kernel");
+    edge_data_to_slots_kernel<uint16_t><<<(unsigned)blocks, 256, 0, stream>>>(
+        nnz, eids, n_edges, units, static_cast<const uint16_t*>(w), static_cast<uint16_t*>(out), bad_flag);
+  DGLB200_POST_LAUNCH("edge_data_to_slots_kernel");
   return 0;
 }
 

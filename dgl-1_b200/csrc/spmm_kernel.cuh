@@ -58,39 +58,49 @@ struct SpmmArgs {
   int64_t x_ld;            // leading dimension (elements) of x rows; == feat when dense
   int64_t y_ld;            // leading dimension (elements) of y rows
   int y_vec;               // y rows take 16-byte stores (base and y_ld aligned)
+  int w_slab_scalar;       // per-head weights, every feature pass inside one head: scalar variant
 };
 
 constexpr int kSpmmThreads = 128;  // measured: 128 > 256 > 512 on C2 at every slab width
 constexpr int kSpmmWarps = kSpmmThreads / 32;
 // One pipeline stage: the U edges of a step, their loaded rows and per-edge scalars.
-template <int U, int TILES, int VEC, bool MUL, bool MASKED>
+template <int U, int TILES, int VEC, bool MUL, bool MASKED, bool CW>
 struct SpmmStage {
   float xv[U][TILES][VEC];
-  float wv[MUL ? U : 1][MUL ? TILES : 1][MUL ? VEC : 1];     // non-scalar edge weights
+  float wv[MUL ? U : 1][MUL ? TILES : 1][MUL ? VEC : 1];     // element-wise edge weights
+  float wc[CW ? U : 1][CW ? TILES : 1];                       // one weight per 16-byte chunk (per head)
   int32_t am[MASKED ? U : 1][MASKED ? TILES : 1][MASKED ? VEC : 1];  // argmax mask (backward of max)
   int32_t s[U];   // source row (or -1: no edge)
   int32_t e[U];   // edge id
   float ws[U];    // scalar edge weight
 };
 
-// WS: the edge weight is one scalar per edge, known at compile time (src_mul_edge with w_width == 1:
-// the GCN-norm / R-GCN / single-head GAT case).  That variant carries no per-element weight
-// registers and no edge ids through the pipeline: 72 registers instead of 138, i.e. 7 CTAs per SM
-// instead of 3 (measured at C2: 31.7 ms -> see DESIGN.md section 6).
+// WM, the compile-time weight mode of src_mul_edge:
+//  kWmScalar  one scalar per edge (w_width == 1: GCN norm on edges, R-GCN, single-head attention).  No
+//             per-element weight registers and no edge ids in the pipeline: 76 registers instead of
+//             138, 6 CTAs per SM instead of 3 (C2: 31.7 -> 8.2 ms).
+//  kWmChunk   one weight per head with head_dim a multiple of the vector (multi-head attention,
+//             (E, H, 1) weights): a lane's 16-byte chunk lies inside one head, so the weight is one
+//             4-byte load per (edge, chunk) and the accumulate is the same FFMA2.
+//  kWmAny     decided at run time (element-wise weights, ragged heads, the masked gradient).
+enum { kWmAny = 0, kWmScalar = 1, kWmChunk = 2 };
+
 template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads,
-          bool WS = false>
+          int WM = kWmAny>
 __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
+  constexpr bool WS = (WM == kWmScalar);
+  constexpr bool CW = (WM == kWmChunk);
   constexpr int RPW = 32 / G;  // items per warp
   constexpr bool kMul = (MSG == DGLB200_MSG_SRC_MUL_EDGE || MSG == kMsgMasked);
-  constexpr bool kMulVec = kMul && !WS;   // element-wise / grouped weights (or decided at run time)
+  constexpr bool kMulVec = kMul && WM == kWmAny;   // element-wise / grouped weights, decided at run time
   constexpr bool kMasked = (MSG == kMsgMasked);
   constexpr bool kMax = (RED == DGLB200_RED_MAX);
   constexpr bool kNeedE = (MSG != DGLB200_MSG_COPY_SRC) || kMax;
   constexpr bool kNeedX = (MSG != DGLB200_MSG_COPY_EDGE);
   constexpr bool kPackedAdd = !kMax && !kMul && (VEC % 2 == 0) && DGLB200_PACKED_ADD;
-  constexpr bool kPackedFma = !kMax && WS && !kMasked && (VEC % 2 == 0) && DGLB200_PACKED_ADD;
+  constexpr bool kPackedFma = !kMax && (WS || CW) && !kMasked && (VEC % 2 == 0) && DGLB200_PACKED_ADD;
   // edge ids ride through the pipeline only when a stage consumes them
-  constexpr bool kStageE = (MSG == DGLB200_MSG_COPY_EDGE) || kMax || kMasked || kMulVec;
+  constexpr bool kStageE = (MSG == DGLB200_MSG_COPY_EDGE) || kMax || kMasked || kMulVec || CW;
   // register budget per stage: 32 loaded floats for plain gathers, 16 when weights/masks ride along
   constexpr int kBudget = kMulVec ? 16 : 32;
   constexpr int U0 = kBudget / (TILES * VEC);
@@ -99,7 +109,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
   constexpr int U = U1 * 2 <= G ? U1 : G / 2;              // at least two steps per index block
   constexpr int SPI = G / U;  // steps served by one coalesced index load (even)
   static_assert(SPI >= 2 && SPI % 2 == 0, "pipeline needs an even number of steps per block");
-  using Stage = SpmmStage<U, TILES, VEC, kMulVec, kMasked>;
+  using Stage = SpmmStage<U, TILES, VEC, kMulVec, kMasked, CW>;
 
   const int lane = threadIdx.x & 31;
   const int gl = lane % G;     // lane inside the group
@@ -157,9 +167,13 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
     fvalid[t] = foff[t] < a.feat;
     const int64_t fo = fvalid[t] ? foff[t] : 0;
     xb[t] = static_cast<const char*>(MSG == DGLB200_MSG_COPY_EDGE ? a.w : a.x) + fo * (int64_t)sizeof(T);
-    wb[t] = static_cast<const char*>(a.w) + fo * (int64_t)sizeof(T);
+    wb[t] = static_cast<const char*>(a.w) + (CW ? fo / a.w_group : fo) * (int64_t)sizeof(T);
   }
-  const bool w_scalar = kMul && a.w != nullptr && (WS || a.w_mode == kWScalar);
+  const uint32_t wc_row_bytes = (uint32_t)(a.w_width * (int64_t)sizeof(T));   // kWmChunk: (E, H) rows
+  const bool w_scalar = kMul && !CW && a.w != nullptr && (WS || a.w_mode == kWScalar);
+  // kWmScalar also serves per-head weights when a feature pass never straddles two heads: the
+  // weight of (edge, pass) is then the scalar w[e, head of this pass]
+  const int64_t ws_head = WS ? fbase / a.w_group : 0;
   const bool w_full = kMulVec && a.w != nullptr && a.w_mode == kWFull;
   const bool w_grouped = kMulVec && a.w != nullptr && a.w_mode == kWGrouped;
 
@@ -191,7 +205,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
     if (p < end) {
       s = kNeedX ? ld_stream_i32(a.indices + p) : 0;
       if (kNeedE) e = a.eids ? ld_stream_i32(a.eids + p) : (int32_t)p;
-      if (w_scalar) wsc = to_float(w[e]);
+      if (w_scalar) wsc = to_float(WS ? w[(int64_t)e * a.w_width + ws_head] : w[e]);
     }
   };
   // issue every global load of one step; nothing here depends on another in-flight load
@@ -215,6 +229,9 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
         }
         if (ok) {
           Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(xb[t], gid, row_bytes)), st.xv[k][t]);
+          if constexpr (CW) {
+            st.wc[k][t] = to_float(*reinterpret_cast<const T*>(row_ptr(wb[t], (uint32_t)st.e[k], wc_row_bytes)));
+          }
           if constexpr (kMulVec) {
             if (w_full) {
               Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(wb[t], (uint32_t)st.e[k], w_row_bytes)),
@@ -234,6 +251,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
       }
     }
   };
+  auto ok_cw = [&](const Stage& st, int k, int t) { return st.s[k] >= 0 && fvalid[t]; };
   // fold one step into the accumulators, strictly in slot order
   auto consume = [&](auto full_tag, const Stage& st) {
     constexpr bool FULL = decltype(full_tag)::value;
@@ -257,7 +275,8 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
         if constexpr (kPackedFma) {
           // scalar-weighted sum: acc += x * w as fma.rn.f32x2 (the scalar form contracts to the
           // same FFMA, so the bits do not change)
-          const float2 wk = make_float2(st.ws[k], st.ws[k]);
+          const float wk1 = CW ? ((FULL || ok_cw(st, k, t)) ? st.wc[k][t] : 0.f) : st.ws[k];
+          const float2 wk = make_float2(wk1, wk1);
 #pragma unroll
           for (int v = 0; v < VEC; v += 2) {
             const float2 r = __ffma2_rn(make_float2(st.xv[k][t][v], st.xv[k][t][v + 1]), wk,
@@ -273,6 +292,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
           float m = st.xv[k][t][v];
           if constexpr (kMul) {
             if (w_scalar) m *= st.ws[k];
+            if constexpr (CW) m *= (ok ? st.wc[k][t] : 0.f);
             if constexpr (kMulVec) {
               if (w_full || w_grouped) m *= (ok ? st.wv[k][t][v] : 0.f);
             }
@@ -386,7 +406,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
 // ---- dispatch over (G, TILES, MSG, RED) for one storage type -----------------------------------
 
 template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads,
-          bool WS = false>
+          int WM = kWmAny>
 int launch_one(const SpmmArgs& a, cudaStream_t stream) {
   constexpr int RPW = 32 / G;
   SpmmArgs args = a;
@@ -398,7 +418,7 @@ int launch_one(const SpmmArgs& a, cudaStream_t stream) {
                   (long long)blocks, (long long)slabs);
   if (blocks == 0) return 0;
   dim3 grid((unsigned)blocks, (unsigned)slabs);
-  spmm_kernel<T, VEC, G, TILES, MSG, RED, UCAP, NT, WS><<<grid, NT, 0, stream>>>(args);
+  spmm_kernel<T, VEC, G, TILES, MSG, RED, UCAP, NT, WM><<<grid, NT, 0, stream>>>(args);
   DGLB200_POST_LAUNCH("spmm_kernel");
   return 0;
 }
@@ -439,7 +459,7 @@ int launch_tuned(const SpmmArgs& a, cudaStream_t stream, bool* handled) {
   return 0;
 }
 
-template <typename T, int VEC, int MSG, int RED, bool WS = false>
+template <typename T, int VEC, int MSG, int RED, int WM = kWmAny>
 int launch_shape(const SpmmArgs& a, cudaStream_t stream) {
   bool handled = false;
   const int rc = launch_tuned<T, VEC, MSG, RED>(a, stream, &handled);
@@ -448,14 +468,14 @@ int launch_shape(const SpmmArgs& a, cudaStream_t stream) {
   // L2-residency slabbing (run_spmm): a narrower pass keeps one feature slab of every source row
   // in the 126 MB L2 while all destination rows are visited; the slab index is blockIdx.y.
   if (a.slab_chunks > 0 && VEC > 1 && a.slab_chunks < chunks) chunks = a.slab_chunks;
-  if (chunks <= 4) return launch_one<T, VEC, 4, 1, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
-  if (chunks <= 8) return launch_one<T, VEC, 8, 1, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
-  if (chunks <= 16) return launch_one<T, VEC, 16, 1, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
-  if (chunks <= 32) return launch_one<T, VEC, 32, 1, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
+  if (chunks <= 4) return launch_one<T, VEC, 4, 1, MSG, RED, 0, kSpmmThreads, WM>(a, stream);
+  if (chunks <= 8) return launch_one<T, VEC, 8, 1, MSG, RED, 0, kSpmmThreads, WM>(a, stream);
+  if (chunks <= 16) return launch_one<T, VEC, 16, 1, MSG, RED, 0, kSpmmThreads, WM>(a, stream);
+  if (chunks <= 32) return launch_one<T, VEC, 32, 1, MSG, RED, 0, kSpmmThreads, WM>(a, stream);
   if (VEC * sizeof(T) == 16 && sizeof(T) == 2)  // bf16 vector path: 8 accumulators per tile
-    return launch_one<T, VEC, 32, (VEC == 1 ? 4 : 2), MSG, RED, 0, kSpmmThreads, WS>(a, stream);
-  if (chunks <= 64 || VEC != 1) return launch_one<T, VEC, 32, 2, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
-  return launch_one<T, VEC, 32, 4, MSG, RED, 0, kSpmmThreads, WS>(a, stream);
+    return launch_one<T, VEC, 32, (VEC == 1 ? 4 : 2), MSG, RED, 0, kSpmmThreads, WM>(a, stream);
+  if (chunks <= 64 || VEC != 1) return launch_one<T, VEC, 32, 2, MSG, RED, 0, kSpmmThreads, WM>(a, stream);
+  return launch_one<T, VEC, 32, 4, MSG, RED, 0, kSpmmThreads, WM>(a, stream);
 }
 
 template <typename T, int VEC>
@@ -464,7 +484,10 @@ int launch_ops(const SpmmArgs& a, int msg, int red, cudaStream_t stream) {
     switch (msg) {
       case DGLB200_MSG_COPY_SRC: return launch_shape<T, VEC, DGLB200_MSG_COPY_SRC, DGLB200_RED_SUM>(a, stream);
       case DGLB200_MSG_SRC_MUL_EDGE:
-        if (a.w_mode == kWScalar) return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_SUM, true>(a, stream);
+        if (a.w_mode == kWScalar || a.w_slab_scalar)
+          return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_SUM, kWmScalar>(a, stream);
+        if (a.w_mode == kWGrouped && a.w_group % VEC == 0)
+          return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_SUM, kWmChunk>(a, stream);
         return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_SUM>(a, stream);
       case DGLB200_MSG_COPY_EDGE: return launch_shape<T, VEC, DGLB200_MSG_COPY_EDGE, DGLB200_RED_SUM>(a, stream);
       case kMsgMasked: return launch_shape<T, VEC, kMsgMasked, DGLB200_RED_SUM>(a, stream);
@@ -473,7 +496,10 @@ int launch_ops(const SpmmArgs& a, int msg, int red, cudaStream_t stream) {
     switch (msg) {
       case DGLB200_MSG_COPY_SRC: return launch_shape<T, VEC, DGLB200_MSG_COPY_SRC, DGLB200_RED_MAX>(a, stream);
       case DGLB200_MSG_SRC_MUL_EDGE:
-        if (a.w_mode == kWScalar) return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_MAX, true>(a, stream);
+        if (a.w_mode == kWScalar || a.w_slab_scalar)
+          return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_MAX, kWmScalar>(a, stream);
+        if (a.w_mode == kWGrouped && a.w_group % VEC == 0)
+          return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_MAX, kWmChunk>(a, stream);
         return launch_shape<T, VEC, DGLB200_MSG_SRC_MUL_EDGE, DGLB200_RED_MAX>(a, stream);
       case DGLB200_MSG_COPY_EDGE: return launch_shape<T, VEC, DGLB200_MSG_COPY_EDGE, DGLB200_RED_MAX>(a, stream);
     }

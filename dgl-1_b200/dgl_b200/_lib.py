@@ -55,7 +55,7 @@ SIGNATURES = {
     "dglb200_spmm_csr_strided": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_int, c_int,
                                          c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
                                          ctypes.POINTER(SpmmPlanStruct), c_vp]),
-    "dglb200_edge_scalars_to_slots": (c_int, [c_i64, c_vp, c_i64, c_int, c_vp, c_vp, c_vp, c_vp]),
+    "dglb200_edge_data_to_slots": (c_int, [c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "dglb200_spmm_csr_backward_x": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_vp, c_i64,
                                             c_vp, c_i64, c_vp, c_vp,
                                             ctypes.POINTER(SpmmPlanStruct), c_vp]),

@@ -195,28 +195,30 @@ def _pad_rows(x, multiple):
 SLOT_ORDER_MIN_NNZ = 1 << 22   # below this the per-slot w[eid] gather stays in L2 and costs nothing
 
 
-def edge_scalars_to_slots(csr, w):
-    """w (E,) or (E, 1) in edge-id order -> (nnz,) in the slot order of `csr`
-    (dglb200_edge_scalars_to_slots).  Identity when the CSR carries no edge ids."""
+def edge_data_to_slots(csr, w):
+    """w (E,) or (E, k) in edge-id order -> the same rows in the slot order of `csr`
+    (dglb200_edge_data_to_slots).  Identity when the CSR carries no edge ids."""
     lib = _lib.get_lib()
     _need_cuda(w, csr.indptr)
-    flat = w.contiguous().reshape(-1)
+    w = w.contiguous()
     if csr.eids is None:
-        return flat
-    out = torch.empty((csr.nnz,), dtype=w.dtype, device=w.device)
+        return w
+    width = w.numel() // max(w.shape[0], 1)
+    out = torch.empty((csr.nnz,) + tuple(w.shape[1:]), dtype=w.dtype, device=w.device)
     with torch.cuda.device(w.device):
-        _lib.check_call(lib.dglb200_edge_scalars_to_slots(
-            csr.nnz, _ptr(csr.eids), flat.numel(), _dtype_code(w), _ptr(flat), _ptr(out), None, _stream()))
+        _lib.check_call(lib.dglb200_edge_data_to_slots(
+            csr.nnz, _ptr(csr.eids), w.shape[0], width * w.element_size(), _ptr(w), _ptr(out), None,
+            _stream()))
     return out
 
 
-def _slot_ordered_scalar(csr, w, w_width, need_eids):
-    """(w, eids) to hand to the kernel: large graphs with a scalar weight per edge get the weights
-    permuted to slot order once (coalesced reads in every feature slab afterwards)."""
-    if (w is None or w_width != 1 or need_eids or csr.eids is None or csr.nnz < SLOT_ORDER_MIN_NNZ
-            or w.numel() != w.shape[0]):
+def _slot_ordered_weights(csr, w, w_width, feat, need_eids):
+    """(w, eids) to hand to the kernel: on large graphs narrow edge weights (a scalar or one per
+    head) are permuted to slot order once, so that every feature slab reads them coalesced."""
+    if (w is None or need_eids or csr.eids is None or csr.nnz < SLOT_ORDER_MIN_NNZ
+            or w_width >= feat or w_width * w.element_size() > 64):
         return w, csr.eids
-    return edge_scalars_to_slots(csr, w), None
+    return edge_data_to_slots(csr, w.reshape(w.shape[0], -1)), None
 
 
 def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chunk=DEFAULT_CHUNK,
@@ -265,7 +267,7 @@ def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chun
     y_ld = int(y.stride(0)) if y.shape[0] > 1 else feat
     eids = csr.eids
     if msg_op == MSG_SRC_MUL_EDGE:
-        w, eids = _slot_ordered_scalar(csr, w, w_width, need_eids=arg is not None)
+        w, eids = _slot_ordered_weights(csr, w, w_width, feat, need_eids=arg is not None)
     with torch.cuda.device(ref.device):
         _lib.check_call(lib.dglb200_spmm_csr_strided(
             csr.n_rows, csr.n_cols, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices), _ptr(eids),
@@ -291,7 +293,7 @@ def spmm_backward_x(csr_t, dy, w=None, w_width=1, arg=None, chunk=DEFAULT_CHUNK)
     eids = csr_t.eids
     if w is not None:
         w = w.contiguous()
-        w, eids = _slot_ordered_scalar(csr_t, w, w_width, need_eids=arg is not None)
+        w, eids = _slot_ordered_weights(csr_t, w, w_width, feat, need_eids=arg is not None)
     with torch.cuda.device(dy.device):
         _lib.check_call(lib.dglb200_spmm_csr_backward_x(
             csr_t.n_rows, csr_t.n_cols, csr_t.nnz, _ptr(csr_t.indptr), _ptr(csr_t.indices), _ptr(eids),

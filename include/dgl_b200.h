@@ -175,17 +175,18 @@ int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz,
                              const dglb200_spmm_plan_t* plan, void* stream);
 
 /*
- * Scalar edge data in edge-id order -> CSR slot order: out[p] = w[eids[p]], p in [0, nnz).
+ * Narrow edge data (a scalar or one weight per head) in edge-id order -> CSR slot order:
+ * out[p, :] = w[eids[p], :], p in [0, nnz), rows of row_bytes bytes (even, <= 4096).
  * The SpMM kernels index edge data with e(p) = eids[p], or p itself when eids == NULL; on a large
- * graph the per-slot w[eids[p]] read is a random 4-byte gather repeated for every feature slab
- * (measured 38 ms instead of 7 ms at 114.6M edges), so callers that reduce with SUM (no arg
- * output, edge ids not needed) permute once with this entry point and pass eids = NULL + out as w.
- * This is the READ_ROW(edge_frame, eid) of the reference's SPMV_WITH_DATA schedule
+ * graph the per-slot w[eids[p]] read is a random gather repeated for every feature slab (measured
+ * 38 ms instead of 7 ms at 114.6M edges with scalar weights), so callers that reduce with SUM (no
+ * arg output, edge ids not needed) permute once with this entry point and pass eids = NULL + out
+ * as w.  This is the READ_ROW(edge_frame, eid) of the reference's SPMV_WITH_DATA schedule
  * (python/dgl/runtime/scheduler.py:540-559, runtime/spmv.py:154-227).  Ids outside [0, n_edges)
  * are never dereferenced (the slot is left unwritten); bad_flag (nullable) is set to 1 for them.
  */
-int dglb200_edge_scalars_to_slots(int64_t nnz, const int32_t* eids, int64_t n_edges, int dtype,
-                                  const void* w, void* out, int32_t* bad_flag, void* stream);
+int dglb200_edge_data_to_slots(int64_t nnz, const int32_t* eids, int64_t n_edges, int64_t row_bytes,
+                               const void* w, void* out, int32_t* bad_flag, void* stream);
 
 /*
  * Gradient of MAX wrt x (and of SUM, with arg == NULL) in gather form over the CSR keyed by

@@ -67,7 +67,8 @@ def test_copy_src_sum(feat, chunk):
 
 
 @pytest.mark.parametrize("feat,wshape", [(1, ()), (8, ()), (8, (1,)), (64, ()), (64, (64,)),
-                                         (64, (8,)), (60, (5,)), (7, (7,)), (256, ())])
+                                         (64, (8,)), (60, (5,)), (7, (7,)), (256, ()),
+                                         (24, (8,)), (256, (8,)), (6, (2,))])
 @pytest.mark.parametrize("chunk", [32, 512])
 def test_src_mul_edge_sum(feat, wshape, chunk):
     from dgl_b200 import ops
@@ -238,7 +239,7 @@ def test_gather_rows():
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_slot_ordered_scalar_weights(dtype, monkeypatch):
-    """dglb200_edge_scalars_to_slots + eids == NULL: the large-graph form of SPMV_WITH_DATA.
+    """dglb200_edge_data_to_slots + eids == NULL: the large-graph form of SPMV_WITH_DATA.
     The permutation is bit-exact; forward and dx equal the edge-id-indexed form bit for bit."""
     from dgl_b200 import ops
     n, feat = 500, 64
@@ -247,8 +248,8 @@ def test_slot_ordered_scalar_weights(dtype, monkeypatch):
     rs = np.random.RandomState(3)
     x = torch.from_numpy(rs.randn(n, feat).astype(np.float32)).cuda().to(dtype)
     w = torch.from_numpy(rs.rand(len(src), 1).astype(np.float32)).cuda().to(dtype)
-    ws = ops.edge_scalars_to_slots(csr, w)
-    assert torch.equal(ws, w.reshape(-1)[csr.eids.long()])
+    ws = ops.edge_data_to_slots(csr, w)
+    assert torch.equal(ws.reshape(-1), w.reshape(-1)[csr.eids.long()])
     y0, _ = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w, w_width=1)
     dx0 = ops.spmm_backward_x(csr_t, x, w=w, w_width=1)
     monkeypatch.setattr(ops, "SLOT_ORDER_MIN_NNZ", 0)
@@ -318,3 +319,46 @@ def test_ragged_width_takes_padded_vector_path(feat, dtype):
         assert np.array_equal(arg.cpu().numpy().astype(np.int64), warg)
         dx = ops.spmm_backward_x(_csr(src, dst, n, transpose=True), xt, w=wt, w_width=1)
         _close(dx, oracle.spmm_grad(src, dst, n, x, w), rtol)
+
+
+@pytest.mark.parametrize("heads,dim", [(8, 8), (4, 32), (8, 3), (2, 4)])
+def test_multi_head_weights_max_bf16_gradient(heads, dim):
+    """(E, H, 1) weights against (N, H, D) features - the multi-head attention case
+    (python/dgl/function/message.py:75-91 rank alignment): max + argmax, bf16 storage and the
+    gradient wrt x, through the per-head chunk variant (D a multiple of the vector) and the
+    generic one (D = 3)."""
+    from dgl_b200 import ops
+    n, feat = 260, heads * dim
+    src, dst = random_graph(n, 4000, 13 + feat, hubs=2, hub_deg=600, zero_deg_frac=0.15)
+    E = len(src)
+    rng = np.random.RandomState(feat)
+    x = rng.randint(-3, 4, size=(n, feat)).astype(np.float32)
+    w = rng.randint(1, 4, size=(E, heads)).astype(np.float32)
+    csr, csr_t = _csr(src, dst, n), _csr(src, dst, n, transpose=True)
+    m = oracle.message("src_mul_edge", src, x.reshape(n, heads, dim), w.reshape(E, heads, 1)).reshape(E, feat)
+    xt, wt = torch.from_numpy(x).cuda(), torch.from_numpy(w).cuda()
+    want, warg = oracle.reduce_max(dst, m, n)
+    for chunk in (0, 64):
+        y, arg = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_MAX, x=xt, w=wt, w_width=heads,
+                          want_arg=True, chunk=chunk)
+        assert np.array_equal(y.cpu().numpy(), want)
+        assert np.array_equal(arg.cpu().numpy().astype(np.int64), warg)
+    # small integers are exact in bf16: the bf16 sum must equal the fp32 oracle after rounding
+    ys, _ = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=xt.bfloat16(), w=wt.bfloat16(), w_width=heads)
+    _close(ys, oracle.reduce_sum(dst, m, n), RTOL_BF16)
+    dy = rng.randn(n, feat).astype(np.float32)
+    want_dx = oracle.spmm_grad(src, dst, n, dy.reshape(n, heads, dim), w.reshape(E, heads, 1)).reshape(n, feat)
+    dx = ops.spmm_backward_x(csr_t, torch.from_numpy(dy).cuda(), w=wt, w_width=heads)
+    _close(dx, want_dx, RTOL_F32)
+    # large-graph form: per-head weights permuted to slot order, eids == NULL; same bits
+    y0, _ = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=xt, w=wt, w_width=heads)
+    assert torch.equal(ops.edge_data_to_slots(csr, wt), wt[csr.eids.long()])
+    assert torch.equal(ops.edge_data_to_slots(csr, wt.bfloat16()), wt.bfloat16()[csr.eids.long()])
+    old = ops.SLOT_ORDER_MIN_NNZ
+    ops.SLOT_ORDER_MIN_NNZ = 0
+    try:
+        y1, _ = ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=xt, w=wt, w_width=heads)
+        dx1 = ops.spmm_backward_x(csr_t, torch.from_numpy(dy).cuda(), w=wt, w_width=heads)
+    finally:
+        ops.SLOT_ORDER_MIN_NNZ = old
+    assert torch.equal(y0, y1) and torch.equal(dx, dx1)
