@@ -284,6 +284,7 @@ def run_b200(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
         torch.cuda.set_device(local)
+        os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")   # the stream-ordered barriers must not queue behind SpMM CTAs
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
@@ -399,6 +400,12 @@ def run_b200(args):
         torch.cuda.synchronize()
         k_avg_ms = sum(a.elapsed_time(b) for a, b in kev) / len(kev)
     xchg_ms = max(0.0, op_ms - k_avg_ms)
+    k_ranks = None
+    if world > 1:          # per-rank kernel time: the spread is what the barriers of the exchange wait for
+        mine = torch.tensor([k_avg_ms], device=dev, dtype=torch.float64)
+        allk = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allk, mine)
+        k_ranks = [round(float(t[0]), 3) for t in allk]
     loc_e = (loc_in.nnz + loc_out.nnz) / 2.0
     alg_launch = graphs.spmm_alg_bytes(loc_e, rows, feat)
     peak, peak_kind = measured_peak()
@@ -441,6 +448,15 @@ def run_b200(args):
         check_ref = None
         torch.cuda.empty_cache()
     xchg_bytes = part.exchange_bytes(feat)
+    transfer = None
+    if exchange == "halo" and world > 1 and part.halo_in.timing:
+        # DGL_B200_TIMING=1: the transfers alone (between the barriers), per rank
+        torch.cuda.synchronize()
+        tm = [a.elapsed_time(b) for h in (part.halo_in, part.halo_out) for a, b in h.timing[-2 * args.steps:]]
+        mine = torch.tensor([sum(tm) / len(tm), float(xchg_bytes)], device=dev, dtype=torch.float64)
+        allr = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        transfer = [{"ms": round(float(t[0]), 3), "GBps_in": round(float(t[1]) / float(t[0]) / 1e6, 1)} for t in allr]
     del x_loc, dy_loc, y_loc, dx_loc
     part._full.clear()
     if exchange == "halo":
@@ -580,7 +596,7 @@ def run_b200(args):
                            world, "NVLink peer-load" if (args.transport == "peer" and world > 1) else "NCCL",
                            "compacted halo" if exchange == "halo" else "all-gather halo"),
                        "exchange_bytes_per_rank_per_spmm": xchg_bytes,
-                       "op_ms_rank0": op_ms, "exposed_exchange_ms_rank0": xchg_ms,
+                       "op_ms_rank0": op_ms, "exposed_exchange_ms_rank0": xchg_ms, "transfer_per_rank": transfer, "kernel_ms_per_rank": k_ranks,
                        "graph_build_s": round(t_build, 2)},
             "edge_feat_per_s": 2 * e * feat / (ms_step * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,

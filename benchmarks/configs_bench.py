@@ -116,6 +116,69 @@ def c4():
     report("C4", "spmm copy_src->max + argmax F=16", ms, graphs.spmm_alg_bytes(e, n, hid) + n * hid * 4, n=n, e=e)
 
 
+def c4_per_relation():
+    """C4 also as 90 per-relation src_mul_edge->sum launches (the reference's R-GCN loops
+    over relations in Python: examples/pytorch/rgcn/layers.py) against the one batched launch."""
+    c = graphs.C4_AIFB
+    n, hid, rels = c["n"], c["hidden"], c["rels"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], DEV)
+    e = src.shape[0]
+    g = torch.Generator(device=DEV)
+    g.manual_seed(c["seed"])
+    rel = torch.randint(0, rels, (e,), device=DEV, generator=g)
+    x = torch.randn(n, hid, device=DEV)
+    w = torch.rand(e, 1, device=DEV)
+    subs = []
+    for r in range(rels):
+        m = rel == r
+        subs.append((ops.csr_build(dst[m], src[m], n, n), w[m].contiguous()))
+
+    def per_relation():
+        acc = torch.zeros(n, hid, device=DEV)
+        for csr, wr in subs:
+            acc += ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=wr, w_width=1)[0]
+        return acc
+    ms = timeit(per_relation)
+    report("C4", "90 per-relation src_mul_edge->sum launches + accumulate", ms,
+           graphs.spmm_alg_bytes(e, n, hid, weights=True) + 2 * rels * n * hid * 4, n=n, e=e)
+    cin = ops.csr_build(dst, src, n, n)
+    ms = timeit(lambda: ops.spmm(cin, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w, w_width=1))
+    report("C4", "the same as ONE batched launch", ms, graphs.spmm_alg_bytes(e, n, hid, weights=True), n=n, e=e)
+    got = ops.spmm(cin, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=x, w=w, w_width=1)[0]
+    want = per_relation()
+    assert torch.allclose(got, want, rtol=1e-4, atol=1e-4), "batched != per-relation"
+
+
+def c2_torch_sparse():
+    """'Reference on GPU' row (optional): the reference's own GPU path is th.sparse.mm on
+    the uncoalesced COO it builds in edge-id order (python/dgl/backend/pytorch/tensor.py:45-51,146).
+    Library call timed beside the engine on the same graph and features; forward and fwd+bwd."""
+    c = graphs.C2_REDDIT
+    n, e = c["n"], c["e"]
+    src, dst = graphs.powerlaw_symmetric(n, e, c["seed"], DEV)
+    idx = torch.stack([dst, src])
+    del src, dst
+    adj = torch.sparse_coo_tensor(idx, torch.ones(e, device=DEV), (n, n))
+    x = torch.randn(n, 256, device=DEV, requires_grad=True)
+    dy = torch.randn(n, 256, device=DEV)
+    alg = graphs.spmm_alg_bytes(e, n, 256)
+    try:
+        ms = timeit(lambda: torch.sparse.mm(adj, x.detach()), warm=2, iters=5)
+        report("C2", "REFERENCE ON GPU: th.sparse.mm(uncoalesced COO) forward F=256", ms, alg, n=n, e=e)
+
+        def fb():
+            y = torch.sparse.mm(adj, x)
+            y.backward(dy)
+            x.grad = None
+        ms = timeit(fb, warm=2, iters=5)
+        report("C2", "REFERENCE ON GPU: th.sparse.mm fwd + autograd bwd F=256", ms, 2 * alg, n=n, e=e)
+        adj_c = adj.coalesce()
+        ms = timeit(lambda: torch.sparse.mm(adj_c, x.detach()), warm=2, iters=5)
+        report("C2", "th.sparse.mm(pre-coalesced COO) forward F=256", ms, alg, n=n, e=e)
+    except RuntimeError as err:      # e.g. out of memory inside the library's coalesce
+        report("C2", "REFERENCE ON GPU: th.sparse.mm failed: %s" % str(err)[:80], float("nan"), 0, n=n, e=e)
+
+
 def c2_structure():
     c = graphs.C2_REDDIT
     n, e = c["n"], c["e"]
@@ -155,7 +218,7 @@ def c2_structure():
 
 
 if __name__ == "__main__":
-    sections = dict(c1=c1, c3=c3, c4=c4, c2=c2_structure)
+    sections = dict(c1=c1, c3=c3, c4=c4, c4rel=c4_per_relation, c2=c2_structure, c2ref=c2_torch_sparse)
     for name in (sys.argv[1:] or list(sections)):
         sections[name]()
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)

@@ -138,6 +138,7 @@ static int pick_slab_chunks(int64_t x_rows, int64_t nnz, size_t row_bytes) {
 
 static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_plan_t* plan,
                     int64_t x_rows, int64_t nnz, cudaStream_t stream) {
+  a.nnz = nnz;
   a.chunk = 1 << 30;
   a.n_long_rows = 0;
   a.n_chunks = 0;
@@ -235,6 +236,7 @@ int dglb200_set_tuning(const char* key, int64_t value) {
   if (k == "spmm_ucap") t.ucap = (int)value;
   else if (k == "spmm_slab_chunks") t.slab_chunks = (int)value;
   else if (k == "spmm_threads") t.threads = (int)value;
+  else if (k == "spmm_rows_per_group") t.rows_per_group = (int)value;
   else {
     set_error("set_tuning: unknown key '%s'", key);
     return -1;

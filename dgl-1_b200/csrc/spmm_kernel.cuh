@@ -59,6 +59,8 @@ struct SpmmArgs {
   int64_t y_ld;            // leading dimension (elements) of y rows
   int y_vec;               // y rows take 16-byte stores (base and y_ld aligned)
   int w_slab_scalar;       // per-head weights, every feature pass inside one head: scalar variant
+  int64_t nnz;
+  int rows_per_group;      // consecutive row steps a group walks (launch_one; >= 1)
 };
 
 constexpr int kSpmmThreads = 128;  // measured: 128 > 256 > 512 on C2 at every slab width
@@ -85,9 +87,16 @@ struct SpmmStage {
 //  kWmAny     decided at run time (element-wise weights, ragged heads, the masked gradient).
 enum { kWmAny = 0, kWmScalar = 1, kWmChunk = 2 };
 
+// copy_src -> sum is held to 64 registers (8 CTAs of 128 threads per SM: its occupancy on the
+// headline workload); the other variants take what they need.
+constexpr int spmm_min_blocks(int msg, int red, int nt, int tiles, int elem_bytes) {
+  return (msg == DGLB200_MSG_COPY_SRC && red == DGLB200_RED_SUM && tiles == 1 && elem_bytes == 4)
+             ? 1024 / nt : 1;
+}
+
 template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads,
           int WM = kWmAny>
-__global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
+__global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)sizeof(T))) spmm_kernel(const SpmmArgs a) {
   constexpr bool WS = (WM == kWmScalar);
   constexpr bool CW = (WM == kWmChunk);
   constexpr int RPW = 32 / G;  // items per warp
@@ -117,6 +126,12 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
   const int64_t gw = (int64_t)blockIdx.x * (NT / 32) + (threadIdx.x >> 5);
   const int64_t fbase = (int64_t)blockIdx.y * (G * TILES * VEC);
 
+  // Sparse graphs (C5: mean degree 3, 75 % of the rows empty) are bound by CTA launch rate when a
+  // warp retires after one short row (measured: an empty row cost as much as 3.65 edges), so a
+  // group then walks `rows_per_group` rows; at every step the warp covers RPW consecutive rows.
+  const int n_items = gw < a.n_chunk_warps ? 1 : a.rows_per_group;
+#pragma unroll 1
+  for (int item_i = 0; item_i < n_items; ++item_i) {
   // ---- which item does this group own? ------------------------------------------------
   int64_t start = 0, end = 0, out_row = -1;
   bool to_partial = false;
@@ -136,7 +151,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
       to_partial = true;
     }
   } else {
-    const int64_t row = (gw - a.n_chunk_warps) * RPW + grp;
+    const int64_t row = ((gw - a.n_chunk_warps) * a.rows_per_group + item_i) * RPW + grp;
     if (row < a.n_rows) {
       start = a.indptr[row];
       end = a.indptr[row + 1];
@@ -341,7 +356,7 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
   run_blocks(std::false_type{}, full_blk, nblk);
 
   // ---- epilogue ---------------------------------------------------------------------------
-  if (out_row < 0) return;
+  if (out_row < 0) continue;
   if constexpr (kMax) {
     // No message beat -inf: an empty item yields 0 (the reference leaves zero-degree rows at the
     // frame initializer's 0), a non-empty one is all -inf and its argmax is the first slot.
@@ -401,7 +416,18 @@ __global__ void __launch_bounds__(NT) spmm_kernel(const SpmmArgs a) {
       }
     }
   }
+  }  // item loop
 }
+
+// Tuning knobs (dglb200_set_tuning): only the fp32 vector copy_src->sum kernel, the one the
+// headline benchmark times, is instantiated in several shapes.
+struct SpmmTuning {
+  int ucap = 0;         // edges per pipeline stage (0 = auto)
+  int slab_chunks = 0;  // 16-byte chunks of a row per pass: 16, 32 or 64 (0 = auto)
+  int threads = 0;      // CTA size: 128, 256 or 512 (0 = auto)
+  int rows_per_group = 0;  // row steps per group (0 = auto from the mean degree)
+};
+SpmmTuning& spmm_tuning();
 
 // ---- dispatch over (G, TILES, MSG, RED) for one storage type -----------------------------------
 
@@ -411,7 +437,14 @@ int launch_one(const SpmmArgs& a, cudaStream_t stream) {
   constexpr int RPW = 32 / G;
   SpmmArgs args = a;
   args.n_chunk_warps = ceil_div(a.n_chunks, RPW);
-  const int64_t warps = args.n_chunk_warps + ceil_div(a.n_rows, RPW);
+  // rows per group: amortise the CTA launch over ~64 edges of work, but keep >= 32 warps per SM
+  const int64_t row_warps = ceil_div(a.n_rows, RPW);
+  const int64_t avg_deg = a.n_rows > 0 ? a.nnz / a.n_rows : 0;
+  int rpg = avg_deg >= 32 ? 1 : (avg_deg >= 16 ? 2 : (avg_deg >= 8 ? 4 : (avg_deg >= 4 ? 8 : 16)));
+  if (spmm_tuning().rows_per_group > 0) rpg = spmm_tuning().rows_per_group;
+  while (rpg > 1 && row_warps / rpg < 148 * 32) rpg >>= 1;
+  args.rows_per_group = rpg;
+  const int64_t warps = args.n_chunk_warps + ceil_div(row_warps, rpg);
   const int64_t blocks = ceil_div(warps, NT / 32);
   const int64_t slabs = ceil_div(ceil_div(a.feat, VEC), (int64_t)G * TILES);
   DGLB200_REQUIRE(blocks < (1ll << 31) && slabs < 65536, "spmm: grid too large (%lld x %lld)",
@@ -423,14 +456,6 @@ int launch_one(const SpmmArgs& a, cudaStream_t stream) {
   return 0;
 }
 
-// Tuning knobs (dglb200_set_tuning): only the fp32 vector copy_src->sum kernel, the one the
-// headline benchmark times, is instantiated in several shapes.
-struct SpmmTuning {
-  int ucap = 0;         // edges per pipeline stage (0 = auto)
-  int slab_chunks = 0;  // 16-byte chunks of a row per pass: 16, 32 or 64 (0 = auto)
-  int threads = 0;      // CTA size: 128, 256 or 512 (0 = auto)
-};
-SpmmTuning& spmm_tuning();
 
 template <typename T, int VEC, int MSG, int RED>
 int launch_tuned(const SpmmArgs& a, cudaStream_t stream, bool* handled) {

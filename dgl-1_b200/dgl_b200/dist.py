@@ -23,12 +23,14 @@ from . import ops
 # full grid: 660 GB/s; 8 ranks all-to-all: full grid 450 GB/s, 256 CTAs 260 GB/s), so bounding the grid
 # to co-schedule the SpMM loses more than the overlap wins: the pipelined paths below (row chunks /
 # feature slabs on a side stream) are kept selectable but are OFF by default
-PULL_CTAS = 0
+PULL_CTAS = int(os.environ.get("DGL_B200_PULL_CTAS", "0"))
 # weight of a row relative to an edge in the partition balance (2 SpMMs per step write every row once)
 ROW_WEIGHT = float(os.environ.get("DGL_B200_ROW_WEIGHT", "2.0"))
-# halo pull: one fused launch over all owners ("fused") or one launch per owner in a rotating order
-# so that every owner serves exactly one puller at a time ("perpeer")
+# halo transport over the mapped peer buffers: "perpeer" = one PULL launch per owner in a rotating order
+# (every owner serves exactly one puller at a time), "fused" = one pull launch over all owners, "push" =
+# the owner gathers and STORES into the requester's buffer (posted NVLink writes)
 PULL_MODE = os.environ.get("DGL_B200_PULL", "perpeer")   # measured, C5 x 8 ranks: perpeer 14.7 ms/step, fused 18.4
+TIMING = bool(int(os.environ.get("DGL_B200_TIMING", "0")))   # record events around the halo transfers
 COMM_PRIORITY = -1      # side stream of the pulls: higher priority than the compute stream
 
 
@@ -365,7 +367,15 @@ class HaloExchange(object):
             self.send_counts.append(sc)
             self.need_cat.append(need_cat.contiguous())
             self.serve_local.append(serve.contiguous())           # already local ids of THIS rank
+        # push transport: where the rows I serve land inside requester r's compact buffer, per chunk
+        self.push_dst = None
+        if world > 1:
+            objs = [None] * world
+            dist.all_gather_object(objs, (self.chunk_start, self.recv_counts), group=group)
+            self.push_dst = [[int(objs[r][0][k] + sum(objs[r][1][k][:rank])) for r in range(world)]
+                             for k in range(self.chunks)]
         self.chunk_csr = None
+        self.timing = []
         self._buf = None
         self._peer_buf = None
         self._barrier = None
@@ -403,6 +413,21 @@ class HaloExchange(object):
         """Bring chunk k's halo rows into buf (current stream)."""
         start = self.chunk_start[k]
         cnts = self.recv_counts[k]
+        if self._peer_buf is not None and PULL_MODE == "push":
+            # owner-side: gather the rows each requester needs out of my block and STORE them straight
+            # into its compact buffer over NVLink (posted writes, no request round trip); rotating
+            # order so that every requester is written by one owner at a time
+            sc = self.send_counts[k]
+            seg = [0]
+            for r in range(self.world):
+                seg.append(seg[-1] + sc[r])
+            for j in range(1, self.world):
+                r = (self.rank + j) % self.world
+                if sc[r]:
+                    d0 = self.push_dst[k][r]
+                    ops.gather_rows(buf[:self.rows], self.serve_local[k][seg[r]:seg[r + 1]],
+                                    out=self._peer_buf[r][d0:d0 + sc[r]], max_ctas=PULL_CTAS)
+            return
         if self._peer_buf is not None:
             # one launch pulls this chunk's rows from every owner at once (NVLink peer loads)
             seg = [0]
@@ -433,8 +458,14 @@ class HaloExchange(object):
             return buf
         if self._barrier is not None:
             self._barrier()
+        if TIMING and x_local.is_cuda:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
         for k in range(self.chunks):
             self._fetch_chunk(k, buf)
+        if TIMING and x_local.is_cuda:
+            b.record()
+            self.timing.append((a, b))
         if self._barrier is not None:
             self._barrier()
         return buf
@@ -444,6 +475,8 @@ class HaloExchange(object):
         flight on the side stream.  `out` [rows, feat] must be given."""
         if self.world == 1 or self.chunks == 1:
             return spmm_fn(self.csr, self.exchange(x_local), out)
+        if self._peer_buf is not None and PULL_MODE == "push":
+            return self._aggregate_pushed(x_local, spmm_fn, out)
         buf = self.buffer(x_local.shape[1], x_local)
         own = buf[:self.rows]
         if own.data_ptr() != x_local.data_ptr():
@@ -475,6 +508,42 @@ class HaloExchange(object):
                 spmm_fn(csr_k, buf, out[self.row_cuts[k]:self.row_cuts[k + 1]])
         if self._barrier is not None:
             self._barrier()                                       # nobody overwrites rows still being read
+        return out
+
+
+    def _aggregate_pushed(self, x_local, spmm_fn, out):
+        """Pipelined PUSH exchange + SpMM.  A push is local loads + posted NVLink stores, so (unlike
+        a pull, which needs the whole GPU's loads in flight to cover the NVLink round trip) a small
+        grid keeps the link busy and the SpMM of the previous row chunk keeps the other SMs.  A
+        pushed chunk is complete on the receiver only when EVERY owner has stored its share: one
+        stream-ordered barrier per chunk on the side stream."""
+        buf = self.buffer(x_local.shape[1], x_local)
+        own = buf[:self.rows]
+        if own.data_ptr() != x_local.data_ptr():
+            own.copy_(x_local)
+        if self._comm is None:
+            self._comm = torch.cuda.Stream(device=x_local.device, priority=COMM_PRIORITY)
+        cur = torch.cuda.current_stream(x_local.device)
+        self._barrier()                       # every rank's previous SpMM has finished reading its buffer
+        self._comm.wait_stream(cur)
+        events = []
+        with torch.cuda.stream(self._comm):
+            for k in range(self.chunks):
+                if TIMING:
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                self._fetch_chunk(k, buf)
+                if TIMING:
+                    b.record()
+                    self.timing.append((a, b))
+                self._barrier()               # chunk k's halo has landed everywhere
+                ev = torch.cuda.Event()
+                ev.record(self._comm)
+                events.append(ev)
+        for k, csr_k in enumerate(self.row_chunks()):
+            cur.wait_event(events[k])
+            if csr_k.n_rows:
+                spmm_fn(csr_k, buf, out[self.row_cuts[k]:self.row_cuts[k + 1]])
         return out
 
 

@@ -49,6 +49,14 @@ def _worker(rank, world, port, n, e, feat, q, halo=False, chunks=1):
             part = HaloPartition(_csr_cpu(src, dst, n, False), _csr_cpu(src, dst, n, True),
                                  spmm_fn=_oracle_block_spmm, gather_fn=lambda x, idx: x[idx], chunks=chunks)
             assert part.halo_in.n_halo <= n - part.rows
+            for h in (part.halo_in, part.halo_out):          # push plan: my rows' slot in every requester
+                exp = [[h.chunk_start[k] + sum(h.recv_counts[k][:q]) for q in range(world)]
+                       for k in range(h.chunks)]
+                allexp = [None] * world
+                dist.all_gather_object(allexp, exp)
+                for k in range(h.chunks):
+                    assert h.push_dst[k] == [allexp[r][k][rank] for r in range(world)]
+                    assert sum(h.send_counts[k]) == h.serve_local[k].numel()
         else:
             part = RowPartition(_csr_cpu(src, dst, n, False), _csr_cpu(src, dst, n, True),
                                 spmm_fn=_oracle_block_spmm)
