@@ -186,6 +186,11 @@ class GCNModel(object):
         return loss
 
 
+def b200dist_mode():
+    from dgl_b200 import dist as b200dist
+    return b200dist.PULL_MODE
+
+
 def gcn_dims(cfg):
     c = graphs.C2_REDDIT
     return c["feat_in"], cfg["feat"], c["classes"]
@@ -310,7 +315,8 @@ def run_b200(args):
     if exchange == "auto":   # compacted halo pays when rows are referenced rarely (C5: mean degree 3)
         exchange = "halo" if (world > 1 and e < 16 * n) else "allgather"
     if exchange == "halo":
-        part = HaloPartition(csr_in, csr_out, rank=rank, world=world, chunks=args.chunks)
+        chunks = args.chunks or (4 if args.transport == "peer" else 1)
+        part = HaloPartition(csr_in, csr_out, rank=rank, world=world, chunks=chunks)
     else:
         part = RowPartition(csr_in, csr_out, rank=rank, world=world)
     bounds, r0, r1, rows = part.bounds, part.r0, part.r1, part.rows
@@ -593,8 +599,10 @@ def run_b200(args):
                        "l2": "inputs_exceed_l2 (X %.0f MB + structure %.0f MB per SpMM; no flush)"
                              % (n * feat * 4 / 1e6, e * 4 / 1e6),
                        "parallelism": "row-partition x%d + %s %s" % (
-                           world, "NVLink peer-load" if (args.transport == "peer" and world > 1) else "NCCL",
-                           "compacted halo" if exchange == "halo" else "all-gather halo"),
+                           world, ("NVLink peer " + (b200dist_mode() if exchange == "halo" else "block copies"))
+                           if (args.transport == "peer" and world > 1) else "NCCL",
+                           ("compacted halo, %d row chunks" % part.halo_in.chunks) if exchange == "halo"
+                           else "all-gather halo"),
                        "exchange_bytes_per_rank_per_spmm": xchg_bytes,
                        "op_ms_rank0": op_ms, "exposed_exchange_ms_rank0": xchg_ms, "transfer_per_rank": transfer, "kernel_ms_per_rank": k_ranks,
                        "graph_build_s": round(t_build, 2)},
@@ -618,8 +626,9 @@ def main():
     ap.add_argument("--exchange", default="auto", choices=["auto", "allgather", "halo"])
     ap.add_argument("--transport", default="peer", choices=["nccl", "peer"],
                     help="N>1 data path: NCCL collectives, or peer loads over NVLink from IPC-mapped buffers")
-    ap.add_argument("--chunks", type=int, default=1,
-                    help="row chunks of the pipelined halo exchange (1 = unpipelined; measured faster)")
+    ap.add_argument("--chunks", type=int, default=0,
+                    help="row chunks of the pipelined halo exchange (0 = auto: 4 with the peer transport, "
+                         "whose pushes run beside the SpMM of the previous chunk; 1 = unpipelined)")
     ap.add_argument("--check", action="store_true", help="N>1: verify the exchange against the all-gather path")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")

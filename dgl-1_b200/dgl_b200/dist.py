@@ -25,11 +25,14 @@ from . import ops
 # feature slabs on a side stream) are kept selectable but are OFF by default
 PULL_CTAS = int(os.environ.get("DGL_B200_PULL_CTAS", "0"))
 # weight of a row relative to an edge in the partition balance (2 SpMMs per step write every row once)
-ROW_WEIGHT = float(os.environ.get("DGL_B200_ROW_WEIGHT", "2.0"))
+ROW_WEIGHT = float(os.environ.get("DGL_B200_ROW_WEIGHT", "4.0"))
 # halo transport over the mapped peer buffers: "perpeer" = one PULL launch per owner in a rotating order
 # (every owner serves exactly one puller at a time), "fused" = one pull launch over all owners, "push" =
 # the owner gathers and STORES into the requester's buffer (posted NVLink writes)
-PULL_MODE = os.environ.get("DGL_B200_PULL", "perpeer")   # measured, C5 x 8 ranks: perpeer 14.7 ms/step, fused 18.4
+# measured, C5 x 8 ranks (ms/step): perpeer 14.8, fused 18.4, push 14.5; x 2 ranks: push 26.6, push pipelined
+# in 4 row chunks with a 128-CTA push grid 24.7
+PULL_MODE = os.environ.get("DGL_B200_PULL", "push")
+PUSH_CTAS_PIPELINED = 128   # grid of a push that runs beside the SpMM of the previous row chunk
 TIMING = bool(int(os.environ.get("DGL_B200_TIMING", "0")))   # record events around the halo transfers
 COMM_PRIORITY = -1      # side stream of the pulls: higher priority than the compute stream
 
@@ -421,12 +424,13 @@ class HaloExchange(object):
             seg = [0]
             for r in range(self.world):
                 seg.append(seg[-1] + sc[r])
+            ctas = PULL_CTAS or (PUSH_CTAS_PIPELINED if self.chunks > 1 else 0)
             for j in range(1, self.world):
                 r = (self.rank + j) % self.world
                 if sc[r]:
                     d0 = self.push_dst[k][r]
                     ops.gather_rows(buf[:self.rows], self.serve_local[k][seg[r]:seg[r + 1]],
-                                    out=self._peer_buf[r][d0:d0 + sc[r]], max_ctas=PULL_CTAS)
+                                    out=self._peer_buf[r][d0:d0 + sc[r]], max_ctas=ctas)
             return
         if self._peer_buf is not None:
             # one launch pulls this chunk's rows from every owner at once (NVLink peer loads)
