@@ -1,0 +1,60 @@
+"""-m "not gpu": the HOST layer (DGLGraph entry points, scheduler, plans, write-back, autograd
+wiring) against the golden vectors of the unmodified reference, with the kernel-launching functions
+of dgl_b200.ops swapped for the CPU restatements of tests/cpu_engine.py.
+
+The bodies are the `-m gpu` tests of tests/test_gpu_graph_api.py, run unchanged: only the device of
+the tensors and the engine behind `ops` differ.  This checks everything above the C ABI in a
+container without a GPU; the kernels themselves are checked by the `-m gpu` suite on the B200.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from tests import cpu_engine
+from tests import test_gpu_graph_api as api
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+CASES = sorted(glob.glob(os.path.join(GOLDEN, "case_*.npz")))
+
+BODIES = [api.test_adjacency_and_degrees_bit_exact, api.test_update_all_every_builtin_pair,
+          api.test_max_bit_exact, api.test_gradients, api.test_send_and_recv_pull_push,
+          api.test_udf_fallbacks_equal_builtins, api.test_degree_bucketing_vs_reference]
+
+
+def _cpu_graph(case, extra_loops=False):
+    import dgl_b200
+    n, src, dst = int(case["n"]), case["src"], case["dst"]
+    if extra_loops:
+        src = np.concatenate([src, np.arange(n)])
+        dst = np.concatenate([dst, np.arange(n)])
+    g = dgl_b200.DGLGraph()
+    g.add_nodes(n)
+    g.add_edges(torch.from_numpy(src), torch.from_numpy(dst))
+    return g.to("cpu")
+
+
+@pytest.fixture()
+def cpu_api(monkeypatch):
+    monkeypatch.setattr(api, "cu", lambda a: torch.from_numpy(np.ascontiguousarray(a)))
+    monkeypatch.setattr(api, "graph", _cpu_graph)
+    with cpu_engine.installed():
+        yield api
+
+
+@pytest.mark.parametrize("body", BODIES, ids=[b.__name__ for b in BODIES])
+@pytest.mark.parametrize("path", CASES[:2], ids=[os.path.basename(c) for c in CASES[:2]])
+def test_host_layer_against_reference_golden(cpu_api, path, body):
+    body(dict(np.load(path)))
+
+
+def test_cpu_engine_is_not_left_installed():
+    """Outside the context manager the product has no CPU path."""
+    from dgl_b200 import ops
+    from dgl_b200.base import DGLError
+    with cpu_engine.installed():
+        pass
+    with pytest.raises(DGLError):
+        ops.csr_build(torch.zeros(3, dtype=torch.int64), torch.zeros(3, dtype=torch.int64), 4, 4)
