@@ -14,6 +14,7 @@ import torch
 from . import ops
 from .autograd import Adjacency
 from .base import ALL, DGLError, is_all
+from .init import zero_initializer
 
 
 class FeatureDict(dict):
@@ -23,6 +24,23 @@ class FeatureDict(dict):
         super(FeatureDict, self).__init__()
         self._num_rows_fn = num_rows_fn
         self._kind = kind
+        self._initializers = {}
+        self._default_initializer = zero_initializer
+
+    def set_initializer(self, initializer, column=None):
+        """Frame.set_initializer (python/dgl/frame.py:240-256)."""
+        if column is None:
+            self._default_initializer = initializer
+        else:
+            self._initializers[column] = initializer
+
+    def get_initializer(self, column=None):
+        """Frame.get_initializer (python/dgl/frame.py:225-238); the default is the zero
+        initializer the reference falls back to (frame.py:219-223)."""
+        return self._initializers.get(column, self._default_initializer)
+
+    def num_rows(self):
+        return self._num_rows_fn()
 
     def __setitem__(self, key, val):
         if not torch.is_tensor(val):
@@ -57,6 +75,9 @@ class DGLGraph(object):
         self._readonly = readonly
         self.ndata = FeatureDict(self.number_of_nodes, "node")
         self.edata = FeatureDict(self.number_of_edges, "edge")
+        # message frame + per-edge "has a pending message" flag (graph.py:191-196 in the reference)
+        self._msg = FeatureDict(self.number_of_edges, "message")
+        self._msg_index = None
         self._message_func = None
         self._reduce_func = None
         self._apply_node_func = None
@@ -92,6 +113,7 @@ class DGLGraph(object):
         if u.is_cuda:
             self._device = u.device
         self.clear_cache()
+        self._reset_messages()
 
     def to(self, device):
         """Move the structure to `device` (features are moved by the user, as in the reference)."""
@@ -101,6 +123,7 @@ class DGLGraph(object):
             self._src = self._src.to(device)
             self._dst = self._dst.to(device)
         self.clear_cache()
+        self._reset_messages()
         return self
 
     def number_of_nodes(self):
@@ -115,6 +138,26 @@ class DGLGraph(object):
     def clear_cache(self):
         """Drop the cached device CSRs (GraphIndex.clear_cache, graph_index.py:113-115)."""
         self._adj = None
+
+    def _reset_messages(self):
+        """Structure changed: pending messages are dropped (the reference appends zero rows to
+        _msg_index / _msg_frame on add_edges, graph.py:308-309,368-369; here the flags restart)."""
+        self._msg.clear()
+        self._msg_index = None
+
+    def msg_index(self):
+        """int8[E] device flags: 1 = the edge holds a message that no recv has consumed."""
+        if self._msg_index is None or self._msg_index.shape[0] != self._e:
+            self._msg_index = torch.zeros(self._e, dtype=torch.int8, device=self._need_device())
+        return self._msg_index
+
+    def set_n_initializer(self, initializer, field=None):
+        """python/dgl/graph.py:1590-1618."""
+        self.ndata.set_initializer(initializer, field)
+
+    def set_e_initializer(self, initializer, field=None):
+        """python/dgl/graph.py:1620-1648."""
+        self.edata.set_initializer(initializer, field)
 
     def _need_device(self):
         if self._device is None or self._device.type != "cuda":
@@ -263,6 +306,49 @@ class DGLGraph(object):
         from . import scheduler
         m, r, a = self._defaults(message_func, reduce_func, apply_node_func)
         self._run(lambda prog: scheduler.schedule_update_all(prog, self, m, r, a))
+
+    def _resolve_edges(self, edges):
+        """(u, v, eid) of an edge specification: ALL, a (u, v) pair (every parallel edge between
+        the pairs, Graph::EdgeIds) or an edge-id container (graph.py:1962-1974)."""
+        if is_all(edges):
+            u, v = self.edges()
+            return u, v, None
+        if isinstance(edges, tuple):
+            return self.edge_ids(edges[0], edges[1])
+        return self.find_edges(edges)
+
+    def send(self, edges=ALL, message_func="default"):
+        """python/dgl/graph.py:1926-1985: compute messages on `edges` and park them in the message
+        frame until a recv consumes them; a later send on the same edge overwrites."""
+        from . import scheduler
+        if message_func == "default":
+            message_func = self._message_func
+        assert message_func is not None
+        self._need_device()
+        u, v, eid = self._resolve_edges(edges)
+        if eid is not None and eid.numel() == 0:
+            return   # no edge to be triggered
+        if self._e == 0:
+            return
+        self._run(lambda prog: scheduler.schedule_send(prog, self, u, v, eid, message_func))
+
+    def recv(self, v=ALL, reduce_func="default", apply_node_func="default", inplace=False):
+        """python/dgl/graph.py:1987-2087: reduce the pending messages on the in-edges of `v`
+        (consuming them), then apply."""
+        from . import scheduler
+        if reduce_func == "default":
+            reduce_func = self._reduce_func
+        if apply_node_func == "default":
+            apply_node_func = self._apply_node_func
+        assert reduce_func is not None
+        dev = self._need_device()
+        if is_all(v):
+            v = torch.arange(self._n, dtype=torch.int64, device=dev)
+        v = _as_ids(v, dev)
+        if v.numel() == 0:
+            return   # no vertex to be triggered
+        self._run(lambda prog: scheduler.schedule_recv(prog, self, v, reduce_func, apply_node_func,
+                                                       inplace))
 
     def send_and_recv(self, edges, message_func="default", reduce_func="default",
                       apply_node_func="default", inplace=False):

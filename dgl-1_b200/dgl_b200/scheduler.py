@@ -1,7 +1,8 @@
 """Scheduler: lowers a message-passing call to an executor plan (plan.Prog).
 
 Mirrors python/dgl/runtime/scheduler.py (schedule_update_all :158-198, schedule_snr :111-156,
-schedule_pull :309-361, schedule_apply_nodes :200-232, schedule_apply_edges :234-277,
+schedule_pull :309-361, schedule_send :28-56, schedule_recv :58-109, _gen_reduce :428-468,
+schedule_apply_nodes :200-232, schedule_apply_edges :234-277,
 _gen_send_reduce :470-570, _apply_with_accum :398-426) and python/dgl/runtime/spmv.py
 (analyze_v2v_spmv :11-55, gen_v2v_spmv_schedule :83-113, gen_e2v_spmv_schedule :115-132) with the
 same op names, the same variable numbering and the same output guarantee: reduced features are
@@ -23,6 +24,7 @@ from . import ops
 from .autograd import Adjacency, aggregate
 from .base import DGLError
 from .function import BuiltinFunction, BundledFunction
+from .init import zero_initializer
 from .udf import EdgeBatch, NodeBatch
 
 _MSG_CODE = {"copy_src": ops.MSG_COPY_SRC, "src_mul_edge": ops.MSG_SRC_MUL_EDGE,
@@ -81,8 +83,10 @@ def _write_rows(d, idx, new, total_rows, inplace):
             d[k] = v
             continue
         if k not in d:
-            # new column: rows that are not written come from the zero initializer (init.py:47-61)
-            base = torch.zeros((total_rows,) + tuple(v.shape[1:]), dtype=v.dtype, device=v.device)
+            # new column: rows that are not written come from the column's initializer, zero unless
+            # the user set one (Frame.add_column, frame.py:317-337; init.py:47-61)
+            init = d.get_initializer(k) if hasattr(d, "get_initializer") else zero_initializer
+            base = init((total_rows,) + tuple(v.shape[1:]), v.dtype, v.device, slice(0, total_rows))
             d[k] = base.index_copy(0, idx, v) if not inplace else base.index_copy_(0, idx, v)
         elif inplace:
             d[k].index_copy_(0, idx, v)
@@ -209,11 +213,13 @@ def _gen_send(prog, g, var_nf, var_ef, var_u, var_v, var_eid, mfunc):
                       [prog.var("func", wrapper), fdsrc, fdedge, fddst], "dict")
 
 
-def gen_degree_bucketing_schedule(prog, g, rfunc, vids, recv_nodes, var_nf, var_mf, var_out):
+def gen_degree_bucketing_schedule(prog, g, rfunc, vids, recv_nodes, var_nf, var_mf, var_out, mids=None):
     """gen_degree_bucketing_schedule (runtime/degree_bucketing.py:13-84) with the bucket arrays
-    from kernel (4b) in canonical order.  Message ids are 0..M-1 (scheduler.py:566)."""
+    from kernel (4b) in canonical order.  Message ids are 0..M-1 for messages materialised by the
+    same call (scheduler.py:566) and the edge ids for messages parked by send (scheduler.py:466)."""
     n_msg = int(vids.shape[0])
-    mids = torch.arange(n_msg, dtype=torch.int64, device=vids.device)
+    if mids is None:
+        mids = torch.arange(n_msg, dtype=torch.int64, device=vids.device)
     degs, nids, nsec, bmids, msec = ops.degree_bucketing(mids, vids, recv_nodes, g.number_of_nodes())
     degs = degs.tolist()
     node_bkts = list(torch.split(nids, nsec.tolist()))
@@ -239,8 +245,10 @@ def gen_degree_bucketing_schedule(prog, g, rfunc, vids, recv_nodes, var_nf, var_
     if zero_nodes is not None:
         v0 = prog.var("idx", zero_nodes)
 
-        def new_dict(_out, idx, scheme):   # NewDictExecutor (ir/executor.py:765-778): zero initializer
-            return {k: torch.zeros((idx.shape[0],) + tuple(v.shape[1:]), dtype=v.dtype, device=v.device)
+        def new_dict(_out, idx, scheme):
+            # NewDictExecutor (ir/executor.py:765-778): rows from the node frame's initializers
+            # (the reference's tmp frame is frame_like(node_frame), scheduler.py:443)
+            return {k: g.ndata.get_initializer(k)((idx.shape[0],) + tuple(v.shape[1:]), v.dtype, v.device, idx)
                     for k, v in scheme.items()}
         zero_feat = prog.issue("NEW_DICT", new_dict, [var_out, v0, fd_list[0]], "dict")
         idx_list.append(v0)
@@ -349,6 +357,85 @@ def schedule_snr(prog, g, edge_tuples, message_func, reduce_func, apply_func, in
     n = g.number_of_nodes()
     prog.issue("WRITE_ROW_INPLACE_" if inplace else "WRITE_ROW_",
                lambda nf, idx, new: _write_rows(nf, idx, new, n, inplace), [var_nf, var_recv, final])
+
+
+def schedule_send(prog, g, u, v, eid, message_func):
+    """schedule_send (scheduler.py:28-56): materialise the messages of the given edges and write
+    them into the message frame at rows eid (None = every edge).  The reference only accepts a UDF
+    here (its TODO at :42); builtins are accepted too and run with their UDF-equivalent __call__."""
+    mfunc = _standardize(message_func, "message")
+    if _is_iterable(mfunc):
+        mfunc = BundledFunction(mfunc)
+    var_nf = prog.var("dict", g.ndata, "nf")
+    var_ef = prog.var("dict", g.edata, "ef")
+    var_mf = prog.var("dict", g._msg, "mf")
+    var_u = prog.var("idx", u)
+    var_v = prog.var("idx", v)
+    var_eid = prog.var("idx", eid)
+    msg = _gen_send(prog, g, var_nf, var_ef, var_u, var_v, var_eid, mfunc)
+    m = g.number_of_edges()
+    prog.issue("WRITE_ROW_", lambda mf, idx, val: _write_rows(mf, idx, val, m, False), [var_mf, var_eid, msg])
+    # set message indicator to 1 (scheduler.py:55-56); done at schedule time like the reference
+    flags = g.msg_index()
+    if eid is None:
+        flags.fill_(1)
+    else:
+        flags[eid] = 1
+
+
+def _gen_reduce(prog, g, reduce_func, edge_tuples, recv_nodes, inverse):
+    """_gen_reduce (scheduler.py:428-468): reduce messages that are already in the message frame.
+    Builtin reducers run kernel (1) in its COPY_EDGE form over the sub-CSR of the triggered edges
+    (the reference multiplies by the n x M incidence matrix of build_inc_matrix_eid,
+    spmv.py:249-314, and only for sum); UDF reducers go through degree bucketing with the edge ids
+    as message ids."""
+    src, dst, eid = edge_tuples
+    rfunc = _standardize(reduce_func, "reduce")
+    var_msg = prog.var("dict", g._msg, "msg")
+    var_nf = prog.var("dict", g.ndata, "nf")
+    var_out = prog.var("dict", {})
+    if _is_iterable(rfunc):
+        kernel_r = [r for r in rfunc if r.name in _RED_CODE]
+        rfunc = [r for r in rfunc if r.name not in _RED_CODE]
+        # rows = position of the destination in recv_nodes, slot payload = position in `eid`
+        adj_var = prog.var("spmat", _once(lambda: subset_adjacency(g, src, dst, recv_nodes, inverse)))
+        for rfn in kernel_r:
+            ftmsg = prog.issue("READ_COL", lambda mf, f: mf[f][eid], [var_msg, prog.var("str", rfn.msg_field)], "feat")
+            ftdst = prog.issue("SPMV", _spmv_fn(ops.MSG_COPY_EDGE, _RED_CODE[rfn.name], 1), [adj_var, ftmsg], "feat")
+            prog.issue("WRITE_COL_", lambda out, f, val: out.__setitem__(f, val),
+                       [var_out, prog.var("str", rfn.out_field), ftdst])
+        if len(rfunc) == 0:
+            return var_out
+        rfunc = BundledFunction(rfunc)
+    gen_degree_bucketing_schedule(prog, g, rfunc, dst, recv_nodes, var_nf, var_msg, var_out, mids=eid)
+    return var_out
+
+
+def schedule_recv(prog, g, recv_nodes, reduce_func, apply_func, inplace):
+    """schedule_recv (scheduler.py:58-109)."""
+    src, dst, eid = g.in_edges(recv_nodes)
+    flags = g.msg_index()
+    if eid.numel() > 0:
+        keep = flags[eid].nonzero().reshape(-1)          # only edges that hold a message
+        src, dst, eid = src[keep], dst[keep], eid[keep]
+    if eid.numel() == 0:
+        # downgrade to apply_nodes: all recv nodes are 0-degree, or nothing was sent (:81-86)
+        if apply_func is not None:
+            schedule_apply_nodes(prog, g, recv_nodes, apply_func, inplace)
+        return
+    nodes, _ = ops.unique_sorted(recv_nodes, g.number_of_nodes(), want_inverse=False)
+    inverse = torch.searchsorted(nodes, dst)
+    var_nf = prog.var("dict", g.ndata, "nf")
+    var_recv = prog.var("idx", nodes, "recv_nodes")
+    reduced = _gen_reduce(prog, g, reduce_func, (src, dst, eid), nodes, inverse)
+    final = _apply_with_accum(prog, g, var_recv, var_nf, reduced, apply_func)
+    n = g.number_of_nodes()
+    prog.issue("WRITE_ROW_INPLACE_" if inplace else "WRITE_ROW_",
+               lambda nf, idx, new: _write_rows(nf, idx, new, n, inplace), [var_nf, var_recv, final])
+    # the messages are consumed (:106-109)
+    flags[eid] = 0
+    if not bool(flags.any()):
+        prog.issue("CLEAR_FRAME_", lambda mf: mf.clear(), [prog.var("dict", g._msg, "mf")])
 
 
 def schedule_pull(prog, g, pull_nodes, message_func, reduce_func, apply_func, inplace):

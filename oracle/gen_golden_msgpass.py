@@ -1,0 +1,161 @@
+"""Generate tests/golden/msgpass_*.npz by running the UNMODIFIED reference: the two-phase
+send / recv entry points, push, (u, v)-pair edge specifications, subset apply_nodes / apply_edges
+and user initializers (python/dgl/graph.py:1926-2087, 2301-2396, 1800-1924, 1590-1648;
+runtime/scheduler.py:28-109, 428-468).
+
+TEST INFRASTRUCTURE ONLY.  Run in the build container (the only place /root/reference exists):
+
+    make -C oracle ref
+    DGL_LIBRARY_PATH=oracle/_ref PYTHONPATH=/root/reference/python:. python oracle/gen_golden_msgpass.py
+
+Shapes and scenarios follow the reference's tests/compute/test_basics.py:363-577 (zero-degree
+recv / pull, multigraph send, consecutive sends) on the seeded multigraphs of gen_golden.py.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+import dgl
+import dgl.function as fn
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+from gen_golden import F32, OUT, make_graph, random_case, t  # noqa: E402
+
+
+def msg_h(edges):
+    return {"m": edges.src["h"]}
+
+
+def msg_hw(edges):
+    return {"m": edges.src["h"] * edges.data["w"].unsqueeze(-1)}
+
+
+def msg_3h(edges):
+    return {"m": edges.src["h"] * 3}
+
+
+def red_udf(nodes):
+    return {"h": nodes.data["h"] + nodes.mailbox["m"].sum(1)}
+
+
+def red_udf_new(nodes):
+    return {"h1": nodes.data["h"] + nodes.mailbox["m"].sum(1)}
+
+
+def app2(nodes):
+    return {"h": nodes.data["h"] * 2}
+
+
+def init2(shape, dtype, ctx, ids):
+    return 2 + torch.zeros(shape, dtype=dtype, device=ctx)
+
+
+def gen_case(seed):
+    n, src, dst, rng = random_case(seed)
+    e = len(src)
+    d = dict(n=np.int64(n), src=src, dst=dst)
+    x = rng.randn(n, 16).astype(F32)
+    w = rng.rand(e).astype(F32)
+    d["in_x"], d["in_w"] = x, w
+    eids_a = rng.choice(e, e // 3, replace=False).astype(np.int64)
+    eids_b = rng.choice(e, e // 4, replace=False).astype(np.int64)       # overlaps eids_a
+    recv_a = np.concatenate([rng.choice(n - 8, 14, replace=False), [n - 1, n - 4]]).astype(np.int64)
+    d["in_eids_a"], d["in_eids_b"], d["in_recv_a"] = eids_a, eids_b, recv_a
+
+    def fresh():
+        g = make_graph(src, dst, n)
+        g.ndata["h"] = t(x)
+        g.edata["w"] = t(w)
+        return g
+
+    # 1. send(eids, UDF) + recv(nodes, builtin sum / max): only edges holding a message count
+    for red, rf in (("sum", fn.sum), ("max", fn.max)):
+        g = fresh()
+        g.send(t(eids_a), msg_hw)
+        g.recv(t(recv_a), rf("m", "h"))
+        d["sendrecv_builtin_%s_h" % red] = g.ndata["h"].numpy().copy()
+
+    # 2. UDF reducer + apply on a recv set with zero-degree nodes and nodes without messages
+    g = fresh()
+    g.send(t(eids_a), msg_h)
+    g.recv(t(recv_a), red_udf, app2)
+    d["sendrecv_udf_apply_h"] = g.ndata["h"].numpy().copy()
+
+    # 3. consecutive sends (the later overwrites), partial recv, then recv of everything left
+    g = fresh()
+    g.send(t(eids_a), msg_h)
+    g.send(t(eids_b), msg_3h)
+    g.recv(t(recv_a), fn.sum("m", "h"))
+    d["two_sends_partial_h"] = g.ndata["h"].numpy().copy()
+    d["two_sends_partial_flags"] = g._msg_index.tousertensor().numpy().astype(np.int64)
+    g.recv(reduce_func=fn.sum("m", "h"))
+    d["two_sends_rest_h"] = g.ndata["h"].numpy().copy()
+    assert int(g._msg_index.tousertensor().sum()) == 0
+
+    # 4. send on every edge + recv on every node == update_all
+    g = fresh()
+    g.send(message_func=msg_hw)
+    g.recv(reduce_func=fn.sum("m", "h"))
+    d["send_all_recv_all_h"] = g.ndata["h"].numpy().copy()
+
+    # 5. recv with nothing pending downgrades to apply_nodes
+    g = fresh()
+    g.recv(t(recv_a), fn.sum("m", "h"), app2)
+    d["recv_nothing_sent_h"] = g.ndata["h"].numpy().copy()
+
+    # 6. (u, v) pair forms on a multigraph: every parallel edge between the pairs is triggered
+    pick = rng.choice(e, 25, replace=False)
+    pu, pv = src[pick].copy(), dst[pick].copy()
+    d["in_pair_u"], d["in_pair_v"] = pu, pv
+    g = fresh()
+    g.send_and_recv((t(pu), t(pv)), fn.src_mul_edge("h", "w", "m"), fn.sum("m", "h"))
+    d["snr_pairs_h"] = g.ndata["h"].numpy().copy()
+    g = fresh()
+    g.send((t(pu), t(pv)), msg_h)
+    d["send_pairs_flags"] = g._msg_index.tousertensor().numpy().astype(np.int64)
+    g.recv(reduce_func=fn.max("m", "h"))
+    d["send_pairs_recv_max_h"] = g.ndata["h"].numpy().copy()
+
+    # 7. push
+    push_u = np.unique(src)[:9].astype(np.int64)
+    d["in_push_u"] = push_u
+    for name, mf in (("copy_src", fn.copy_src("h", "m")), ("src_mul_edge", fn.src_mul_edge("h", "w", "m"))):
+        g = fresh()
+        g.push(t(push_u), mf, fn.sum("m", "h"), app2)
+        d["push_%s_apply_h" % name] = g.ndata["h"].numpy().copy()
+
+    # 8. subset apply_nodes / apply_edges
+    g = fresh()
+    g.apply_nodes(app2, t(recv_a))
+    d["apply_nodes_subset_h"] = g.ndata["h"].numpy().copy()
+    g.apply_edges(lambda edges: {"w": edges.data["w"] + edges.src["h"][:, 0] - edges.dst["h"][:, 1]}, t(eids_a))
+    d["apply_edges_subset_w"] = g.edata["w"].numpy().copy()
+    g.apply_edges(lambda edges: {"s": edges.src["h"] + edges.dst["h"]})
+    d["apply_edges_all_s"] = g.edata["s"].numpy().copy()
+
+    # 9. user initializers: zero-degree pull rows on the bucketing path, and the untouched rows of
+    #    a column that a partial write creates
+    g = fresh()
+    g.set_n_initializer(init2, "h")
+    g.pull(t(recv_a), msg_h, red_udf, app2)
+    d["pull_init2_h"] = g.ndata["h"].numpy().copy()
+    g = fresh()
+    g.set_n_initializer(init2, "h1")
+    g.send(t(eids_a), msg_h)
+    g.recv(t(recv_a), red_udf_new)
+    d["recv_newfield_init2_h1"] = g.ndata["h1"].numpy().copy()
+    return d
+
+
+def main():
+    os.makedirs(OUT, exist_ok=True)
+    torch.manual_seed(0)
+    for seed in range(2):
+        np.savez_compressed(os.path.join(OUT, "msgpass_%d.npz" % seed), **gen_case(seed))
+    print("wrote", sorted(f for f in os.listdir(OUT) if f.startswith("msgpass")))
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -15,6 +15,7 @@ import torch
 
 from tests import cpu_engine
 from tests import test_gpu_graph_api as api
+from tests import test_gpu_msgpass as mp
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(glob.glob(os.path.join(GOLDEN, "case_*.npz")))
@@ -48,6 +49,32 @@ def cpu_api(monkeypatch):
 @pytest.mark.parametrize("path", CASES[:2], ids=[os.path.basename(c) for c in CASES[:2]])
 def test_host_layer_against_reference_golden(cpu_api, path, body):
     body(dict(np.load(path)))
+
+
+MP_CASES = sorted(glob.glob(os.path.join(GOLDEN, "msgpass_*.npz")))
+MP_BODIES = [mp.test_send_then_recv_builtin_reducers, mp.test_send_then_recv_udf_reducer_with_apply,
+             mp.test_consecutive_sends_partial_recv, mp.test_send_all_recv_all_equals_update_all,
+             mp.test_recv_without_pending_messages_is_apply, mp.test_pair_specifications_on_multigraph,
+             mp.test_push_with_apply, mp.test_subset_apply_nodes_and_edges, mp.test_user_initializers]
+
+
+@pytest.fixture()
+def cpu_mp(monkeypatch):
+    monkeypatch.setattr(mp, "cu", lambda a: torch.from_numpy(np.ascontiguousarray(a)))
+    monkeypatch.setattr(mp, "device", lambda: torch.device("cpu"))
+    with cpu_engine.installed():
+        yield mp
+
+
+@pytest.mark.parametrize("body", MP_BODIES, ids=[b.__name__ for b in MP_BODIES])
+@pytest.mark.parametrize("path", MP_CASES, ids=[os.path.basename(c) for c in MP_CASES])
+def test_send_recv_host_layer_against_reference_golden(cpu_mp, path, body):
+    body(dict(np.load(path)))
+
+
+def test_reference_style_scenarios_on_host_layer(cpu_mp):
+    mp.test_recv_0deg_like_reference()
+    mp.test_send_multigraph_like_reference()
 
 
 def test_cpu_engine_is_not_left_installed():
