@@ -279,6 +279,47 @@ class ClockSampler(object):
 # B200 arm
 # ---------------------------------------------------------------------------------------------
 
+def e2e_partitioned(part, x_loc, dy_loc, y_loc, dx_loc, alg_step, barrier, dev, world, args):
+    """N > 1 end-to-end: every rank's row blocks of X and dY start in HOST (pinned) memory and its
+    blocks of Y and dX end there, every step, through the partition's public calls
+    (RowPartition / HaloPartition .forward / .backward = exchange + SpMM).  All copies and kernels
+    are stream-ordered on the current stream; the exchange's own barriers keep a block from being
+    overwritten while a peer still reads it.  Timed with CUDA events, max over ranks."""
+    import torch.distributed as dist
+    rows, feat = x_loc.shape
+    xh = torch.randn(rows, feat).pin_memory()
+    dyh = torch.randn(rows, feat).pin_memory()
+    yh = torch.empty(rows, feat).pin_memory()
+    dxh = torch.empty(rows, feat).pin_memory()
+
+    def one():
+        x_loc.copy_(xh, non_blocking=True)
+        dy_loc.copy_(dyh, non_blocking=True)
+        part.forward(x_loc, out=y_loc)
+        yh.copy_(y_loc, non_blocking=True)
+        part.backward(dy_loc, out=dx_loc)
+        dxh.copy_(dx_loc, non_blocking=True)
+
+    for _ in range(2):
+        one()
+    barrier()
+    k = max(3, min(args.steps, 10))
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(k):
+        one()
+    b.record()
+    barrier()
+    t = torch.tensor([a.elapsed_time(b) / k], device=dev, dtype=torch.float64)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    nbytes = torch.tensor([2.0 * rows * feat * 4], device=dev, dtype=torch.float64)
+    dist.all_reduce(nbytes)                                   # whole job, all ranks
+    return {"value": alg_step / (ms * 1e-3) / 1e9, "unit": UNIT,
+            "h2d_bytes_per_step": int(nbytes.item()), "d2h_bytes_per_step": int(nbytes.item()),
+            "ms_per_step": ms, "steps": k}
+
+
 def run_b200(args):
     import torch.distributed as dist
     from dgl_b200 import ops, _lib
@@ -454,6 +495,9 @@ def run_b200(args):
         check_ref = None
         torch.cuda.empty_cache()
     xchg_bytes = part.exchange_bytes(feat)
+    e2e_multi = None
+    if world > 1 and not args.no_e2e and n * feat * 4 <= (8 << 30):
+        e2e_multi = e2e_partitioned(part, x_loc, dy_loc, y_loc, dx_loc, alg_step, barrier, dev, world, args)
     transfer = None
     if exchange == "halo" and world > 1 and part.halo_in.timing:
         # DGL_B200_TIMING=1: the transfers alone (between the barriers), per rank
@@ -534,7 +578,7 @@ def run_b200(args):
                "ms_per_step": t_e2e * 1e3, "steps": k}
         del xh, dyh, yh, dxh
     elif world > 1:
-        e2e = None
+        e2e = e2e_multi
 
     # ---- GCN epoch (second half of BASELINE.json's metric) ------------------------------------
     gcn = None

@@ -6,8 +6,11 @@ send_and_recv / pull, python/dgl/function); all computation is in libdgl_b200.so
 """
 from .base import ALL, DGLError
 from . import function
+from . import init
 from . import ops
 from .graph import DGLGraph
 from .udf import EdgeBatch, NodeBatch
+from .propagate import prop_nodes, prop_edges, prop_nodes_bfs, prop_nodes_topo
+from .traversal import bfs_nodes_generator, bfs_edges_generator, topological_nodes_generator
 
 __version__ = "0.1.0"

@@ -386,6 +386,26 @@ class DGLGraph(object):
             return   # scheduler.py:302-305
         self._run(lambda prog: scheduler.schedule_snr(prog, self, (uu, vv, eid), m, r, a, inplace))
 
+    def prop_nodes(self, nodes_generator, message_func="default", reduce_func="default",
+                   apply_node_func="default"):
+        """python/dgl/graph.py:2443-2517: pull on every node frontier, in the generator's order."""
+        for node_frontier in nodes_generator:
+            self.pull(node_frontier, message_func, reduce_func, apply_node_func)
+
+    def prop_edges(self, edges_generator, message_func="default", reduce_func="default",
+                   apply_node_func="default"):
+        """python/dgl/graph.py:2519-2598: send_and_recv on every edge frontier."""
+        for edge_frontier in edges_generator:
+            self.send_and_recv(edge_frontier, message_func, reduce_func, apply_node_func)
+
+    def adjacency_coo(self, transpose=False):
+        """(idx int64[2E], eid int64[E]) as _CAPI_DGLGraphGetAdj(handle, transpose, "coo") returns:
+        idx = [dst | src] in edge-id order ([src | dst] when transposed) and the identity shuffle
+        (Graph::GetAdj, src/graph/graph.cc:509-524)."""
+        src, dst = self.edges()
+        idx = torch.cat([src, dst]) if transpose else torch.cat([dst, src])
+        return idx, torch.arange(self._e, dtype=torch.int64, device=idx.device)
+
     def apply_nodes(self, func="default", v=ALL, inplace=False):
         """python/dgl/graph.py:1800-1852."""
         from . import scheduler

@@ -149,8 +149,70 @@ def gen_case(seed):
     return d
 
 
+def gen_traversal(seed):
+    """Frontier generators (python/dgl/traversal.py -> src/graph/traversal.h) and propagation
+    (python/dgl/propagate.py) on a random DAG (forest-like, TreeLSTM-shaped) and on the cyclic
+    multigraph of random_case."""
+    rng = np.random.RandomState(100 + seed)
+    n = 60
+    # DAG: every node i > 0 gets 1-3 parents among the nodes below it; edges child -> parent order
+    # is arbitrary, parallel edges allowed
+    src, dst = [], []
+    for i in range(1, n):
+        for p in rng.choice(i, size=min(i, rng.randint(1, 4)), replace=True):
+            src.append(int(p))
+            dst.append(i)
+    perm = rng.permutation(len(src))
+    relabel = rng.permutation(n)
+    src = relabel[np.asarray(src, dtype=np.int64)[perm]]
+    dst = relabel[np.asarray(dst, dtype=np.int64)[perm]]
+    d = dict(dag_n=np.int64(n), dag_src=src, dag_dst=dst)
+    g = make_graph(src, dst, n)
+
+    def pack(tag, frontiers):
+        fr = [f.numpy().astype(np.int64) for f in frontiers]
+        d[tag + "_ids"] = np.concatenate(fr) if fr else np.zeros(0, np.int64)
+        d[tag + "_sections"] = np.asarray([len(f) for f in fr], dtype=np.int64)
+
+    pack("dag_topo", dgl.topological_nodes_generator(g))
+    pack("dag_topo_rev", dgl.topological_nodes_generator(g, True))
+    roots = np.asarray([int(relabel[0]), int(relabel[1])], dtype=np.int64)
+    d["in_dag_bfs_src"] = roots
+    pack("dag_bfs", dgl.bfs_nodes_generator(g, t(roots)))
+    pack("dag_bfs_edges", dgl.bfs_edges_generator(g, t(roots)))
+    x = rng.randn(n, 8).astype(F32)
+    d["in_dag_x"] = x
+    g.ndata["h"] = t(x)
+    dgl.prop_nodes_topo(g, message_func=fn.copy_src("h", "m"), reduce_func=fn.sum("m", "h"))
+    d["dag_prop_topo_sum_h"] = g.ndata["h"].numpy().copy()
+    g.ndata["h"] = t(x)
+    dgl.prop_nodes_topo(g, message_func=msg_h, reduce_func=red_udf, apply_node_func=app2)
+    d["dag_prop_topo_udf_h"] = g.ndata["h"].numpy().copy()
+    g.ndata["h"] = t(x)
+    dgl.prop_edges(g, dgl.bfs_edges_generator(g, t(roots)), fn.copy_src("h", "m"), fn.max("m", "h"))
+    d["dag_prop_bfs_edges_max_h"] = g.ndata["h"].numpy().copy()
+
+    # cyclic multigraph: BFS both directions
+    cn, csrc, cdst, crng = random_case(seed)
+    cg = make_graph(csrc, cdst, cn)
+    start = np.asarray([5, 3, 17], dtype=np.int64)
+    d["cyc_n"], d["cyc_src"], d["cyc_dst"], d["in_cyc_bfs_src"] = np.int64(cn), csrc, cdst, start
+    pack("cyc_bfs", dgl.bfs_nodes_generator(cg, t(start)))
+    pack("cyc_bfs_rev", dgl.bfs_nodes_generator(cg, t(start), True))
+    pack("cyc_bfs_edges", dgl.bfs_edges_generator(cg, t(start)))
+    pack("cyc_bfs_edges_rev", dgl.bfs_edges_generator(cg, t(start), True))
+    cx = crng.randn(cn, 8).astype(F32)
+    d["in_cyc_x"] = cx
+    cg.ndata["h"] = t(cx)
+    dgl.prop_nodes_bfs(cg, t(start), message_func=fn.copy_src("h", "m"), reduce_func=fn.sum("m", "h"))
+    d["cyc_prop_bfs_sum_h"] = cg.ndata["h"].numpy().copy()
+    return d
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    for seed in range(2):
+        np.savez_compressed(os.path.join(OUT, "traversal_%d.npz" % seed), **gen_traversal(seed))
     torch.manual_seed(0)
     for seed in range(2):
         np.savez_compressed(os.path.join(OUT, "msgpass_%d.npz" % seed), **gen_case(seed))

@@ -15,7 +15,7 @@ import torch
 
 from tests import cpu_engine
 from tests import test_gpu_graph_api as api
-from tests import test_gpu_msgpass as mp
+from tests import test_sendrecv_gpu as mp
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 CASES = sorted(glob.glob(os.path.join(GOLDEN, "case_*.npz")))
@@ -70,6 +70,14 @@ def cpu_mp(monkeypatch):
 @pytest.mark.parametrize("path", MP_CASES, ids=[os.path.basename(c) for c in MP_CASES])
 def test_send_recv_host_layer_against_reference_golden(cpu_mp, path, body):
     body(dict(np.load(path)))
+
+
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "traversal_*.npz"))),
+                         ids=lambda p: os.path.basename(p))
+def test_traversal_and_propagation_against_reference_golden(cpu_mp, path):
+    case = dict(np.load(path))
+    mp.test_frontier_generators_bit_exact(case)
+    mp.test_propagation_against_reference(case)
 
 
 def test_reference_style_scenarios_on_host_layer(cpu_mp):

@@ -260,3 +260,69 @@ def test_send_multigraph_like_reference():
     new = g.ndata["a"]
     assert torch.allclose(new[1], answer(old[0], old[2], old[3]))
     assert torch.allclose(new[[0, 2]], torch.zeros(2, 5, device=dev))
+
+
+# ---- frontier generators + propagation (python/dgl/traversal.py, propagate.py) ------------------
+
+TRAVERSAL = sorted(glob.glob(os.path.join(GOLDEN, "traversal_*.npz")))
+
+
+@pytest.fixture(scope="module", params=TRAVERSAL, ids=[os.path.basename(c) for c in TRAVERSAL])
+def trav(request):
+    return dict(np.load(request.param))
+
+
+def _graph_of(case, tag):
+    import dgl_b200
+    g = dgl_b200.DGLGraph()
+    g.add_nodes(int(case[tag + "_n"]))
+    g.add_edges(torch.from_numpy(case[tag + "_src"]), torch.from_numpy(case[tag + "_dst"]))
+    return g.to(device())
+
+
+def _same_frontiers(frontiers, case, tag):
+    """Bit-exact: same number of frontiers, same ids in the same order inside each."""
+    got = [f.cpu().numpy() for f in frontiers]
+    assert [len(f) for f in got] == case[tag + "_sections"].tolist(), tag
+    cat = np.concatenate(got) if got else np.zeros(0, np.int64)
+    assert np.array_equal(cat, case[tag + "_ids"]), tag
+
+
+def test_frontier_generators_bit_exact(trav):
+    import dgl_b200
+    g = _graph_of(trav, "dag")
+    _same_frontiers(dgl_b200.topological_nodes_generator(g), trav, "dag_topo")
+    _same_frontiers(dgl_b200.topological_nodes_generator(g, True), trav, "dag_topo_rev")
+    roots = cu(trav["in_dag_bfs_src"])
+    _same_frontiers(dgl_b200.bfs_nodes_generator(g, roots), trav, "dag_bfs")
+    _same_frontiers(dgl_b200.bfs_edges_generator(g, roots), trav, "dag_bfs_edges")
+    c = _graph_of(trav, "cyc")
+    start = cu(trav["in_cyc_bfs_src"])
+    _same_frontiers(dgl_b200.bfs_nodes_generator(c, start), trav, "cyc_bfs")
+    _same_frontiers(dgl_b200.bfs_nodes_generator(c, start, True), trav, "cyc_bfs_rev")
+    _same_frontiers(dgl_b200.bfs_edges_generator(c, start), trav, "cyc_bfs_edges")
+    _same_frontiers(dgl_b200.bfs_edges_generator(c, start, True), trav, "cyc_bfs_edges_rev")
+    from dgl_b200.base import DGLError
+    with pytest.raises(DGLError):
+        dgl_b200.topological_nodes_generator(c)       # loop detected (traversal.h:209-211)
+
+
+def test_propagation_against_reference(trav):
+    import dgl_b200
+    from dgl_b200 import function as fn
+    g = _graph_of(trav, "dag")
+    g.ndata["h"] = cu(trav["in_dag_x"])
+    dgl_b200.prop_nodes_topo(g, message_func=fn.copy_src("h", "m"), reduce_func=fn.sum("m", "h"))
+    close(g.ndata["h"], trav["dag_prop_topo_sum_h"], rtol=1e-4)
+    g.ndata["h"] = cu(trav["in_dag_x"])
+    dgl_b200.prop_nodes_topo(g, message_func=msg_h, reduce_func=red_udf, apply_node_func=app2)
+    close(g.ndata["h"], trav["dag_prop_topo_udf_h"], rtol=1e-4)
+    g.ndata["h"] = cu(trav["in_dag_x"])
+    dgl_b200.prop_edges(g, dgl_b200.bfs_edges_generator(g, cu(trav["in_dag_bfs_src"])),
+                        fn.copy_src("h", "m"), fn.max("m", "h"))
+    close(g.ndata["h"], trav["dag_prop_bfs_edges_max_h"])
+    c = _graph_of(trav, "cyc")
+    c.ndata["h"] = cu(trav["in_cyc_x"])
+    dgl_b200.prop_nodes_bfs(c, cu(trav["in_cyc_bfs_src"]), message_func=fn.copy_src("h", "m"),
+                            reduce_func=fn.sum("m", "h"))
+    close(c.ndata["h"], trav["cyc_prop_bfs_sum_h"], rtol=1e-4)
