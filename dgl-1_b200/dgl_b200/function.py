@@ -16,6 +16,7 @@ import operator
 import torch
 
 __all__ = ["src_mul_edge", "copy_src", "copy_edge", "sum", "max",
+           "u_add_v", "u_mul_v", "u_dot_v", "copy_u", "copy_v",
            "BuiltinFunction", "BundledFunction"]
 
 
@@ -224,3 +225,61 @@ def sum(msg, out):  # pylint: disable=redefined-builtin
 def max(msg, out):  # pylint: disable=redefined-builtin
     """Builtin reducer: max of mailbox[msg] -> out."""
     return SimpleReduceFunction("max", _torch_max, msg, out)
+
+
+# ---- builtin edge functions (SURVEY.md 8f rank 2) -------------------------------------------------
+# The reference (0.1.3) has no builtin for apply_edges: the GAT example computes
+# a1[src] + a2[dst] in a Python edge UDF over three materialised E-row gathers
+# (examples/pytorch/gat/train.py:90-97 through runtime/scheduler.py:234-277).  These builtins name the
+# same per-edge expressions so that apply_edges lowers them to ONE launch of the SDDMM kernel
+# (dglb200_sddmm_csr); called as a UDF they compute exactly what the UDF would.
+
+class EdgeFunction(BuiltinFunction):
+    """u-op-v over (edges.src[lhs], edges.dst[rhs]) -> edges.data[out]."""
+
+    def __init__(self, name, lhs_field, rhs_field, out_field):
+        self._name = name
+        self.lhs_field = lhs_field
+        self.rhs_field = rhs_field
+        self.out_field = out_field
+
+    @property
+    def name(self):
+        return self._name
+
+    def __call__(self, edges):
+        if self._name == "copy_u":
+            return {self.out_field: edges.src[self.lhs_field]}
+        if self._name == "copy_v":
+            return {self.out_field: edges.dst[self.rhs_field]}
+        u, v = edges.src[self.lhs_field], edges.dst[self.rhs_field]
+        if self._name == "u_add_v":
+            return {self.out_field: u + v}
+        if self._name == "u_mul_v":
+            return {self.out_field: u * v}
+        return {self.out_field: (u * v).sum(-1, keepdim=True)}      # u_dot_v over the last dim
+
+
+def u_add_v(lhs, rhs, out):
+    """Builtin edge function: edges.src[lhs] + edges.dst[rhs] -> out."""
+    return EdgeFunction("u_add_v", lhs, rhs, out)
+
+
+def u_mul_v(lhs, rhs, out):
+    """Builtin edge function: edges.src[lhs] * edges.dst[rhs] -> out."""
+    return EdgeFunction("u_mul_v", lhs, rhs, out)
+
+
+def u_dot_v(lhs, rhs, out):
+    """Builtin edge function: <edges.src[lhs], edges.dst[rhs]> over the last dim -> out (..., 1)."""
+    return EdgeFunction("u_dot_v", lhs, rhs, out)
+
+
+def copy_u(lhs, out):
+    """Builtin edge function: edges.src[lhs] -> out."""
+    return EdgeFunction("copy_u", lhs, None, out)
+
+
+def copy_v(rhs, out):
+    """Builtin edge function: edges.dst[rhs] -> out."""
+    return EdgeFunction("copy_v", None, rhs, out)

@@ -420,7 +420,10 @@ class DGLGraph(object):
         if func == "default":
             func = self._apply_edge_func
         assert func is not None
-        if is_all(edges):
+        from .function import EdgeFunction
+        if is_all(edges) and isinstance(func, EdgeFunction):
+            u = v = eid = None          # one SDDMM launch over the cached CSR: no edge list needed
+        elif is_all(edges):
             u, v = self.edges()
             eid = None
         elif isinstance(edges, tuple):

@@ -23,7 +23,7 @@ import torch
 from . import ops
 from .autograd import Adjacency, aggregate
 from .base import DGLError
-from .function import BuiltinFunction, BundledFunction
+from .function import BuiltinFunction, BundledFunction, EdgeFunction
 from .init import zero_initializer
 from .udf import EdgeBatch, NodeBatch
 
@@ -478,9 +478,21 @@ def schedule_apply_nodes(prog, g, v, apply_func, inplace):
 
 
 def schedule_apply_edges(prog, g, u, v, eid, apply_func, inplace):
-    """schedule_apply_edges (scheduler.py:234-277); eid None = all edges."""
+    """schedule_apply_edges (scheduler.py:234-277); eid None = all edges.  A builtin edge function
+    over all edges is ONE SDDMM launch on the cached in-edge CSR (no E-row gathers, no UDF)."""
     var_nf = prog.var("dict", g.ndata, "nf")
     var_ef = prog.var("dict", g.edata, "ef")
+    if isinstance(apply_func, EdgeFunction) and eid is None:
+        from . import edge_ops
+        fn = apply_func
+        adj_var = prog.var("spmat", _once(g.adjacency))
+        read = lambda f: (prog.issue("READ_COL", lambda nf, k: nf[k], [var_nf, prog.var("str", f)], "feat")  # noqa: E731
+                          if f is not None else prog.var("feat", None))
+        lhs, rhs = read(fn.lhs_field), read(fn.rhs_field)
+        out = prog.issue("SDDMM", lambda adj, a, b: edge_ops.sddmm(adj(), fn.name, a, b), [adj_var, lhs, rhs], "feat")
+        prog.issue("WRITE_COL_", lambda ef, f, val: ef.__setitem__(f, val),
+                   [var_ef, prog.var("str", fn.out_field), out])
+        return
     var_u = prog.var("idx", u)
     var_v = prog.var("idx", v)
     var_eid = prog.var("idx", eid)

@@ -146,11 +146,54 @@ def _edge_data_to_slots(csr, w):
     return w if csr.eids is None else w[csr.eids.long()]
 
 
+def _edge_softmax(csr, score):
+    rows = _csr_row_ids(csr)
+    e = _slot_edge(csr)
+    s = score.float()[e]
+    alpha = torch.zeros_like(score, dtype=torch.float32)
+    for r in range(csr.n_rows):
+        sel = (rows == r).nonzero().reshape(-1)
+        if sel.numel():
+            alpha[e[sel]] = torch.softmax(s[sel], 0)
+    return alpha
+
+
+def _edge_softmax_backward(csr, alpha, dalpha):
+    rows = torch.empty(csr.nnz, dtype=torch.int64)
+    rows[_slot_edge(csr)] = _csr_row_ids(csr)          # destination of every edge id
+    dot = torch.zeros((csr.n_rows, alpha.shape[1]), dtype=torch.float32)
+    dot.index_add_(0, rows, alpha * dalpha)
+    return alpha * (dalpha - dot[rows])
+
+
+def _gat_aggregate(csr, a_src, a_dst, ft, negative_slope, flavour=1, want_edge=True):
+    heads, dim = int(ft.shape[1]), int(ft.shape[2])
+    rows = _csr_row_ids(csr)
+    s_idx = csr.indices.long()
+    e = _slot_edge(csr)
+    s = torch.nn.functional.leaky_relu(a_src.reshape(-1, heads)[s_idx] + a_dst.reshape(-1, heads)[rows], negative_slope)
+    if flavour == ops.SOFTMAX_GAT_EXAMPLE:
+        a = torch.exp(s).clamp(-10, 10)
+    else:
+        mx = torch.full((csr.n_rows, heads), -float("inf")).scatter_reduce(0, rows[:, None].expand_as(s), s, "amax")
+        a = torch.exp(s - mx[rows])
+    z = torch.zeros((csr.n_rows, heads)).index_add_(0, rows, a)
+    num = torch.zeros((csr.n_rows, heads, dim)).index_add_(0, rows, a[:, :, None] * ft[s_idx])
+    out = torch.where(z[:, :, None] > 0, num / z[:, :, None].clamp_min(1e-38), torch.zeros_like(num))
+    a_out = None
+    if want_edge:
+        a_out = torch.zeros((csr.nnz, heads))
+        a_out[e] = a
+    return out, a_out, z
+
+
 _PATCHES = {
     "csr_build": _csr_build, "widen": _widen, "degrees": _degrees, "csr_row_ids": _csr_row_ids,
     "spmm": _spmm, "spmm_backward_x": _spmm_backward_x, "sddmm": _sddmm,
     "unique_sorted": _unique_sorted, "degree_bucketing": _degree_bucketing,
     "gather_rows": _gather_rows, "edge_data_to_slots": _edge_data_to_slots,
+    "edge_softmax": _edge_softmax, "edge_softmax_backward": _edge_softmax_backward,
+    "gat_aggregate": _gat_aggregate,
 }
 
 

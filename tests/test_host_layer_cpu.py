@@ -80,6 +80,18 @@ def test_traversal_and_propagation_against_reference_golden(cpu_mp, path):
     mp.test_propagation_against_reference(case)
 
 
+def test_edge_ops_autograd_wiring(monkeypatch):
+    from tests import test_edge_ops_gpu as eo
+    monkeypatch.setattr(eo, "device", lambda: torch.device("cpu"))
+    with cpu_engine.installed():
+        for op in ("u_add_v", "u_mul_v", "u_dot_v", "copy_u", "copy_v"):
+            for tail in ((6,), (4, 8), (3, 1)):
+                eo.test_sddmm_forward_and_gradients(op, tail)
+        eo.test_edge_softmax_forward_and_gradient()
+        eo.test_gat_attention_matches_udf_formulation_with_gradients()
+        eo.test_apply_edges_builtin_is_one_sddmm_executor()
+
+
 def test_reference_style_scenarios_on_host_layer(cpu_mp):
     mp.test_recv_0deg_like_reference()
     mp.test_send_multigraph_like_reference()
