@@ -81,7 +81,7 @@ def test_traversal_and_propagation_against_reference_golden(cpu_mp, path):
 
 
 def test_edge_ops_autograd_wiring(monkeypatch):
-    from tests import test_edge_ops_gpu as eo
+    from tests import test_uopv_edge_ops_gpu as eo
     monkeypatch.setattr(eo, "device", lambda: torch.device("cpu"))
     with cpu_engine.installed():
         for op in ("u_add_v", "u_mul_v", "u_dot_v", "copy_u", "copy_v"):
