@@ -227,6 +227,10 @@ def gcn_epoch_cpu(src, dst, n, cfg, epochs=2, warm=1):
 # ---------------------------------------------------------------------------------------------
 
 class ClockSampler(object):
+    """nvidia-smi polled every 20 ms into a file.  Started BEFORE the warm-up (the tool needs a few
+    hundred ms to come up), `mark()` is called when the timed region starts; `stop()` reports the
+    samples taken after the mark, or - when the timed region was shorter than a polling interval -
+    the last samples of the warm-up, which ran the same kernels back to back (`window` says which)."""
     FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
               "clocks_event_reasons.sw_power_cap")
@@ -235,12 +239,23 @@ class ClockSampler(object):
     def __init__(self, index):
         self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
         self.p = None
+        self.mark_line = 0
         try:
             self.p = subprocess.Popen(
                 ["nvidia-smi", "--query-gpu=" + self.FIELDS, "--format=csv,noheader,nounits",
-                 "-lms", "100", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
+                 "-lms", "20", "-i", str(index)], stdout=self.f, stderr=subprocess.DEVNULL)
         except OSError:
             self.p = None
+
+    def _lines(self):
+        try:
+            with open(self.f.name) as f:
+                return f.read().splitlines()
+        except OSError:
+            return []
+
+    def mark(self):
+        self.mark_line = len(self._lines())
 
     def stop(self):
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
@@ -251,10 +266,16 @@ class ClockSampler(object):
             self.p.wait(timeout=5)
         except subprocess.TimeoutExpired:
             self.p.kill()
-        self.f.flush()
-        self.f.seek(0)
+        lines = self._lines()
+        self.f.close()
+        os.unlink(self.f.name)
+        window = "timed"
+        picked = lines[self.mark_line:]
+        if len(picked) < 2:                      # timed region shorter than the polling interval
+            window = "warmup_tail+timed"
+            picked = lines[max(0, self.mark_line - 10):]
         sm, mx, reasons, power = [], [], set(), []
-        for ln in self.f.read().splitlines():
+        for ln in picked:
             parts = [s.strip() for s in ln.split(",")]
             if len(parts) < 7:
                 continue
@@ -267,11 +288,9 @@ class ClockSampler(object):
             for name, val in zip(self.NAMES, parts[3:7]):
                 if val == "Active":
                     reasons.add(name)
-        self.f.close()
-        os.unlink(self.f.name)
         if sm:
             out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons),
-                       samples=len(sm), power_w_max=max(power))
+                       samples=len(sm), power_w_max=max(power), window=window)
         return out
 
 
@@ -337,6 +356,7 @@ def run_b200(args):
     cfg = workload_cfg(args.workload)
     n, e, feat = cfg["n"], cfg["e"], cfg["feat"]
     lib = _lib.get_lib()
+    sampler = ClockSampler(local) if rank == 0 else None     # polls from now on; mark() at the timed region
 
     # ---- graph + structure (one-off, cached per graph like GraphIndex.adjacency_matrix) ------
     t0 = time.time()
@@ -406,10 +426,24 @@ def run_b200(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    # warm-up: the requested steps, then as many more as it takes to have run ~0.3 s back to back
+    # (clocks settle under load and the sampler has samples to fall back on); the extra count is
+    # decided by rank 0 and broadcast so that every rank runs the same number of exchanges
+    torch.cuda.synchronize()
+    t_w = time.time()
+    n_warm = max(args.warmup, 3)
+    for _ in range(n_warm):
+        step(False)
+    torch.cuda.synchronize()
+    per = max((time.time() - t_w) / n_warm, 1e-5)
+    extra = torch.tensor([min(2000, max(0, int((0.3 - per * n_warm) / per)))], device=dev, dtype=torch.int64)
+    if world > 1:
+        dist.broadcast(extra, src=0)
+    for _ in range(int(extra.item())):
         step(False)
     barrier()
-    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.mark()
     l0 = _lib.launch_count()
     s_ev, e_ev = ev(), ev()
     s_ev.record()
@@ -649,7 +683,7 @@ def run_b200(args):
                            else "all-gather halo"),
                        "exchange_bytes_per_rank_per_spmm": xchg_bytes,
                        "op_ms_rank0": op_ms, "exposed_exchange_ms_rank0": xchg_ms, "transfer_per_rank": transfer, "kernel_ms_per_rank": k_ranks,
-                       "graph_build_s": round(t_build, 2)},
+                       "graph_build_s": round(t_build, 2), "extra_warmup_steps": int(extra.item())},
             "edge_feat_per_s": 2 * e * feat / (ms_step * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches), "clocks": clocks, "gcn_epoch": gcn,
