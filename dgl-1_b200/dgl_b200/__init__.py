@@ -10,6 +10,8 @@ from . import init
 from . import ops
 from .graph import DGLGraph
 from .udf import EdgeBatch, NodeBatch
+from .batched_graph import (BatchedDGLGraph, batch, unbatch, sum_nodes, sum_edges, mean_nodes,
+                            mean_edges, max_nodes, max_edges)
 from .edge_ops import sddmm, edge_softmax, gat_attention
 from .propagate import prop_nodes, prop_edges, prop_nodes_bfs, prop_nodes_topo
 from .traversal import bfs_nodes_generator, bfs_edges_generator, topological_nodes_generator

@@ -209,8 +209,61 @@ def gen_traversal(seed):
     return d
 
 
+def gen_batched(seed):
+    """dgl.batch + update_all on the union + per-graph readout (python/dgl/batched_graph.py)."""
+    rng = np.random.RandomState(200 + seed)
+    sizes = [(7, 20), (1, 0), (12, 40), (5, 3), (9, 30)]           # (nodes, edges); one graph has no edge
+    d = dict(batch_sizes=np.asarray(sizes, dtype=np.int64))
+    graphs = []
+    for i, (n, e) in enumerate(sizes):
+        src = rng.randint(0, n, size=e).astype(np.int64)
+        dst = rng.randint(0, n, size=e).astype(np.int64)
+        g = make_graph(src, dst, n)
+        x = rng.randn(n, 3, 4).astype(F32)
+        w = rng.rand(n).astype(F32)
+        ew = rng.randn(e, 5).astype(F32)
+        es = rng.rand(e).astype(F32)
+        g.ndata["h"], g.ndata["w"] = t(x), t(w)
+        if e > 0:
+            g.edata["e"], g.edata["s"] = t(ew), t(es)
+        graphs.append(g)
+        d["g%d_src" % i], d["g%d_dst" % i] = src, dst
+        d["in_g%d_h" % i], d["in_g%d_w" % i], d["in_g%d_e" % i], d["in_g%d_s" % i] = x, w, ew, es
+    bg = dgl.batch(graphs)
+    d["batch_num_nodes"] = np.asarray(bg.batch_num_nodes, dtype=np.int64)
+    d["batch_num_edges"] = np.asarray(bg.batch_num_edges, dtype=np.int64)
+    bs, bd = bg.edges()
+    d["batched_src"], d["batched_dst"] = bs.numpy().astype(np.int64), bd.numpy().astype(np.int64)
+    d["batched_h"] = bg.ndata["h"].numpy().copy()
+    d["sum_nodes_h"] = dgl.sum_nodes(bg, "h").numpy().copy()
+    d["sum_nodes_h_w"] = dgl.sum_nodes(bg, "h", "w").numpy().copy()
+    d["mean_nodes_h"] = dgl.mean_nodes(bg, "h").numpy().copy()
+    d["mean_nodes_h_w"] = dgl.mean_nodes(bg, "h", "w").numpy().copy()
+    d["max_nodes_h"] = dgl.max_nodes(bg, "h").numpy().copy()
+    d["sum_edges_e"] = dgl.sum_edges(bg, "e").numpy().copy()
+    d["sum_edges_e_s"] = dgl.sum_edges(bg, "e", "s").numpy().copy()
+    d["max_edges_e"] = dgl.max_edges(bg, "e").numpy().copy()
+    bg.update_all(fn.copy_src("h", "m"), fn.sum("m", "h"))
+    d["batched_update_all_h"] = bg.ndata["h"].numpy().copy()
+    d["sum_nodes_after_update"] = dgl.sum_nodes(bg, "h").numpy().copy()
+    parts = dgl.unbatch(bg)
+    for i, gp in enumerate(parts):
+        d["unbatch%d_h" % i] = gp.ndata["h"].numpy().copy()
+    # gradient of a readout (torch autograd through unsorted_1d_segment_sum in the reference)
+    bg2 = dgl.batch(graphs)
+    hx = bg2.ndata["h"].clone().requires_grad_(True)
+    bg2.ndata["h"] = hx
+    gout = rng.randn(len(sizes), 3, 4).astype(F32)
+    d["in_readout_gout"] = gout
+    (dgl.sum_nodes(bg2, "h", "w") * t(gout)).sum().backward()
+    d["grad_sum_nodes_h_w"] = hx.grad.numpy().copy()
+    return d
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    for seed in range(2):
+        np.savez_compressed(os.path.join(OUT, "batched_%d.npz" % seed), **gen_batched(seed))
     for seed in range(2):
         np.savez_compressed(os.path.join(OUT, "traversal_%d.npz" % seed), **gen_traversal(seed))
     torch.manual_seed(0)

@@ -80,6 +80,14 @@ def test_traversal_and_propagation_against_reference_golden(cpu_mp, path):
     mp.test_propagation_against_reference(case)
 
 
+@pytest.mark.parametrize("path", sorted(glob.glob(os.path.join(GOLDEN, "batched_*.npz"))),
+                         ids=lambda p: os.path.basename(p))
+def test_batched_graph_readout_against_reference_golden(cpu_mp, path):
+    case = dict(np.load(path))
+    mp.test_batch_readout_unbatch_against_reference(case)
+    mp.test_readout_gradient_against_reference(case)
+
+
 def test_edge_ops_autograd_wiring(monkeypatch):
     from tests import test_uopv_edge_ops_gpu as eo
     monkeypatch.setattr(eo, "device", lambda: torch.device("cpu"))

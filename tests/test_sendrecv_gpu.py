@@ -326,3 +326,89 @@ def test_propagation_against_reference(trav):
     dgl_b200.prop_nodes_bfs(c, cu(trav["in_cyc_bfs_src"]), message_func=fn.copy_src("h", "m"),
                             reduce_func=fn.sum("m", "h"))
     close(c.ndata["h"], trav["cyc_prop_bfs_sum_h"], rtol=1e-4)
+
+
+# ---- batched graphs + per-graph readout (python/dgl/batched_graph.py) -------------------------------
+
+BATCHED = sorted(glob.glob(os.path.join(GOLDEN, "batched_*.npz")))
+
+
+@pytest.fixture(scope="module", params=BATCHED, ids=[os.path.basename(c) for c in BATCHED])
+def bcase(request):
+    return dict(np.load(request.param))
+
+
+def _component_graphs(case):
+    import dgl_b200
+    graphs = []
+    for i, (n, e) in enumerate(case["batch_sizes"].tolist()):
+        g = dgl_b200.DGLGraph()
+        g.add_nodes(n)
+        if e > 0:
+            g.add_edges(torch.from_numpy(case["g%d_src" % i]), torch.from_numpy(case["g%d_dst" % i]))
+        g.to(device())
+        g.ndata["h"], g.ndata["w"] = cu(case["in_g%d_h" % i]), cu(case["in_g%d_w" % i])
+        if e > 0:
+            g.edata["e"], g.edata["s"] = cu(case["in_g%d_e" % i]), cu(case["in_g%d_s" % i])
+        graphs.append(g)
+    return graphs
+
+
+def test_batch_readout_unbatch_against_reference(bcase):
+    import dgl_b200
+    from dgl_b200 import batched_graph as bgm
+    from dgl_b200 import function as fn
+    from dgl_b200.base import DGLError
+    bg = bgm.batch(_component_graphs(bcase))
+    assert bg.batch_size == len(bcase["batch_sizes"])
+    assert bg.batch_num_nodes == bcase["batch_num_nodes"].tolist()
+    assert bg.batch_num_edges == bcase["batch_num_edges"].tolist()
+    s, d = bg.edges()
+    assert np.array_equal(s.cpu().numpy(), bcase["batched_src"]) and np.array_equal(d.cpu().numpy(), bcase["batched_dst"])
+    close(bg.ndata["h"], bcase["batched_h"])
+    with pytest.raises(DGLError):
+        bg.add_nodes(1)
+    close(bgm.sum_nodes(bg, "h"), bcase["sum_nodes_h"])
+    close(bgm.sum_nodes(bg, "h", "w"), bcase["sum_nodes_h_w"])
+    close(bgm.mean_nodes(bg, "h"), bcase["mean_nodes_h"])
+    close(bgm.mean_nodes(bg, "h", "w"), bcase["mean_nodes_h_w"])
+    assert np.array_equal(bgm.max_nodes(bg, "h").cpu().numpy(), bcase["max_nodes_h"])     # max is bit-exact
+    close(bgm.sum_edges(bg, "e"), bcase["sum_edges_e"])
+    close(bgm.sum_edges(bg, "e", "s"), bcase["sum_edges_e_s"])
+    assert np.array_equal(bgm.max_edges(bg, "e").cpu().numpy(), bcase["max_edges_e"])
+    bg.update_all(fn.copy_src("h", "m"), fn.sum("m", "h"))
+    close(bg.ndata["h"], bcase["batched_update_all_h"])
+    close(bgm.sum_nodes(bg, "h"), bcase["sum_nodes_after_update"])
+    parts = bgm.unbatch(bg)
+    assert [p.number_of_nodes() for p in parts] == bcase["batch_num_nodes"].tolist()
+    assert [p.number_of_edges() for p in parts] == bcase["batch_num_edges"].tolist()
+    for i, p in enumerate(parts):
+        close(p.ndata["h"], bcase["unbatch%d_h" % i])
+        if p.number_of_edges():
+            ps, pd = p.edges()
+            assert np.array_equal(ps.cpu().numpy(), bcase["g%d_src" % i]) and np.array_equal(pd.cpu().numpy(), bcase["g%d_dst" % i])
+    # a single (unbatched) graph reads out over all of its nodes (batched_graph.py:397-399)
+    g0 = _component_graphs(bcase)[0]
+    close(bgm.sum_nodes(g0, "h"), bcase["sum_nodes_h"][0])
+    close(bgm.max_nodes(g0, "h"), bcase["max_nodes_h"][0])
+
+
+def test_readout_gradient_against_reference(bcase):
+    from dgl_b200 import batched_graph as bgm
+    bg = bgm.batch(_component_graphs(bcase))
+    hx = bg.ndata["h"].clone().requires_grad_(True)
+    bg.ndata["h"] = hx
+    (bgm.sum_nodes(bg, "h", "w") * cu(bcase["in_readout_gout"])).sum().backward()
+    close(hx.grad, bcase["grad_sum_nodes_h_w"])
+    # max readout routes the gradient to the arg-max node of every (graph, feature)
+    hx2 = bg.ndata["h"].detach().clone().requires_grad_(True)
+    bg.ndata["h"] = hx2
+    bgm.max_nodes(bg, "h").sum().backward()
+    ref = bg.ndata["h"].detach().clone().requires_grad_(True)
+    off, tot = 0, 0
+    for n_i in bg.batch_num_nodes:
+        if n_i:
+            tot = tot + ref[off:off + n_i].max(0)[0].sum()
+        off += n_i
+    tot.backward()
+    close(hx2.grad, ref.grad)
