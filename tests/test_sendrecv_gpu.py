@@ -411,4 +411,4 @@ def test_readout_gradient_against_reference(bcase):
             tot = tot + ref[off:off + n_i].max(0)[0].sum()
         off += n_i
     tot.backward()
-    close(hx2.grad, ref.grad)
+    close(hx2.grad, ref.grad.cpu().numpy())
