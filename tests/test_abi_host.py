@@ -29,6 +29,27 @@ def test_library_exports_every_declared_symbol():
     assert lib.dglb200_abi_version() == 1
 
 
+def test_plain_c_client_compiles_links_and_runs(tmp_path):
+    """The boundary is a C ABI: the header is valid C99 (and C++), and a C program that includes it
+    links against libdgl_b200.so and runs the argument-validating calls without a GPU."""
+    import shutil
+    import subprocess
+    from dgl_b200 import _lib
+    if shutil.which("gcc") is None:
+        pytest.skip("no gcc")
+    src = os.path.join(ROOT, "tests", "native", "abi_smoke.c")
+    libdir = os.path.dirname(_lib.lib_path())
+    exe = str(tmp_path / "abi_smoke")
+    subprocess.check_call(["gcc", "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror",
+                           "-I", os.path.join(ROOT, "include"), src, "-L", libdir, "-ldgl_b200",
+                           "-Wl,-rpath," + libdir, "-o", exe])
+    out = subprocess.check_output([exe]).decode()
+    assert "abi ok" in out
+    if shutil.which("g++") is not None:      # the same header from C++
+        subprocess.check_call(["g++", "-std=c++11", "-fsyntax-only", "-x", "c++", "-Wall", "-Werror",
+                               "-I", os.path.join(ROOT, "include"), src])
+
+
 def test_error_convention_no_gpu_needed():
     """0 / -1 + thread-local message (cf. DGLGetLastError, src/runtime/c_runtime_api.cc:130-148)."""
     from dgl_b200 import _lib
