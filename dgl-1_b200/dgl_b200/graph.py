@@ -406,6 +406,37 @@ class DGLGraph(object):
         idx = torch.cat([src, dst]) if transpose else torch.cat([dst, src])
         return idx, torch.arange(self._e, dtype=torch.int64, device=idx.device)
 
+    def adjacency_matrix(self, transpose=False, ctx=None):
+        """python/dgl/graph.py:2721-2742 -> GraphIndex.adjacency_matrix (graph_index.py:537-585): the
+        n x n torch sparse COO the reference hands to users, rows = destinations (sources when
+        transposed), one entry of 1.0 per edge in edge-id order (uncoalesced, as the reference's)."""
+        if not isinstance(transpose, bool):
+            raise DGLError('Expect bool value for "transpose" arg, but got %s.' % (type(transpose)))
+        idx, _ = self.adjacency_coo(transpose)
+        dat = torch.ones(self._e, dtype=torch.float32, device=idx.device)
+        adj = torch.sparse_coo_tensor(idx.view(2, self._e), dat, (self._n, self._n))
+        return adj if ctx is None else adj.to(ctx)
+
+    def incidence_matrix(self, typestr, ctx=None):
+        """python/dgl/graph.py:2744-2788 -> GraphIndex.incidence_matrix (graph_index.py:587-662):
+        n x E sparse COO; 'in': I[v, e] = 1 if v is the destination of e; 'out': if v is its source;
+        'both': +1 / -1 for in / out, self loops dropped."""
+        src, dst = self.edges()
+        eid = torch.arange(self._e, dtype=torch.int64, device=src.device)
+        if typestr == "in":
+            idx, dat = torch.stack([dst, eid]), torch.ones(self._e, device=src.device)
+        elif typestr == "out":
+            idx, dat = torch.stack([src, eid]), torch.ones(self._e, device=src.device)
+        elif typestr == "both":
+            keep = src != dst
+            s, d, e = src[keep], dst[keep], eid[keep]
+            idx = torch.stack([torch.cat([s, d]), torch.cat([e, e])])
+            dat = torch.cat([-torch.ones(s.numel(), device=src.device), torch.ones(s.numel(), device=src.device)])
+        else:
+            raise DGLError("Invalid incidence matrix type: %s" % str(typestr))
+        inc = torch.sparse_coo_tensor(idx, dat, (self._n, self._e))
+        return inc if ctx is None else inc.to(ctx)
+
     def apply_nodes(self, func="default", v=ALL, inplace=False):
         """python/dgl/graph.py:1800-1852."""
         from . import scheduler

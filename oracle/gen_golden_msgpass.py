@@ -135,6 +135,13 @@ def gen_case(seed):
     g.apply_edges(lambda edges: {"s": edges.src["h"] + edges.dst["h"]})
     d["apply_edges_all_s"] = g.edata["s"].numpy().copy()
 
+    # 8b. the sparse matrices handed to users (graph.py:2721-2788)
+    g = fresh()
+    d["adj_dense"] = g.adjacency_matrix().to_dense().numpy().copy()
+    d["adj_t_dense"] = g.adjacency_matrix(transpose=True).to_dense().numpy().copy()
+    for ty in ("in", "out", "both"):
+        d["inc_%s_dense" % ty] = g.incidence_matrix(ty).to_dense().numpy().copy()
+
     # 9. user initializers: zero-degree pull rows on the bucketing path, and the untouched rows of
     #    a column that a partial write creates
     g = fresh()

@@ -165,6 +165,17 @@ def test_subset_apply_nodes_and_edges(case):
     close(g.edata["s"], case["apply_edges_all_s"])
 
 
+def test_user_facing_sparse_matrices(case):
+    """DGLGraph.adjacency_matrix / incidence_matrix (graph.py:2721-2788) as dense, against the reference."""
+    g = fresh(case)
+    assert np.array_equal(g.adjacency_matrix().to_dense().cpu().numpy(), case["adj_dense"])
+    assert np.array_equal(g.adjacency_matrix(transpose=True).to_dense().cpu().numpy(), case["adj_t_dense"])
+    for ty in ("in", "out", "both"):
+        assert np.array_equal(g.incidence_matrix(ty).to_dense().cpu().numpy(), case["inc_%s_dense" % ty]), ty
+    g.drop_coo()                                   # answered from the CSRs alone
+    assert np.array_equal(g.adjacency_matrix().to_dense().cpu().numpy(), case["adj_dense"])
+
+
 def test_user_initializers(case):
     """tests/compute/test_basics.py:363-513: zero-degree rows on the bucketing path and the untouched
     rows of a column created by a partial write come from the user's initializer."""
