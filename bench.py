@@ -91,6 +91,8 @@ def cpu_reference(cfg, steps, warmup, budget_s=25.0, gcn=False):
     probe_e = min(cfg["e"], 2_000_000)
     src, dst = make_edges(cfg, "cpu", probe_e, probe_e / cfg["e"])
 
+    busy = [0.0]
+
     def one_pass(src, dst, reps):
         idx, _ = oracle.get_adj_coo(src.numpy(), dst.numpy())          # Graph::GetAdj "coo"
         e = src.shape[0]
@@ -98,12 +100,14 @@ def cpu_reference(cfg, steps, warmup, budget_s=25.0, gcn=False):
         x = torch.randn(n, feat, requires_grad=True)
         dy = torch.randn(n, feat)
         ts = []
+        c0 = time.process_time()
         for _ in range(reps):
             t0 = time.perf_counter()
             y = torch.sparse.mm(adj, x)
             y.backward(dy)
             ts.append(time.perf_counter() - t0)
             x.grad = None
+        busy[0] = (time.process_time() - c0) / max(sum(ts), 1e-9)     # CPU seconds per wall second
         return ts
 
     t_probe = min(one_pass(src, dst, 2))
@@ -118,8 +122,10 @@ def cpu_reference(cfg, steps, warmup, budget_s=25.0, gcn=False):
     gcn = gcn_epoch_cpu(src, dst, n, cfg) if (gcn and cfg["kind"] == "powerlaw") else None
     return dict(gcn_epoch=gcn, value=alg / t / 1e9, unit=UNIT, cores=cores, kind="port",
                 sample="th.sparse.mm(COO)+autograd bwd, fp32, N=%d F=%d, E=%d of %d edges (1/%.1f), "
-                       "%d timed passes, %.3f s/pass" % (n, feat, e_s, cfg["e"], cfg["e"] / e_s,
-                                                         len(ts), t),
+                       "%d timed passes, %.3f s/pass; %d torch threads offered, %.1f busy on average"
+                       % (n, feat, e_s, cfg["e"], cfg["e"] / e_s,
+                                                                  len(ts), t, cores, busy[0]),
+                effective_cores=round(busy[0], 2),
                 edge_feat_per_s=2 * e_s * feat / t, ms_per_step=t * 1e3, sample_edges=e_s)
 
 
@@ -136,7 +142,7 @@ def run_reference(args):
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": cfg["name"], "n": cfg["n"], "e": cfg["e"], "feat": cfg["feat"],
                    "sample_edges": r["sample_edges"]},
-        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "effective_cores", "kind", "sample")},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "edge_feat_per_s": r["edge_feat_per_s"], "gpu_launches": 0, "gcn_epoch": r["gcn_epoch"],
     }
@@ -666,7 +672,7 @@ def run_b200(args):
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_reference(cfg, 2, 1, budget_s=20.0)
-        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        cpu = {k: cpu[k] for k in ("value", "unit", "cores", "effective_cores", "kind", "sample")}
 
     if rank == 0:
         line = {
