@@ -102,9 +102,88 @@ gather_rows_multi_kernel(const MultiSrc ms, const int64_t* __restrict__ idx, int
   }
 }
 
+// Converting row gather for the reduced-precision WIRE mode of the halo exchange (dist.py,
+// DGL_B200_WIRE=bf16): TO_BF16 packs out[i, :] = bf16_rn(x[idx[i], :]) (the owner's push over NVLink
+// moves half the bytes), !TO_BF16 widens out[i, :] = float(x[idx[i], :]) (the receiver restores the
+// fp32 operand the SpMM reads).  A unit of work is 8 consecutive elements of one row: two 16-byte
+// fp32 accesses against one 16-byte bf16 access; rows whose width is not a multiple of 8 finish
+// element-wise.  Same grid-stride / max_ctas structure as gather_rows_kernel.
+template <bool TO_BF16>
+__global__ void __launch_bounds__(256)
+gather_rows_convert_kernel(int64_t n_out, const int64_t* __restrict__ idx, int64_t x_rows,
+                           const void* __restrict__ x_, int64_t x_ld, int64_t feat,
+                           void* __restrict__ out_, int64_t out_ld, int vec_ok,
+                           int32_t* __restrict__ bad) {
+  using In = typename std::conditional<TO_BF16, float, __nv_bfloat16>::type;
+  using Out = typename std::conditional<TO_BF16, __nv_bfloat16, float>::type;
+  const In* x = static_cast<const In*>(x_);
+  Out* out = static_cast<Out*>(out_);
+  const int64_t units = (feat + 7) / 8;
+  const int64_t total = n_out * units;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; u < total; u += stride) {
+    const int64_t row = u / units;
+    const int64_t f0 = (u - row * units) * 8;
+    const int64_t s = idx ? idx[row] : row;
+    if (s < 0 || s >= x_rows) {
+      atomicExch(bad, 1);
+      continue;
+    }
+    const In* src = x + s * x_ld + f0;
+    Out* dst = out + row * out_ld + f0;
+    if (vec_ok && f0 + 8 <= feat) {
+      if constexpr (TO_BF16) {
+        const float4 a = *reinterpret_cast<const float4*>(src);
+        const float4 b = *reinterpret_cast<const float4*>(src + 4);
+        uint4 t;
+        t.x = pack_bf16(a.x, a.y); t.y = pack_bf16(a.z, a.w);
+        t.z = pack_bf16(b.x, b.y); t.w = pack_bf16(b.z, b.w);
+        *reinterpret_cast<uint4*>(dst) = t;
+      } else {
+        const uint4 t = *reinterpret_cast<const uint4*>(src);
+        *reinterpret_cast<float4*>(dst) = make_float4(bf16_lo(t.x), bf16_hi(t.x), bf16_lo(t.y), bf16_hi(t.y));
+        *reinterpret_cast<float4*>(dst + 4) = make_float4(bf16_lo(t.z), bf16_hi(t.z), bf16_lo(t.w), bf16_hi(t.w));
+      }
+    } else {
+      const int64_t f1 = f0 + 8 < feat ? f0 + 8 : feat;
+      for (int64_t f = f0; f < f1; ++f) {
+        if constexpr (TO_BF16) dst[f - f0] = __float2bfloat16_rn(src[f - f0]);
+        else dst[f - f0] = __bfloat162float(src[f - f0]);
+      }
+    }
+  }
+}
+
 }  // namespace dglb200
 
 using namespace dglb200;
+
+extern "C" int dglb200_gather_rows_convert(int64_t n_out, const int64_t* idx, int64_t x_rows,
+                                           int to_bf16, const void* x, int64_t x_ld, int64_t feat,
+                                           void* out, int64_t out_ld, int32_t* bad_flag,
+                                           int max_ctas, void* stream_) {
+  clear_error();
+  DGLB200_REQUIRE(n_out >= 0 && x_rows >= 0 && feat >= 1, "gather_rows_convert: bad sizes");
+  DGLB200_REQUIRE(x_ld >= feat && out_ld >= feat, "gather_rows_convert: leading dimension < feat");
+  if (n_out == 0) return 0;
+  DGLB200_REQUIRE(x && out && bad_flag, "gather_rows_convert: NULL pointer");
+  // 16-byte accesses on both sides: bases aligned, leading dimensions multiples of 8 elements
+  const int vec_ok = (reinterpret_cast<uintptr_t>(x) % 16 == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0) &&
+                     x_ld % 8 == 0 && out_ld % 8 == 0;
+  const int64_t total = n_out * ((feat + 7) / 8);
+  int64_t blocks = ceil_div(total, 256);
+  if (max_ctas > 0 && blocks > max_ctas) blocks = max_ctas;
+  if (blocks > 148 * 64) blocks = 148 * 64;      // grid-stride: a few waves of the 148 SMs are enough
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  if (to_bf16)
+    gather_rows_convert_kernel<true><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, x, x_ld, feat, out,
+                                                                         out_ld, vec_ok, bad_flag);
+  else
+    gather_rows_convert_kernel<false><<<(unsigned)blocks, 256, 0, stream>>>(n_out, idx, x_rows, x, x_ld, feat, out,
+                                                                          out_ld, vec_ok, bad_flag);
+  DGLB200_POST_LAUNCH("gather_rows_convert_kernel");
+  return 0;
+}
 
 extern "C" int dglb200_gather_rows_multi(int n_src, const void* const* src_base_host,
                                          const int64_t* src_rows_host, const int64_t* seg_ptr_host,

@@ -77,6 +77,8 @@ SIGNATURES = {
     "dglb200_gather_rows": (c_int, [c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, c_vp, c_vp]),
     "dglb200_gather_rows_strided": (c_int, [c_i64, c_vp, c_i64, c_vp, c_i64, c_i64, c_vp, c_i64, c_vp,
                                             c_int, c_vp]),
+    "dglb200_gather_rows_convert": (c_int, [c_i64, c_vp, c_i64, c_int, c_vp, c_i64, c_i64, c_vp, c_i64, c_vp,
+                                            c_int, c_vp]),
     "dglb200_gather_rows_multi": (c_int, [c_int, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_vp, c_int, c_vp]),
     "dglb200_ipc_get_handle": (c_int, [c_vp, c_vp, ctypes.POINTER(c_i64)]),
     "dglb200_ipc_open": (c_int, [c_vp, ctypes.POINTER(c_vp)]),

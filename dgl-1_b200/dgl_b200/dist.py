@@ -32,6 +32,11 @@ ROW_WEIGHT = float(os.environ.get("DGL_B200_ROW_WEIGHT", "4.0"))
 # measured, C5 x 8 ranks (ms/step): perpeer 14.8, fused 18.4, push 14.5; x 2 ranks: push 26.6, push pipelined
 # in 4 row chunks with a 128-CTA push grid 24.7
 PULL_MODE = os.environ.get("DGL_B200_PULL", "push")
+# precision of the halo rows ON THE WIRE (push transport only): "f32" is the parity mode; "bf16" rounds
+# the pushed rows to bfloat16 (half the NVLink bytes: SURVEY.md 8e lever 2), the receiver widens them
+# back into its fp32 operand, accumulation stays fp32 - results within the 1e-2 bf16 tolerance.
+# Opt-in and NOT yet measured on the GPUs (added after this round's GPU budget was spent).
+WIRE = os.environ.get("DGL_B200_WIRE", "f32")
 PUSH_CTAS_PIPELINED = 128   # grid of a push that runs beside the SpMM of the previous row chunk
 TIMING = bool(int(os.environ.get("DGL_B200_TIMING", "0")))   # record events around the halo transfers
 COMM_PRIORITY = -1      # side stream of the pulls: higher priority than the compute stream
@@ -381,6 +386,7 @@ class HaloExchange(object):
         self.timing = []
         self._buf = None
         self._peer_buf = None
+        self._wire = self._peer_wire = None     # bf16 wire mode (enable_peer_transport)
         self._barrier = None
         self._comm = None
 
@@ -400,6 +406,14 @@ class HaloExchange(object):
         buf = self.buffer(feat, like)
         self._peer_buf = share_with_peers(buf, self.rank, self.world, self.group)
         self._barrier = StreamBarrier(like.device, self.group)
+        self._wire = self._peer_wire = None
+        if WIRE == "bf16" and PULL_MODE == "push" and buf.dtype == torch.float32:
+            # halo rows arrive here as bf16 (written by their owners) and are widened into `buf`
+            self._wire = torch.empty((max(self.n_halo, 1), feat), dtype=torch.bfloat16, device=like.device)
+            self._peer_wire = share_with_peers(self._wire, self.rank, self.world, self.group)
+            rows_all = [None] * self.world
+            dist.all_gather_object(rows_all, self.rows, group=self.group)
+            self._rows_of_rank = rows_all
 
     def row_chunks(self):
         """The remapped CSR cut into the plan's row chunks (views; each with its own long-row plan)."""
@@ -429,8 +443,13 @@ class HaloExchange(object):
                 r = (self.rank + j) % self.world
                 if sc[r]:
                     d0 = self.push_dst[k][r]
-                    ops.gather_rows(buf[:self.rows], self.serve_local[k][seg[r]:seg[r + 1]],
-                                    out=self._peer_buf[r][d0:d0 + sc[r]], max_ctas=ctas)
+                    if self._peer_wire is not None:
+                        h0 = d0 - self._rows_of_rank[r]          # position inside r's halo region
+                        ops.gather_rows_convert(buf[:self.rows], self.serve_local[k][seg[r]:seg[r + 1]],
+                                                out=self._peer_wire[r][h0:h0 + sc[r]], max_ctas=ctas)
+                    else:
+                        ops.gather_rows(buf[:self.rows], self.serve_local[k][seg[r]:seg[r + 1]],
+                                        out=self._peer_buf[r][d0:d0 + sc[r]], max_ctas=ctas)
             return
         if self._peer_buf is not None:
             # one launch pulls this chunk's rows from every owner at once (NVLink peer loads)
@@ -452,6 +471,17 @@ class HaloExchange(object):
         dist.all_to_all_single(buf[start:start + sum(cnts)], send, output_split_sizes=cnts,
                                input_split_sizes=self.send_counts[k], group=self.group)
 
+    def _widen_chunk(self, k, buf):
+        """bf16 wire mode: chunk k's halo rows have landed in the bf16 staging buffer; widen them
+        into the fp32 operand (local HBM traffic only)."""
+        if self._wire is None:
+            return
+        cnt = sum(self.recv_counts[k])
+        if cnt:
+            h0 = self.chunk_start[k] - self.rows
+            ops.gather_rows_convert(self._wire[h0:h0 + cnt], None,
+                                    out=buf[self.chunk_start[k]:self.chunk_start[k] + cnt])
+
     def exchange(self, x_local):
         """Unpipelined: returns the compact buffer with own rows and every halo row."""
         buf = self.buffer(x_local.shape[1], x_local)
@@ -472,6 +502,8 @@ class HaloExchange(object):
             self.timing.append((a, b))
         if self._barrier is not None:
             self._barrier()
+        for k in range(self.chunks):
+            self._widen_chunk(k, buf)
         return buf
 
     def aggregate(self, x_local, spmm_fn, out):
@@ -541,6 +573,7 @@ class HaloExchange(object):
                     b.record()
                     self.timing.append((a, b))
                 self._barrier()               # chunk k's halo has landed everywhere
+                self._widen_chunk(k, buf)
                 ev = torch.cuda.Event()
                 ev.record(self._comm)
                 events.append(ev)
@@ -579,6 +612,8 @@ class HaloPartition(RowPartition):
         return self._halo(key).buffer(feat, like)
 
     def exchange_bytes(self, feat, elem=4):
+        if self.halo_in._wire is not None:
+            elem = 2
         return max(self.halo_in.n_halo, self.halo_out.n_halo) * feat * elem
 
     def forward(self, x_local, out=None, key="x"):

@@ -463,6 +463,44 @@ def gather_rows(x, idx, out=None, max_ctas=0):
     return ret
 
 
+def gather_rows_convert(x, idx, out, max_ctas=0):
+    """out[i] = x[idx[i]] (or x[i] when idx is None) converted float32 -> bfloat16 (round to nearest
+    even) or bfloat16 -> float32 (dglb200_gather_rows_convert).  2-D tensors with unit inner stride;
+    `out` may alias a peer GPU's mapped memory.  The reduced-precision wire mode of dist.py."""
+    lib = _lib.get_lib()
+    _need_cuda(x, idx, out)
+    if (x.dtype, out.dtype) == (torch.float32, torch.bfloat16):
+        to_bf16 = 1
+    elif (x.dtype, out.dtype) == (torch.bfloat16, torch.float32):
+        to_bf16 = 0
+    else:
+        raise DGLError("gather_rows_convert: needs float32 -> bfloat16 or bfloat16 -> float32, got %s -> %s"
+                       % (x.dtype, out.dtype))
+    if x.dim() != 2 or out.dim() != 2 or x.shape[1] != out.shape[1]:
+        raise DGLError("gather_rows_convert: x and out must be 2-D with the same width")
+    if (x.shape[1] > 1 and x.stride(1) != 1) or (out.shape[1] > 1 and out.stride(1) != 1):
+        raise DGLError("gather_rows_convert: unit inner stride required")
+    n_out = int(idx.shape[0]) if idx is not None else int(x.shape[0])
+    if int(out.shape[0]) != n_out:
+        raise DGLError("gather_rows_convert: out has %d rows, expected %d" % (out.shape[0], n_out))
+    if idx is not None:
+        idx = idx.contiguous()
+        if idx.dtype != torch.int64:
+            raise DGLError("gather_rows_convert: ids must be int64")
+    feat = int(x.shape[1])
+    x_ld = int(x.stride(0)) if x.shape[0] > 1 else feat
+    o_ld = int(out.stride(0)) if n_out > 1 else feat
+    dev = out.device
+    bad = _BAD_FLAGS.get(dev)
+    if bad is None:
+        bad = _BAD_FLAGS[dev] = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_gather_rows_convert(n_out, _ptr(idx), int(x.shape[0]), to_bf16, _ptr(x),
+                                                        max(x_ld, feat), feat, _ptr(out), max(o_ld, feat),
+                                                        _ptr(bad), int(max_ctas), _stream()))
+    return out
+
+
 def gather_rows_multi(sources, seg_ptr, idx, out, max_ctas=0):
     """out[i] = sources[q][idx[i]] for seg_ptr[q] <= i < seg_ptr[q+1] (dglb200_gather_rows_multi):
     one launch that pulls from several (peer) tensors at once.  sources: dense 2-D tensors of equal

@@ -322,6 +322,19 @@ int dglb200_gather_rows_multi(int n_src, const void* const* src_base_host, const
                               const int64_t* seg_ptr_host, const int64_t* idx, int64_t row_bytes,
                               void* out, int32_t* bad_flag, int max_ctas, void* stream);
 
+/*
+ * Converting row gather for the reduced-precision WIRE mode of the halo exchange (no counterpart in
+ * the reference, which has no multi-GPU layer; SURVEY.md 8e lever 2 "bf16 on the wire, fp32
+ * accumulate").  to_bf16 != 0: x is float, out is bf16, out[i, :] = round_to_nearest_even(x[idx[i], :]);
+ * to_bf16 == 0: x is bf16, out is float (exact widening).  x_ld / out_ld are leading dimensions in
+ * ELEMENTS; idx == NULL converts row i to row i.  `out` may be a peer GPU's mapped memory (push).
+ * Off by default (DGL_B200_WIRE=bf16 selects it); the fp32 wire is the parity mode.
+ */
+int dglb200_gather_rows_convert(int64_t n_out, const int64_t* idx, int64_t x_rows, int to_bf16,
+                                const void* x, int64_t x_ld, int64_t feat,
+                                void* out, int64_t out_ld, int32_t* bad_flag,
+                                int max_ctas, void* stream);
+
 /* ---- CUDA IPC (multi-GPU peer-load exchange) ------------------------------------------------- */
 
 /*
