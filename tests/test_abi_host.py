@@ -50,6 +50,27 @@ def test_plain_c_client_compiles_links_and_runs(tmp_path):
                                "-I", os.path.join(ROOT, "include"), src])
 
 
+def test_converting_gather_kernel_source_runs_under_host_shim(tmp_path):
+    """The CUDA source of gather_rows_convert_kernel (no warp primitives) executed on the CPU under a
+    minimal host shim: bit-exact float32 -> bfloat16 (RNE) and exact widening over vector and scalar
+    paths, strides, gathers and out-of-range ids.  Complements the -m gpu test of the same kernel."""
+    import shutil
+    import subprocess
+    if shutil.which("g++") is None:
+        pytest.skip("no g++")
+    src = open(os.path.join(ROOT, "dgl-1_b200", "csrc", "gather.cu")).read()
+    a = src.index("template <bool TO_BF16>")
+    kernel = src[a:src.index("}  // namespace dglb200", a)]
+    nat = os.path.join(ROOT, "tests", "native")
+    cpp = tmp_path / "emu.cpp"
+    cpp.write_text(open(os.path.join(nat, "emu_gather_convert_shim.inc")).read() + kernel +
+                   open(os.path.join(nat, "emu_gather_convert_main.inc")).read())
+    exe = str(tmp_path / "emu")
+    subprocess.check_call(["g++", "-O1", "-std=c++17", "-w", str(cpp), "-o", exe])
+    out = subprocess.check_output([exe]).decode()
+    assert "fails=0" in out, out
+
+
 def test_error_convention_no_gpu_needed():
     """0 / -1 + thread-local message (cf. DGLGetLastError, src/runtime/c_runtime_api.cc:130-148)."""
     from dgl_b200 import _lib
