@@ -109,6 +109,17 @@ def share_with_peers(t, rank, world, group=None):
     return peers
 
 
+def close_peer_mappings():
+    """Unmap every peer buffer this process opened with share_with_peers (dglb200_ipc_close).  Call it
+    once the tensors returned by share_with_peers are no longer used (e.g. before tearing a
+    partition down in a long-lived process); process exit unmaps them anyway."""
+    from . import _lib
+    lib = _lib.get_lib()
+    while _OPEN_HANDLES:
+        ptr = _OPEN_HANDLES.pop()
+        _lib.check_call(lib.dglb200_ipc_close(ptr))
+
+
 class StreamBarrier(object):
     """Cross-rank barrier in STREAM order (no host stall): a 1-element all-reduce.  Every rank's
     kernels enqueued before it are complete before any rank's kernels enqueued after it start."""

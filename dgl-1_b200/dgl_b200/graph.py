@@ -104,6 +104,8 @@ class DGLGraph(object):
             v = v.expand(u.numel())
         if u.numel() != v.numel():
             raise DGLError("add_edges: u and v have different lengths")
+        if self._e > 0 and self._src is None:
+            self._src, self._dst = self.edges()     # the edge list was dropped: recover it from the CSRs
         if self._e == 0:
             self._src, self._dst = u.contiguous(), v.contiguous()
         else:
@@ -118,6 +120,8 @@ class DGLGraph(object):
     def to(self, device):
         """Move the structure to `device` (features are moved by the user, as in the reference)."""
         device = torch.device(device)
+        if self._e > 0 and self._src is None:
+            self._src, self._dst = self.edges()     # dropped edge list: recover before the cache goes
         self._device = device
         if self._src is not None:
             self._src = self._src.to(device)

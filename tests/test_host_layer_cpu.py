@@ -56,7 +56,7 @@ MP_BODIES = [mp.test_send_then_recv_builtin_reducers, mp.test_send_then_recv_udf
              mp.test_consecutive_sends_partial_recv, mp.test_send_all_recv_all_equals_update_all,
              mp.test_recv_without_pending_messages_is_apply, mp.test_pair_specifications_on_multigraph,
              mp.test_push_with_apply, mp.test_subset_apply_nodes_and_edges, mp.test_user_initializers,
-             mp.test_user_facing_sparse_matrices]
+             mp.test_user_facing_sparse_matrices, mp.test_structure_changes_after_drop_coo]
 
 
 @pytest.fixture()

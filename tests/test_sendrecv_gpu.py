@@ -176,6 +176,29 @@ def test_user_facing_sparse_matrices(case):
     assert np.array_equal(g.adjacency_matrix().to_dense().cpu().numpy(), case["adj_dense"])
 
 
+def test_structure_changes_after_drop_coo(case):
+    """add_edges / to() after the edge list was dropped recover it from the CSRs first."""
+    from dgl_b200 import function as fn
+    g = fresh(case)
+    g.in_csr(), g.out_csr()
+    g.drop_coo()
+    n = g.number_of_nodes()
+    g.add_edges(torch.tensor([0, 1]), torch.tensor([2, 2]))
+    s, d = g.edges()
+    assert np.array_equal(s.cpu().numpy(), np.concatenate([case["src"], [0, 1]]))
+    assert np.array_equal(d.cpu().numpy(), np.concatenate([case["dst"], [2, 2]]))
+    g.in_csr()
+    g.drop_coo()
+    g.to(device())
+    assert g.number_of_edges() == len(case["src"]) + 2
+    g.ndata["h"] = cu(case["in_x"])
+    g.update_all(fn.copy_src("h", "m"), fn.sum("m", "y"))
+    want = np.zeros_like(case["in_x"])
+    np.add.at(want, np.concatenate([case["dst"], [2, 2]]), case["in_x"][np.concatenate([case["src"], [0, 1]])])
+    close(g.ndata["y"], want)
+    assert n == g.number_of_nodes()
+
+
 def test_user_initializers(case):
     """tests/compute/test_basics.py:363-513: zero-degree rows on the bucketing path and the untouched
     rows of a column created by a partial write come from the user's initializer."""
