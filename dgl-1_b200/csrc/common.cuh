@@ -74,24 +74,38 @@ struct Workspace {
 
 // Structure arrays (column ids, edge ids) are read once per launch: bypass L1 so they do not
 // evict feature rows that hub sources keep hot.
+// (DGLB200_HOST_EMU: tests/native/cuda_emu compiles these sources for the host to run the kernels'
+// logic without a GPU; the PTX below then reads as the plain C it stands for.)
 __device__ __forceinline__ int32_t ld_stream_i32(const int32_t* p) {
+#ifdef DGLB200_HOST_EMU
+  return *p;
+#else
   int32_t v;
   asm volatile("ld.global.nc.L1::no_allocate.s32 %0, [%1];" : "=r"(v) : "l"(p));
   return v;
+#endif
 }
 __device__ __forceinline__ int64_t ld_stream_i64(const int64_t* p) {
+#ifdef DGLB200_HOST_EMU
+  return *p;
+#else
   int64_t v;
   asm volatile("ld.global.nc.L1::no_allocate.s64 %0, [%1];" : "=l"(v) : "l"(p));
   return v;
+#endif
 }
 
 // base + id * row_bytes as ONE instruction (IMAD.WIDE.U32 with a 64-bit addend).  Written in PTX
 // because the compiler otherwise splits a uniform base from the per-lane offset (3 instructions
 // per gathered row in the SpMM inner loop).
 __device__ __forceinline__ const char* row_ptr(const char* base, uint32_t id, uint32_t row_bytes) {
+#ifdef DGLB200_HOST_EMU
+  return base + (uint64_t)id * (uint64_t)row_bytes;
+#else
   uint64_t r;
   asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(id), "r"(row_bytes), "l"(base));
   return reinterpret_cast<const char*>(r);
+#endif
 }
 
 __device__ __forceinline__ float bf16_lo(uint32_t u) { return __uint_as_float(u << 16); }
