@@ -160,13 +160,18 @@ class Pool {
   uint64_t gen_ = 0;
 };
 
+inline std::mutex& launch_mutex() { static std::mutex m; return m; }
+
 template <typename K>
 void launch(dim3 grid, dim3 block, K kernel) {
-  gridDim = grid;
-  blockDim = block;
   const int threads = (int)(block.x * block.y * block.z);
   const long long n_blocks = (long long)grid.x * grid.y * grid.z;
   if (threads <= 0 || n_blocks <= 0) return;
+  // one launch at a time: the model's state (blockIdx, the current block, the pool) is global, and
+  // tests may call the library from several host threads (ranks of a partition as threads)
+  std::lock_guard<std::mutex> one_launch(launch_mutex());
+  gridDim = grid;
+  blockDim = block;
   // the blocks run one after another on the pool, each with fresh rendezvous objects (lanes that
   // exit early drop out of THEIR block's barriers only)
   std::barrier<> turn(threads);
