@@ -91,10 +91,14 @@ def rewrite_launches(text):
         pos = a1
 
 
-def build(out_dir=None):
-    """Returns the path of the host-emulation library, (re)building it when the sources changed."""
+def build(out_dir=None, sanitize=None):
+    """Returns the path of the host-emulation library, (re)building it when the sources changed.
+    sanitize="address": AddressSanitizer build (every out-of-bounds access of a kernel aborts; the
+    process that loads it must preload libasan, see tests/test_kernels_host_emu.py)."""
+    sanitize = sanitize or os.environ.get("DGLB200_EMU_SANITIZE") or None
     srcs = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh")))
     h = hashlib.sha1()
+    h.update(str(sanitize).encode())
     for f in srcs + ["cuda_runtime.h", "cuda_bf16.h", "build.py"]:
         p = os.path.join(CSRC, f) if f in srcs else os.path.join(HERE, f)
         h.update(open(p, "rb").read())
@@ -116,6 +120,8 @@ def build(out_dir=None):
             cpps.append(os.path.join(work, name))
     flags = ["g++", "-std=c++20", "-O1", "-fPIC", "-pthread", "-w", "-DDGLB200_HOST_EMU",
              "-I", HERE, "-I", work, "-I", os.path.join(ROOT, "include")]
+    san = ["-fsanitize=%s" % sanitize, "-fno-omit-frame-pointer", "-g"] if sanitize else []
+    flags += san
     tls = os.path.join(work, "emu_state.cpp")
     with open(tls, "w") as fh:
         fh.write('#include "cuda_runtime.h"\nthread_local dim3 threadIdx;\ndim3 blockIdx, blockDim, gridDim;\n')
@@ -132,7 +138,7 @@ def build(out_dir=None):
             raise RuntimeError("host build of %s failed:\n%s" % (os.path.basename(c), log[-6000:]))
     # -Bsymbolic: the real libdgl_b200.so may be loaded RTLD_GLOBAL in the same process and defines the
     # same symbols; this library must bind its internal references to its own definitions
-    subprocess.check_call(["g++", "-shared", "-pthread", "-Wl,-Bsymbolic", "-o",
+    subprocess.check_call(["g++", "-shared", "-pthread", "-Wl,-Bsymbolic"] + san + ["-o",
                            os.path.join(work, "libdgl_b200_emu.so")] + objs + ["-ldl"])
     if os.path.isdir(out_dir):
         shutil.rmtree(work, ignore_errors=True)
