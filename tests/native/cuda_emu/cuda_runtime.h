@@ -80,8 +80,19 @@ namespace dglb200_emu {
 struct Warp {
   std::barrier<> bar;
   uint64_t slot[32];
+  std::atomic<unsigned> exited{0};   // bit l set: lane l returned from the kernel
   explicit Warp(int lanes) : bar(lanes) { memset(slot, 0, sizeof(slot)); }
 };
+// DGLB200_EMU_STRICT=1: a warp collective whose MASK names a lane that has already returned from
+// the kernel is undefined on the hardware; report it instead of letting the lane silently drop out.
+inline bool strict() { static const bool s = getenv("DGLB200_EMU_STRICT") != nullptr; return s; }
+inline void check_converged(Warp& w, unsigned mask, const char* what) {
+  const unsigned gone = w.exited.load(std::memory_order_relaxed) & mask;
+  if (strict() && gone != 0) {
+    fprintf(stderr, "cuda_emu: %s with mask %08x names exited lane(s) %08x (divergent collective)\n", what, mask, gone);
+    abort();
+  }
+}
 struct Block {
   std::barrier<> bar;
   std::vector<std::unique_ptr<Warp>> warps;
@@ -104,9 +115,10 @@ inline Warp& warp() { return *cur_block()->warps[threadIdx.x >> 5]; }
 
 // all lanes of the warp publish a value, then every lane reads what it needs
 template <typename T, typename F>
-inline auto exchange(T v, F read) {
+inline auto exchange(unsigned mask, T v, F read) {
   static_assert(sizeof(T) <= 8, "shuffle of > 8 bytes");
   Warp& w = warp();
+  check_converged(w, mask, "warp collective");
   uint64_t raw = 0;
   memcpy(&raw, &v, sizeof(T));
   w.slot[lane_id()] = raw;
@@ -186,6 +198,7 @@ void launch(dim3 grid, dim3 block, K kernel) {
       }
       turn.arrive_and_wait();
       kernel();
+      blk->warps[t >> 5]->exited.fetch_or(1u << (t & 31), std::memory_order_relaxed);
       blk->warps[t >> 5]->bar.arrive_and_drop();
       blk->bar.arrive_and_drop();
       turn.arrive_and_wait();
@@ -197,37 +210,40 @@ void launch(dim3 grid, dim3 block, K kernel) {
 
 // ---- synchronisation + warp collectives -----------------------------------------------------------
 inline void __syncthreads() { dglb200_emu::cur_block()->bar.arrive_and_wait(); }
-inline void __syncwarp(unsigned = 0xffffffffu) { dglb200_emu::warp().bar.arrive_and_wait(); }
+inline void __syncwarp(unsigned mask = 0xffffffffu) {
+  dglb200_emu::check_converged(dglb200_emu::warp(), mask, "__syncwarp");
+  dglb200_emu::warp().bar.arrive_and_wait();
+}
 
 template <typename T>
-inline T __shfl_sync(unsigned, T v, int src, int width = 32) {
+inline T __shfl_sync(unsigned mask, T v, int src, int width = 32) {
   const int lane = dglb200_emu::lane_id();
   const int base = lane / width * width;
-  return dglb200_emu::exchange(v, [&](auto get) { return get(base + (((src % width) + width) % width)); });
+  return dglb200_emu::exchange(mask, v, [&](auto get) { return get(base + (((src % width) + width) % width)); });
 }
 template <typename T>
-inline T __shfl_xor_sync(unsigned, T v, int mask, int width = 32) {
+inline T __shfl_xor_sync(unsigned lanes, T v, int mask, int width = 32) {
   const int lane = dglb200_emu::lane_id();
   const int base = lane / width * width;
   const int peer = lane ^ mask;
-  return dglb200_emu::exchange(v, [&](auto get) { return (peer >= base && peer < base + width) ? get(peer) : get(lane); });
+  return dglb200_emu::exchange(lanes, v, [&](auto get) { return (peer >= base && peer < base + width) ? get(peer) : get(lane); });
 }
 template <typename T>
-inline T __shfl_up_sync(unsigned, T v, unsigned delta, int width = 32) {
+inline T __shfl_up_sync(unsigned mask, T v, unsigned delta, int width = 32) {
   const int lane = dglb200_emu::lane_id();
   const int base = lane / width * width;
   const int peer = lane - (int)delta;
-  return dglb200_emu::exchange(v, [&](auto get) { return peer >= base ? get(peer) : get(lane); });
+  return dglb200_emu::exchange(mask, v, [&](auto get) { return peer >= base ? get(peer) : get(lane); });
 }
 template <typename T>
-inline T __shfl_down_sync(unsigned, T v, unsigned delta, int width = 32) {
+inline T __shfl_down_sync(unsigned mask, T v, unsigned delta, int width = 32) {
   const int lane = dglb200_emu::lane_id();
   const int base = lane / width * width;
   const int peer = lane + (int)delta;
-  return dglb200_emu::exchange(v, [&](auto get) { return peer < base + width ? get(peer) : get(lane); });
+  return dglb200_emu::exchange(mask, v, [&](auto get) { return peer < base + width ? get(peer) : get(lane); });
 }
 inline unsigned __ballot_sync(unsigned mask, int pred) {
-  return dglb200_emu::exchange((int)(pred != 0), [&](auto get) {
+  return dglb200_emu::exchange(mask, (int)(pred != 0), [&](auto get) {
     unsigned m = 0;
     for (int l = 0; l < 32; ++l) if ((mask >> l) & 1u) m |= (get(l) ? 1u : 0u) << l;
     return m;
@@ -235,17 +251,17 @@ inline unsigned __ballot_sync(unsigned mask, int pred) {
 }
 template <typename T>
 inline unsigned __match_any_sync(unsigned mask, T v) {
-  return dglb200_emu::exchange(v, [&](auto get) {
+  return dglb200_emu::exchange(mask, v, [&](auto get) {
     unsigned m = 0;
     for (int l = 0; l < 32; ++l) if (((mask >> l) & 1u) && get(l) == v) m |= 1u << l;
     return m;
   });
 }
 inline int __reduce_max_sync(unsigned mask, int v) {
-  return dglb200_emu::exchange(v, [&](auto get) { int r = v; for (int l = 0; l < 32; ++l) if ((mask >> l) & 1u) { int o = get(l); if (o > r) r = o; } return r; });
+  return dglb200_emu::exchange(mask, v, [&](auto get) { int r = v; for (int l = 0; l < 32; ++l) if ((mask >> l) & 1u) { int o = get(l); if (o > r) r = o; } return r; });
 }
 inline int __reduce_min_sync(unsigned mask, int v) {
-  return dglb200_emu::exchange(v, [&](auto get) { int r = v; for (int l = 0; l < 32; ++l) if ((mask >> l) & 1u) { int o = get(l); if (o < r) r = o; } return r; });
+  return dglb200_emu::exchange(mask, v, [&](auto get) { int r = v; for (int l = 0; l < 32; ++l) if ((mask >> l) & 1u) { int o = get(l); if (o < r) r = o; } return r; });
 }
 inline unsigned __activemask() { return 0xffffffffu; }
 
