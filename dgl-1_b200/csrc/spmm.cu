@@ -53,7 +53,7 @@ __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, i
     const float v = partial[c * feat + f];
     if (RED == DGLB200_RED_SUM) {
       acc += v;
-    } else if (c == c0 || v > acc) {
+    } else if (c == c0 || v > acc || (v != v && acc == acc)) {  // NaN is sticky, as in the kernel
       acc = v;
       if (partial_arg) best = partial_arg[c * feat + f];
     }

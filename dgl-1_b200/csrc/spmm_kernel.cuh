@@ -315,8 +315,11 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
           }
           if (!kMax) {
             acc[t][v] += m;
-          } else if (ok && m > acc[t][v]) {  // strict '>': earliest slot wins ties; acc starts at -inf,
-            acc[t][v] = m;                   // an all -inf row is settled in the epilogue
+          } else if (ok && (m > acc[t][v] || (m != m && acc[t][v] == acc[t][v]))) {
+            // strict '>': earliest slot wins ties; acc starts at -inf, an all -inf row is settled in
+            // the epilogue.  NaN is sticky (the first NaN message wins and stays), like torch.max over
+            // the mailbox in the reference's reducer (function/reducer.py:45-46).
+            acc[t][v] = m;
             best[t][v] = st.e[k];
           }
         }
@@ -441,8 +444,11 @@ int launch_one(const SpmmArgs& a, cudaStream_t stream) {
   const int64_t row_warps = ceil_div(a.n_rows, RPW);
   const int64_t avg_deg = a.n_rows > 0 ? a.nnz / a.n_rows : 0;
   int rpg = avg_deg >= 32 ? 1 : (avg_deg >= 16 ? 2 : (avg_deg >= 8 ? 4 : (avg_deg >= 4 ? 8 : 16)));
-  if (spmm_tuning().rows_per_group > 0) rpg = spmm_tuning().rows_per_group;
-  while (rpg > 1 && row_warps / rpg < 148 * 32) rpg >>= 1;
+  if (spmm_tuning().rows_per_group > 0) {
+    rpg = spmm_tuning().rows_per_group;      // explicit knob: taken as is (tests force it on small graphs)
+  } else {
+    while (rpg > 1 && row_warps / rpg < 148 * 32) rpg >>= 1;
+  }
   args.rows_per_group = rpg;
   const int64_t warps = args.n_chunk_warps + ceil_div(row_warps, rpg);
   const int64_t blocks = ceil_div(warps, NT / 32);

@@ -83,6 +83,10 @@ SIGNATURES = {
     "dglb200_ipc_get_handle": (c_int, [c_vp, c_vp, ctypes.POINTER(c_i64)]),
     "dglb200_ipc_open": (c_int, [c_vp, ctypes.POINTER(c_vp)]),
     "dglb200_ipc_close": (c_int, [c_vp]),
+    "dglb200_peer_push": (c_int, [c_int, c_vp, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64, c_i64, c_i64, c_int,
+                                  c_vp, c_int, c_i32, c_i32, c_vp, c_vp, c_vp, c_int, c_int, c_vp]),
+    "dglb200_peer_signal": (c_int, [c_int, c_vp, c_i32, c_vp]),
+    "dglb200_peer_wait": (c_int, [c_vp, c_int, c_i32, c_vp, c_vp]),
     "dglb200_register_packed_funcs": (c_int, [c_vp, c_int]),
 }
 

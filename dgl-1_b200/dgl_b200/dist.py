@@ -16,6 +16,7 @@ import torch
 import torch.distributed as dist
 
 from . import ops
+from .base import DGLError
 
 
 # CTAs of a peer pull (max_ctas of the gather kernels; 0 = full grid).  Measured on C5: a pull needs
@@ -26,20 +27,33 @@ from . import ops
 PULL_CTAS = int(os.environ.get("DGL_B200_PULL_CTAS", "0"))
 # weight of a row relative to an edge in the partition balance (2 SpMMs per step write every row once)
 ROW_WEIGHT = float(os.environ.get("DGL_B200_ROW_WEIGHT", "4.0"))
-# halo transport over the mapped peer buffers: "perpeer" = one PULL launch per owner in a rotating order
-# (every owner serves exactly one puller at a time), "fused" = one pull launch over all owners, "push" =
-# the owner gathers and STORES into the requester's buffer (posted NVLink writes)
-# measured, C5 x 8 ranks (ms/step): perpeer 14.8, fused 18.4, push 14.5; x 2 ranks: push 26.6, push pipelined
-# in 4 row chunks with a 128-CTA push grid 24.7
-PULL_MODE = os.environ.get("DGL_B200_PULL", "push")
-# precision of the halo rows ON THE WIRE (push transport only): "f32" is the parity mode; "bf16" rounds
+# Transport over the mapped peer buffers:
+#   "signal"  (default) ONE push launch per chunk stores this rank's rows into EVERY peer's buffer over
+#             NVLink and then sets a flag word in each peer's memory; the consumer's stream waits on its
+#             own flag words (dglb200_peer_push / peer_wait / peer_signal).  No NCCL call, no stream
+#             barrier and no host round trip on the data path; pushes of chunk k+1 run on a high-priority
+#             side stream beside the SpMM of chunk k.
+#   "push"    round 1: the owner gathers and STORES into the requester's buffer, one launch per peer in
+#             a rotating order, chunks separated by stream-ordered NCCL barriers (1-element all-reduce)
+#   "perpeer" one PULL launch per owner in a rotating order; "fused": one pull launch over all owners
+# measured, C5 x 8 ranks (ms/step, round 1): perpeer 14.8, fused 18.4, push 14.5, push pipelined 11.3
+PULL_MODE = os.environ.get("DGL_B200_PULL", "signal")
+# precision of the halo rows ON THE WIRE (push transports only): "f32" is the parity mode; "bf16" rounds
 # the pushed rows to bfloat16 (half the NVLink bytes: SURVEY.md 8e lever 2), the receiver widens them
 # back into its fp32 operand, accumulation stays fp32 - results within the 1e-2 bf16 tolerance.
-# Opt-in and NOT yet measured on the GPUs (added after this round's GPU budget was spent).
 WIRE = os.environ.get("DGL_B200_WIRE", "f32")
-PUSH_CTAS_PIPELINED = 128   # grid of a push that runs beside the SpMM of the previous row chunk
+PUSH_CTAS_PIPELINED = 128   # "push" mode: grid of a push that runs beside the SpMM of the previous row chunk
+PUSH_CTAS = int(os.environ.get("DGL_B200_PUSH_CTAS", "0"))   # "signal" mode: grid bound of a push (0 = 2 CTAs per SM)
 TIMING = bool(int(os.environ.get("DGL_B200_TIMING", "0")))   # record events around the halo transfers
-COMM_PRIORITY = -1      # side stream of the pulls: higher priority than the compute stream
+COMM_PRIORITY = -1      # side stream of the exchange: higher priority than the compute stream
+ALLGATHER_SLAB = int(os.environ.get("DGL_B200_AG_SLAB", "64"))   # feature-slab width (elements) of the pipelined all-gather
+
+
+def transport_name(exchange):
+    """Human-readable name of the peer transport in use (bench.py's `config.parallelism`)."""
+    if PULL_MODE == "signal":
+        return "push + flag signals (own kernels, no NCCL on the data path)"
+    return PULL_MODE if exchange == "halo" else "block copies between NCCL stream barriers"
 
 
 def edge_balanced_bounds(indptr_in, indptr_out, parts):
@@ -73,15 +87,16 @@ class _RawCuda(object):
 
 _TYPESTR = {torch.float32: ("<f4", None), torch.bfloat16: ("<u2", torch.bfloat16),
             torch.int64: ("<i8", None), torch.int32: ("<i4", None)}
-_OPEN_HANDLES = []
+_OPEN_HANDLES = {}        # IPC handle bytes -> mapped base pointer (one mapping per exporter allocation)
 
 
 def share_with_peers(t, rank, world, group=None):
     """Map every rank's contiguous CUDA tensor `t` into every other rank's address space with CUDA
     IPC (dglb200_ipc_get_handle / dglb200_ipc_open: the mapping is created on the IMPORTING rank's
     own device, which also enables peer access).  Returns `world` tensors; entry q aliases GPU q's
-    memory and can be read by this rank's kernels over NVLink (measured: random 512-byte rows
-    pulled at 670 GB/s by dglb200_gather_rows).  The owner must keep `t` alive."""
+    memory and can be read AND written by this rank's kernels over NVLink.  The owner must keep `t`
+    alive.  torch sub-allocates: several tensors can live in one cudaMalloc block, so a block that is
+    already mapped is not opened a second time."""
     import ctypes
     from . import _lib
     lib = _lib.get_lib()
@@ -100,11 +115,16 @@ def share_with_peers(t, rank, world, group=None):
             continue
         h, off, shape, dtype = objs[q]
         assert dtype == str(t.dtype)
-        ptr = ctypes.c_void_p()
-        with torch.cuda.device(t.device):
-            _lib.check_call(lib.dglb200_ipc_open(ctypes.c_char_p(h), ctypes.byref(ptr)))
-        _OPEN_HANDLES.append(ptr)
-        pt = torch.as_tensor(_RawCuda(ptr.value + off, shape, typestr), device=t.device)
+        base = _OPEN_HANDLES.get((q, h))
+        if base is None:
+            ptr = ctypes.c_void_p()
+            with torch.cuda.device(t.device):
+                _lib.check_call(lib.dglb200_ipc_open(ctypes.c_char_p(h), ctypes.byref(ptr)))
+            base = _OPEN_HANDLES[(q, h)] = int(ptr.value)
+        if 0 in shape:
+            peers.append(torch.empty(shape, dtype=t.dtype, device=t.device))
+            continue
+        pt = torch.as_tensor(_RawCuda(base + off, shape, typestr), device=t.device)
         peers.append(pt.view(view_as) if view_as is not None else pt)
     return peers
 
@@ -113,11 +133,37 @@ def close_peer_mappings():
     """Unmap every peer buffer this process opened with share_with_peers (dglb200_ipc_close).  Call it
     once the tensors returned by share_with_peers are no longer used (e.g. before tearing a
     partition down in a long-lived process); process exit unmaps them anyway."""
+    import ctypes
     from . import _lib
     lib = _lib.get_lib()
     while _OPEN_HANDLES:
-        ptr = _OPEN_HANDLES.pop()
-        _lib.check_call(lib.dglb200_ipc_close(ptr))
+        _, base = _OPEN_HANDLES.popitem()
+        _lib.check_call(lib.dglb200_ipc_close(ctypes.c_void_p(base)))
+
+
+class PeerSignals(object):
+    """Flag words of one exchange channel: `slots` x world int32 in THIS rank's memory, mapped into
+    every peer.  Word [slot, q] is written by rank q only (and only ever grows: it carries the epoch
+    of the last exchange rank q completed for that slot) and read by this rank only."""
+
+    def __init__(self, slots, rank, world, device, group=None):
+        self.rank, self.world, self.slots = rank, world, slots
+        self.flags = torch.zeros((slots, world), dtype=torch.int32, device=device)
+        self.counter = torch.zeros(max(slots, 1), dtype=torch.int32, device=device)
+        self.err = torch.zeros(1, dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device) if self.flags.is_cuda else None
+        self.peer_flags = share_with_peers(self.flags, rank, world, group)
+
+    def local(self, slot):
+        """My flag words of `slot`, one per rank (what peer_wait polls)."""
+        return self.flags[slot]
+
+    def remote(self, slot):
+        """For every rank q (self included): address of MY word [slot, rank] inside q's flag array."""
+        return [int(self.peer_flags[q][slot, self.rank:self.rank + 1].data_ptr()) for q in range(self.world)]
+
+    def errors(self):
+        return int(self.err.item())
 
 
 class StreamBarrier(object):
@@ -130,6 +176,21 @@ class StreamBarrier(object):
 
     def __call__(self):
         dist.all_reduce(self.token, group=self.group)
+
+
+class _Channel(object):
+    """State of one exchange buffer: the buffer itself, its peer mappings, its flag words and the
+    epoch counter of the signal transport.  One per (key, width, dtype): a model that aggregates at
+    several widths (a 2-layer GCN) never reallocates a buffer that peers have mapped."""
+
+    def __init__(self, buf):
+        self.buf = buf
+        self.peer = None          # every rank's buffer mapped here
+        self.wire = None          # bf16 staging of the halo rows (wire mode)
+        self.peer_wire = None
+        self.sig = None           # PeerSignals
+        self.epoch = 0
+        self.pending_free = 0     # epoch whose "buffer free" signal is still owed (exchange() without SpMM)
 
 
 class RowPartition(object):
@@ -150,39 +211,74 @@ class RowPartition(object):
         else:
             self.loc_in, self.loc_out = csr_in, csr_out
         self._spmm = spmm_fn or (lambda csr, x, out: ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=x, out=out)[0])
-        self._full = {}
-        self._peer_full = {}      # key -> every rank's full buffer mapped here (transport "peer")
+        self._full = {}           # (key, feat, dtype) -> _Channel
+        self._last = {}           # key -> channel of the last exchange under that key
         self._barrier = None
         self._comm = None
+        self._peer_on = False
+
+    # -- buffers ---------------------------------------------------------------------------------
+    def _channel(self, key, feat, like):
+        ck = (key, int(feat), like.dtype)
+        ch = self._full.get(ck)
+        if ch is None:
+            if self._peer_on and self.world > 1:
+                raise DGLError("RowPartition: no peer-mapped exchange buffer for key %r at width %d (%s); call "
+                               "enable_peer_transport(%d, like, keys=(%r,)) collectively first"
+                               % (key, feat, like.dtype, feat, key))
+            ch = self._full[ck] = _Channel(torch.empty((self.n, feat), dtype=like.dtype, device=like.device))
+        self._last[key] = ch
+        return ch
 
     def enable_peer_transport(self, feat, like, keys=("x", "dy")):
-        """Exchange by PEER LOADS over NVLink instead of NCCL: every rank's gather buffer is mapped
-        into every other rank; a rank copies the blocks it lacks straight out of their owners'
-        memory (one device-to-device copy per owner, all inside stream-ordered barriers)."""
+        """Exchange over NVLink peer memory instead of NCCL: every rank's gather buffer is mapped into
+        every other rank (CUDA IPC).  Collective: every rank calls it with the same arguments."""
         if self.world == 1:
             return
+        self._peer_on = False
         for key in keys:
-            full = self.full_buffer(key, feat, like)
-            self._peer_full[key] = share_with_peers(full, self.rank, self.world, self.group)
-        self._barrier = StreamBarrier(like.device, self.group)
+            ch = self._channel(key, feat, like)
+            if ch.peer is None:
+                ch.peer = share_with_peers(ch.buf, self.rank, self.world, self.group)
+                # the push kernel moves 16-byte units: widths whose rows are not 16-byte multiples (41
+                # classes) keep the round-1 transport (block copies between stream barriers)
+                if PULL_MODE == "signal" and (feat * ch.buf.element_size()) % 16 == 0:
+                    n_slab = self._slabs(feat, like.dtype)
+                    ch.sig = PeerSignals(len(n_slab) + 1, self.rank, self.world, like.device, self.group)
+                elif self._barrier is None:
+                    self._barrier = StreamBarrier(like.device, self.group)
+        self._peer_on = True
 
     def _global_rank(self, p):
         return p if self.group is None else dist.get_global_rank(self.group, p)
 
     def full_buffer(self, key, feat, like):
-        """Persistent [n, feat] gather buffer (one per use: 'x' for forward, 'dy' for gradient)."""
-        buf = self._full.get(key)
-        if buf is None or buf.shape[1] != feat or buf.dtype != like.dtype or buf.device != like.device:
-            buf = torch.empty((self.n, feat), dtype=like.dtype, device=like.device)
-            self._full[key] = buf
-        return buf
+        """Persistent [n, feat] gather buffer (one per key, width and dtype)."""
+        return self._channel(key, feat, like).buf
 
     def views(self, full):
         return [full[self.bounds[p]:self.bounds[p + 1]] for p in range(self.world)]
 
+    def release(self):
+        """Drop the exchange buffers (the peer mappings stay open until close_peer_mappings())."""
+        self._full.clear()
+        self._last.clear()
+        self._peer_on = False
+
+    def comm_errors(self):
+        """Signal waits that timed out since the start (0 = none) + out-of-range ids seen by gathers."""
+        ops.check_bad_ids()
+        return sum(ch.sig.errors() for ch in self._full.values() if ch.sig is not None)
+
+    def local_spmm(self, csr, x, out):
+        """The local kernel alone over an already exchanged operand (benchmark kernel-only timing)."""
+        return self._spmm(csr, x, out)
+
+    # -- all-gather --------------------------------------------------------------------------------
     def all_gather_rows(self, local, key):
         """[rows, feat] block of every rank -> [n, feat] on every rank (uneven block sizes)."""
-        full = self.full_buffer(key, local.shape[1], local)
+        ch = self._channel(key, local.shape[1], local)
+        full = ch.buf
         views = self.views(full)
         if self.world == 1:
             if views[0].data_ptr() != local.data_ptr():
@@ -190,12 +286,18 @@ class RowPartition(object):
             return full
         if views[self.rank].data_ptr() != local.data_ptr():
             views[self.rank].copy_(local)
-        if key in self._peer_full:
+        if ch.sig is not None:
+            self._signal_push(ch, self._slabs(local.shape[1], local.dtype), on_comm=False)
+            for i in range(ch.sig.slots - 1):
+                ops.peer_wait(ch.sig.local(i), ch.epoch, ch.sig.err)
+            ch.pending_free = ch.epoch        # the caller's SpMM follows on this stream
+            return full
+        if ch.peer is not None:
             self._barrier()                                   # every owner's block is written
             for k in range(1, self.world):                    # start at a different owner on every rank
                 q = (self.rank + k) % self.world
                 if views[q].numel():
-                    views[q].copy_(self._peer_full[key][q][self.bounds[q]:self.bounds[q + 1]], non_blocking=True)
+                    views[q].copy_(ch.peer[q][self.bounds[q]:self.bounds[q + 1]], non_blocking=True)
             self._barrier()                                   # nobody overwrites a block still being read
             return full
         if dist.get_backend(self.group) == "nccl":
@@ -228,17 +330,70 @@ class RowPartition(object):
         """Bytes this rank receives per exchange."""
         return (self.n - self.rows) * feat * elem if self.world > 1 else 0
 
-    SLAB = 0      # feature-slab pipeline width in elements (64 = the SpMM's L2 slab at C2); 0 = off:
-                  # measured at 8 ranks on C2: 2.63 ms/step pipelined vs 2.48 ms/step plain
+    SLAB = 0      # round-1 feature-slab PULL pipeline (transport "copy"): 0 = off, measured slower
+
+    def _slabs(self, feat, dtype):
+        """Column blocks [(s0, width)] of the pipelined push all-gather: the SpMM's own L2 slab width
+        (64 fp32 at C2), so that the per-slab launches do the work of the one slabbed launch."""
+        w = ALLGATHER_SLAB
+        if w <= 0 or feat <= w or feat % w or (w * torch.empty(0, dtype=dtype).element_size()) % 16:
+            return [(0, feat)]
+        return [(s0, w) for s0 in range(0, feat, w)]
+
+    def _signal_push(self, ch, slabs, on_comm=True):
+        """Enqueue the pushes of a new epoch: for every column slab ONE launch stores this rank's block
+        into every peer's gather buffer and sets the slab's flag word on every rank.  The first launch
+        waits (in the kernel) until every rank has released the buffer of the previous epoch."""
+        if ch.pending_free:       # a bare exchange() left the release of its epoch to the next call
+            ops.peer_signal(ch.sig.remote(ch.sig.slots - 1), ch.pending_free, ch.buf.device)
+            ch.pending_free = 0
+        ch.epoch += 1
+        own = ch.buf[self.r0:self.r1]
+        es = own.element_size()
+        counts = [self.rows if q != self.rank else 0 for q in range(self.world)]
+        free_slot = ch.sig.slots - 1
+        cur = torch.cuda.current_stream(ch.buf.device)
+        if on_comm:
+            if self._comm is None:
+                self._comm = torch.cuda.Stream(device=ch.buf.device, priority=COMM_PRIORITY)
+            self._comm.wait_stream(cur)
+        ctx = torch.cuda.stream(self._comm) if on_comm else _nullcontext()
+        with ctx:
+            for i, (s0, w) in enumerate(slabs):
+                dst = [int(ch.peer[q][self.r0:self.r1, s0:s0 + w].data_ptr()) if (q != self.rank and self.rows) else 0
+                       for q in range(self.world)]
+                ops.peer_push(own[:, s0:s0 + w], None, counts, dst, ch.buf.stride(0) * es, w * es,
+                              signal_addrs=ch.sig.remote(i), signal_value=ch.epoch, counter=ch.sig.counter[i:i + 1],
+                              wait_flags=ch.sig.local(free_slot) if i == 0 else None, wait_value=ch.epoch - 1,
+                              err=ch.sig.err, rotate=self.rank, max_ctas=PUSH_CTAS)
 
     def _aggregate(self, key, local, csr, out):
-        """Exchange + SpMM.  With the peer transport the feature dimension is pipelined in slabs:
-        slab s+1 is copied out of the owners' memory (NVLink) on a side stream while the SpMM runs
-        over slab s (dglb200_spmm_csr_strided on column blocks of the gather buffer)."""
+        """Exchange + SpMM.  Signal transport: the feature dimension is pipelined in slabs - slab s+1
+        is pushed into the peers (NVLink stores from a side stream) while the SpMM runs over slab s
+        (dglb200_spmm_csr_strided on column blocks of the gather buffer)."""
         feat = local.shape[1]
-        if key not in self._peer_full or self.SLAB <= 0 or feat <= self.SLAB or feat % self.SLAB:
+        ch = self._channel(key, feat, local)
+        if ch.sig is not None:
+            full = ch.buf
+            own = full[self.r0:self.r1]
+            if own.data_ptr() != local.data_ptr():
+                own.copy_(local)
+            if out is None:
+                out = torch.empty((csr.n_rows, feat), dtype=local.dtype, device=local.device)
+            slabs = self._slabs(feat, local.dtype)
+            self._signal_push(ch, slabs)
+            for i, (s0, w) in enumerate(slabs):
+                ops.peer_wait(ch.sig.local(i), ch.epoch, ch.sig.err)
+                if len(slabs) == 1:
+                    self._spmm(csr, full, out)
+                else:
+                    self._spmm(csr, full[:, s0:s0 + w], out[:, s0:s0 + w])
+            ops.peer_signal(ch.sig.remote(ch.sig.slots - 1), ch.epoch, full.device)   # buffer released
+            torch.cuda.current_stream(full.device).wait_stream(self._comm)   # my block may be rewritten only after my pushes
+            return out
+        if ch.peer is None or self.SLAB <= 0 or feat <= self.SLAB or feat % self.SLAB:
             return self._spmm(csr, self.exchange(key, local), out)
-        full = self.full_buffer(key, feat, local)
+        full = ch.buf
         views = self.views(full)
         if views[self.rank].data_ptr() != local.data_ptr():
             views[self.rank].copy_(local)
@@ -247,7 +402,7 @@ class RowPartition(object):
         if self._comm is None:
             self._comm = torch.cuda.Stream(device=local.device, priority=COMM_PRIORITY)
         cur = torch.cuda.current_stream(local.device)
-        peers = self._peer_full[key]
+        peers = ch.peer
         self._barrier()                                           # every owner's block is written
         self._comm.wait_stream(cur)
         events = []
@@ -269,13 +424,20 @@ class RowPartition(object):
         return out
 
     def forward(self, x_local, out=None, key="x"):
-        """y_local = (A x)[r0:r1] for update_all(copy_src, sum).  `key` names the gather buffer: a
-        model that aggregates at several widths uses one key per width (no reallocation)."""
+        """y_local = (A x)[r0:r1] for update_all(copy_src, sum).  `key` names the gather buffer."""
         return self._aggregate(key, x_local, self.loc_in, out)
 
     def backward(self, dy_local, out=None, key="dy"):
         """dx_local = (A^T dy)[r0:r1]."""
         return self._aggregate(key, dy_local, self.loc_out, out)
+
+
+class _nullcontext(object):
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *a):
+        return False
 
 
 class _PartitionAggregate(torch.autograd.Function):
@@ -309,10 +471,10 @@ class HaloExchange(object):
       * the compact row space is [own rows | halo of chunk 0 (by owner, ascending id) | chunk 1 ..]
         and the block's column ids are remapped into it
       * an all-to-all of the id lists tells every owner which rows to serve, per chunk
-    Per call, for k = 0..chunks-1 on a side stream: fetch chunk k's halo rows (NCCL: pack with the
-    gather kernel + all_to_all_single; peer transport: the gather kernel pulls them straight out of
-    the owners' memory over NVLink); the SpMM over chunk k's rows starts as soon as its halo has
-    landed, while chunk k+1's halo is in flight.
+    Per call (signal transport), for k = 0..chunks-1 on a side stream: ONE launch pushes the rows of
+    chunk k that every peer needs into the peers' compact buffers and sets their flag words; the
+    SpMM over chunk k's rows waits on this rank's own flag words, so it starts as soon as ITS halo has
+    landed, while chunk k+1 is in flight.
     """
 
     def __init__(self, csr_block, bounds, rank, world, group=None, gather_fn=None, chunks=1):
@@ -383,48 +545,79 @@ class HaloExchange(object):
             if world > 1:
                 dist.all_to_all_single(serve, need_cat, output_split_sizes=sc,
                                        input_split_sizes=self.recv_counts[k], group=group)
+            # the tables the gather / push kernels index with are validated ONCE here (the kernels skip
+            # an out-of-range id and raise a flag that nothing on the hot path reads)
+            if serve.numel() and (int(serve.min()) < 0 or int(serve.max()) >= max(self.rows, 1)):
+                raise DGLError("HaloExchange: a peer asked rank %d for a row outside its block [0, %d)"
+                               % (rank, self.rows))
             self.send_counts.append(sc)
             self.need_cat.append(need_cat.contiguous())
             self.serve_local.append(serve.contiguous())           # already local ids of THIS rank
-        # push transport: where the rows I serve land inside requester r's compact buffer, per chunk
+        # push transports: where the rows I serve land inside requester r's compact buffer, per chunk
         self.push_dst = None
+        self._rows_of_rank = [self.rows]
         if world > 1:
             objs = [None] * world
-            dist.all_gather_object(objs, (self.chunk_start, self.recv_counts), group=group)
+            dist.all_gather_object(objs, (self.chunk_start, self.recv_counts, self.rows), group=group)
             self.push_dst = [[int(objs[r][0][k] + sum(objs[r][1][k][:rank])) for r in range(world)]
                              for k in range(self.chunks)]
+            self._rows_of_rank = [int(objs[r][2]) for r in range(world)]
         self.chunk_csr = None
         self.timing = []
-        self._buf = None
-        self._peer_buf = None
-        self._wire = self._peer_wire = None     # bf16 wire mode (enable_peer_transport)
+        self._chan = {}           # (feat, dtype) -> _Channel
+        self._cur = None          # channel of the last call
+        self._peer_on = False
         self._barrier = None
         self._comm = None
 
     # -- buffers / transports -----------------------------------------------------------------
+    def _channel(self, feat, like):
+        ck = (int(feat), like.dtype)
+        ch = self._chan.get(ck)
+        if ch is None:
+            if self._peer_on and self.world > 1:
+                raise DGLError("HaloExchange: no peer-mapped buffer at width %d (%s); call "
+                               "enable_peer_transport(%d, like) collectively first" % (feat, like.dtype, feat))
+            ch = self._chan[ck] = _Channel(torch.empty((self.rows + self.n_halo, feat), dtype=like.dtype,
+                                                       device=like.device))
+        self._cur = ch
+        return ch
+
     def buffer(self, feat, like):
-        """Compact feature buffer [rows + n_halo, feat]; rows [0, rows) are this rank's block."""
-        if (self._buf is None or self._buf.shape[1] != feat or self._buf.dtype != like.dtype or
-                self._buf.device != like.device):
-            self._buf = torch.empty((self.rows + self.n_halo, feat), dtype=like.dtype, device=like.device)
-        return self._buf
+        """Compact feature buffer [rows + n_halo, feat]; rows [0, rows) are this rank's block.  One
+        buffer (with its peer mappings) per width and dtype."""
+        return self._channel(feat, like).buf
+
+    @property
+    def _wire(self):              # the bf16 staging buffer of the channel in use (tests / stats)
+        return self._cur.wire if self._cur is not None else None
+
+    def release(self):
+        self._chan.clear()
+        self._cur = None
+        self._peer_on = False
+
+    def errors(self):
+        return sum(ch.sig.errors() for ch in self._chan.values() if ch.sig is not None)
 
     def enable_peer_transport(self, feat, like):
-        """Pull the halo rows straight out of their owners' memory with the gather kernel (peer
-        loads over NVLink): no packing pass on the owner, no NCCL on the data path."""
+        """Move the halo rows over NVLink peer memory (no NCCL on the data path).  Collective."""
         if self.world == 1:
             return
-        buf = self.buffer(feat, like)
-        self._peer_buf = share_with_peers(buf, self.rank, self.world, self.group)
-        self._barrier = StreamBarrier(like.device, self.group)
-        self._wire = self._peer_wire = None
-        if WIRE == "bf16" and PULL_MODE == "push" and buf.dtype == torch.float32:
-            # halo rows arrive here as bf16 (written by their owners) and are widened into `buf`
-            self._wire = torch.empty((max(self.n_halo, 1), feat), dtype=torch.bfloat16, device=like.device)
-            self._peer_wire = share_with_peers(self._wire, self.rank, self.world, self.group)
-            rows_all = [None] * self.world
-            dist.all_gather_object(rows_all, self.rows, group=self.group)
-            self._rows_of_rank = rows_all
+        self._peer_on = False
+        ch = self._channel(feat, like)
+        if ch.peer is None:
+            ch.peer = share_with_peers(ch.buf, self.rank, self.world, self.group)
+            if WIRE == "bf16" and PULL_MODE in ("push", "signal") and ch.buf.dtype == torch.float32:
+                # halo rows arrive here as bf16 (written by their owners) and are widened into `buf`
+                ch.wire = torch.empty((max(self.n_halo, 1), feat), dtype=torch.bfloat16, device=like.device)
+                ch.peer_wire = share_with_peers(ch.wire, self.rank, self.world, self.group)
+            unit = 32 if ch.wire is not None else 16
+            if PULL_MODE == "signal" and (feat * ch.buf.element_size()) % unit == 0:
+                ch.sig = PeerSignals(self.chunks + 1, self.rank, self.world, like.device, self.group)
+            elif self._barrier is None:
+                self._barrier = StreamBarrier(like.device, self.group)
+        self._peer_on = True
 
     def row_chunks(self):
         """The remapped CSR cut into the plan's row chunks (views; each with its own long-row plan)."""
@@ -437,11 +630,37 @@ class HaloExchange(object):
         return self.n_halo * feat * elem
 
     # -- data path ---------------------------------------------------------------------------
-    def _fetch_chunk(self, k, buf):
-        """Bring chunk k's halo rows into buf (current stream)."""
+    def _push_chunk_signal(self, ch, k):
+        """Signal transport: ONE launch stores chunk k's rows into every requester's compact buffer (or
+        its bf16 staging buffer) and sets the chunk's flag word on every rank."""
+        buf = ch.buf
+        es = buf.element_size()
+        sc = self.send_counts[k]
+        feat = buf.shape[1]
+        dst = []
+        for r in range(self.world):
+            if r == self.rank or not sc[r]:
+                dst.append(0)
+            elif ch.peer_wire is not None:
+                h0 = self.push_dst[k][r] - self._rows_of_rank[r]          # position inside r's halo region
+                dst.append(int(ch.peer_wire[r][h0:h0 + 1].data_ptr()))
+            else:
+                d0 = self.push_dst[k][r]
+                dst.append(int(ch.peer[r][d0:d0 + 1].data_ptr()))
+        to_bf16 = ch.peer_wire is not None
+        free_slot = ch.sig.slots - 1
+        ops.peer_push(buf[:self.rows], self.serve_local[k], sc, dst,
+                      feat * (2 if to_bf16 else es), feat * es,
+                      signal_addrs=ch.sig.remote(k), signal_value=ch.epoch, counter=ch.sig.counter[k:k + 1],
+                      wait_flags=ch.sig.local(free_slot) if k == 0 else None, wait_value=ch.epoch - 1,
+                      err=ch.sig.err, to_bf16=to_bf16, rotate=self.rank, max_ctas=PUSH_CTAS)
+
+    def _fetch_chunk(self, k, ch):
+        """Bring chunk k's halo rows into the buffer (current stream; barrier / NCCL transports)."""
+        buf = ch.buf
         start = self.chunk_start[k]
         cnts = self.recv_counts[k]
-        if self._peer_buf is not None and PULL_MODE == "push":
+        if ch.peer is not None and PULL_MODE in ("push", "signal"):
             # owner-side: gather the rows each requester needs out of my block and STORE them straight
             # into its compact buffer over NVLink (posted writes, no request round trip); rotating
             # order so that every requester is written by one owner at a time
@@ -454,16 +673,16 @@ class HaloExchange(object):
                 r = (self.rank + j) % self.world
                 if sc[r]:
                     d0 = self.push_dst[k][r]
-                    if self._peer_wire is not None:
+                    if ch.peer_wire is not None:
                         h0 = d0 - self._rows_of_rank[r]          # position inside r's halo region
                         ops.gather_rows_convert(buf[:self.rows], self.serve_local[k][seg[r]:seg[r + 1]],
-                                                out=self._peer_wire[r][h0:h0 + sc[r]], max_ctas=ctas)
+                                                out=ch.peer_wire[r][h0:h0 + sc[r]], max_ctas=ctas)
                     else:
                         ops.gather_rows(buf[:self.rows], self.serve_local[k][seg[r]:seg[r + 1]],
-                                        out=self._peer_buf[r][d0:d0 + sc[r]], max_ctas=ctas)
+                                        out=ch.peer[r][d0:d0 + sc[r]], max_ctas=ctas)
             return
-        if self._peer_buf is not None:
-            # one launch pulls this chunk's rows from every owner at once (NVLink peer loads)
+        if ch.peer is not None:
+            # pull this chunk's rows out of the owners' memory (NVLink peer loads)
             seg = [0]
             for q in range(self.world):
                 seg.append(seg[-1] + cnts[q])
@@ -471,10 +690,10 @@ class HaloExchange(object):
                 for j in range(1, self.world):
                     q = (self.rank + j) % self.world
                     if cnts[q]:
-                        ops.gather_rows(self._peer_buf[q][:self.bounds[q + 1] - self.bounds[q]], self.need_local[k][q],
+                        ops.gather_rows(ch.peer[q][:self.bounds[q + 1] - self.bounds[q]], self.need_local[k][q],
                                         out=buf[start + seg[q]:start + seg[q + 1]], max_ctas=PULL_CTAS)
             elif seg[-1]:
-                srcs = [self._peer_buf[q][:self.bounds[q + 1] - self.bounds[q]] if q != self.rank else None
+                srcs = [ch.peer[q][:self.bounds[q + 1] - self.bounds[q]] if q != self.rank else None
                         for q in range(self.world)]
                 ops.gather_rows_multi(srcs, seg, self.need_cat[k], buf[start:start + seg[-1]], max_ctas=PULL_CTAS)
             return
@@ -482,24 +701,43 @@ class HaloExchange(object):
         dist.all_to_all_single(buf[start:start + sum(cnts)], send, output_split_sizes=cnts,
                                input_split_sizes=self.send_counts[k], group=self.group)
 
-    def _widen_chunk(self, k, buf):
+    def _widen_chunk(self, k, ch):
         """bf16 wire mode: chunk k's halo rows have landed in the bf16 staging buffer; widen them
         into the fp32 operand (local HBM traffic only)."""
-        if self._wire is None:
+        if ch.wire is None:
             return
         cnt = sum(self.recv_counts[k])
         if cnt:
             h0 = self.chunk_start[k] - self.rows
-            ops.gather_rows_convert(self._wire[h0:h0 + cnt], None,
-                                    out=buf[self.chunk_start[k]:self.chunk_start[k] + cnt])
+            ops.gather_rows_convert(ch.wire[h0:h0 + cnt], None,
+                                    out=ch.buf[self.chunk_start[k]:self.chunk_start[k] + cnt])
+
+    def _own_rows(self, ch, x_local):
+        own = ch.buf[:self.rows]
+        if own.data_ptr() != x_local.data_ptr():
+            own.copy_(x_local)
+
+    def _start_epoch(self, ch):
+        if ch.pending_free:       # a bare exchange() left the release of its epoch to the next call
+            ops.peer_signal(ch.sig.remote(ch.sig.slots - 1), ch.pending_free, ch.buf.device)
+            ch.pending_free = 0
+        ch.epoch += 1
 
     def exchange(self, x_local):
         """Unpipelined: returns the compact buffer with own rows and every halo row."""
-        buf = self.buffer(x_local.shape[1], x_local)
-        own = buf[:self.rows]
-        if own.data_ptr() != x_local.data_ptr():
-            own.copy_(x_local)
+        ch = self._channel(x_local.shape[1], x_local)
+        buf = ch.buf
+        self._own_rows(ch, x_local)
         if self.world == 1:
+            return buf
+        if ch.sig is not None:
+            self._start_epoch(ch)
+            for k in range(self.chunks):
+                self._push_chunk_signal(ch, k)
+            for k in range(self.chunks):
+                ops.peer_wait(ch.sig.local(k), ch.epoch, ch.sig.err)
+                self._widen_chunk(k, ch)
+            ch.pending_free = ch.epoch        # the caller's SpMM follows on this stream
             return buf
         if self._barrier is not None:
             self._barrier()
@@ -507,30 +745,31 @@ class HaloExchange(object):
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
         for k in range(self.chunks):
-            self._fetch_chunk(k, buf)
+            self._fetch_chunk(k, ch)
         if TIMING and x_local.is_cuda:
             b.record()
             self.timing.append((a, b))
         if self._barrier is not None:
             self._barrier()
         for k in range(self.chunks):
-            self._widen_chunk(k, buf)
+            self._widen_chunk(k, ch)
         return buf
 
     def aggregate(self, x_local, spmm_fn, out):
         """Pipelined exchange + SpMM: y[rows of chunk k] is computed while chunk k+1's halo is in
         flight on the side stream.  `out` [rows, feat] must be given."""
+        ch = self._channel(x_local.shape[1], x_local)
+        if self.world > 1 and ch.sig is not None:
+            return self._aggregate_signal(ch, x_local, spmm_fn, out)
         if self.world == 1 or self.chunks == 1:
             return spmm_fn(self.csr, self.exchange(x_local), out)
-        if self._peer_buf is not None and PULL_MODE == "push":
-            return self._aggregate_pushed(x_local, spmm_fn, out)
-        buf = self.buffer(x_local.shape[1], x_local)
-        own = buf[:self.rows]
-        if own.data_ptr() != x_local.data_ptr():
-            own.copy_(x_local)
+        if ch.peer is not None and PULL_MODE in ("push", "signal"):
+            return self._aggregate_pushed(ch, x_local, spmm_fn, out)
+        buf = ch.buf
+        self._own_rows(ch, x_local)
         if not x_local.is_cuda:                                   # CPU (gloo tests): same schedule, no streams
             for k, csr_k in enumerate(self.row_chunks()):
-                self._fetch_chunk(k, buf)
+                self._fetch_chunk(k, ch)
                 if csr_k.n_rows:
                     out[self.row_cuts[k]:self.row_cuts[k + 1]] = spmm_fn(csr_k, buf, None)
             return out
@@ -545,7 +784,7 @@ class HaloExchange(object):
         events = []
         with torch.cuda.stream(self._comm):
             for k in range(self.chunks):
-                self._fetch_chunk(k, buf)
+                self._fetch_chunk(k, ch)
                 ev = torch.cuda.Event()
                 ev.record(self._comm)
                 events.append(ev)
@@ -557,17 +796,42 @@ class HaloExchange(object):
             self._barrier()                                       # nobody overwrites rows still being read
         return out
 
+    def _aggregate_signal(self, ch, x_local, spmm_fn, out):
+        """Signal transport.  Side stream: push chunk 0 (waits in the kernel until every rank has
+        released the buffer of the previous epoch), push chunk 1, ...  Compute stream: wait for chunk
+        k's flag words, [widen], SpMM over chunk k's rows, ...; finally tell every rank that this
+        rank's buffer is free again.  A pushed chunk is complete on the receiver when EVERY owner's flag
+        word carries the epoch."""
+        buf = ch.buf
+        self._own_rows(ch, x_local)
+        if self._comm is None:
+            self._comm = torch.cuda.Stream(device=buf.device, priority=COMM_PRIORITY)
+        cur = torch.cuda.current_stream(buf.device)
+        self._start_epoch(ch)
+        self._comm.wait_stream(cur)                               # my rows are written
+        with torch.cuda.stream(self._comm):
+            for k in range(self.chunks):
+                if TIMING:
+                    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                self._push_chunk_signal(ch, k)
+                if TIMING:
+                    b.record()
+                    self.timing.append((a, b))
+        chunk_csrs = self.row_chunks() if self.chunks > 1 else [self.csr]
+        for k, csr_k in enumerate(chunk_csrs):
+            ops.peer_wait(ch.sig.local(k), ch.epoch, ch.sig.err)
+            self._widen_chunk(k, ch)
+            if csr_k.n_rows:
+                spmm_fn(csr_k, buf, out[self.row_cuts[k]:self.row_cuts[k + 1]] if self.chunks > 1 else out)
+        ops.peer_signal(ch.sig.remote(ch.sig.slots - 1), ch.epoch, buf.device)    # my buffer is free again
+        cur.wait_stream(self._comm)        # my block may be rewritten only after my pushes have read it
+        return out
 
-    def _aggregate_pushed(self, x_local, spmm_fn, out):
-        """Pipelined PUSH exchange + SpMM.  A push is local loads + posted NVLink stores, so (unlike
-        a pull, which needs the whole GPU's loads in flight to cover the NVLink round trip) a small
-        grid keeps the link busy and the SpMM of the previous row chunk keeps the other SMs.  A
-        pushed chunk is complete on the receiver only when EVERY owner has stored its share: one
-        stream-ordered barrier per chunk on the side stream."""
-        buf = self.buffer(x_local.shape[1], x_local)
-        own = buf[:self.rows]
-        if own.data_ptr() != x_local.data_ptr():
-            own.copy_(x_local)
+    def _aggregate_pushed(self, ch, x_local, spmm_fn, out):
+        """Round-1 pipelined PUSH exchange + SpMM (per-peer launches, NCCL stream barriers per chunk)."""
+        buf = ch.buf
+        self._own_rows(ch, x_local)
         if self._comm is None:
             self._comm = torch.cuda.Stream(device=x_local.device, priority=COMM_PRIORITY)
         cur = torch.cuda.current_stream(x_local.device)
@@ -579,12 +843,12 @@ class HaloExchange(object):
                 if TIMING:
                     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                     a.record()
-                self._fetch_chunk(k, buf)
+                self._fetch_chunk(k, ch)
                 if TIMING:
                     b.record()
                     self.timing.append((a, b))
                 self._barrier()               # chunk k's halo has landed everywhere
-                self._widen_chunk(k, buf)
+                self._widen_chunk(k, ch)
                 ev = torch.cuda.Event()
                 ev.record(self._comm)
                 events.append(ev)
@@ -621,6 +885,15 @@ class HaloPartition(RowPartition):
 
     def operand(self, key, feat, like):
         return self._halo(key).buffer(feat, like)
+
+    def release(self):
+        self.halo_in.release()
+        self.halo_out.release()
+        super(HaloPartition, self).release()
+
+    def comm_errors(self):
+        ops.check_bad_ids()
+        return self.halo_in.errors() + self.halo_out.errors()
 
     def exchange_bytes(self, feat, elem=4):
         if self.halo_in._wire is not None:

@@ -523,3 +523,73 @@ def gather_rows_multi(sources, seg_ptr, idx, out, max_ctas=0):
         _lib.check_call(lib.dglb200_gather_rows_multi(n_src, base, rows, seg, _ptr(idx), row_bytes, _ptr(out),
                                                       _ptr(bad), int(max_ctas), _stream()))
     return out
+
+
+def _addr(t):
+    return int(t.data_ptr()) if t is not None else 0
+
+
+def peer_push(x, idx, counts, dst_addrs, dst_ld_bytes, row_bytes, signal_addrs=None, signal_value=0,
+              counter=None, wait_flags=None, wait_value=0, err=None, to_bf16=False, rotate=0, max_ctas=0):
+    """dglb200_peer_push: ONE launch stores rows of `x` (2-D, unit inner stride; a column block is fine)
+    into every destination's buffer and then signals the destinations.  counts[q] rows go to destination
+    q: rows idx[sum(counts[:q]) ...] of x (idx int64 CUDA, or None: the segment's row i is x row i).
+    dst_addrs[q]: device address (usually peer memory) of the segment's first output row; signal_addrs[q]:
+    address of the flag word that receives signal_value once all stores are visible."""
+    lib = _lib.get_lib()
+    _need_cuda(x, idx)
+    n_dst = len(counts)
+    seg = [0]
+    for c in counts:
+        seg.append(seg[-1] + int(c))
+    seg_arr = (ctypes.c_int64 * (n_dst + 1))(*seg)
+    dst_arr = (ctypes.c_void_p * n_dst)(*[int(a) if a else None for a in dst_addrs])
+    sig_arr = None
+    if signal_addrs is not None:
+        sig_arr = (ctypes.c_void_p * n_dst)(*[int(a) if a else None for a in signal_addrs])
+    if idx is not None:
+        idx = idx.contiguous()
+        if idx.dtype != torch.int64:
+            raise DGLError("peer_push: ids must be int64")
+    if x.dim() != 2 or (x.shape[1] > 1 and x.stride(1) != 1):
+        raise DGLError("peer_push: x must be 2-D with unit inner stride")
+    es = x.element_size()
+    x_ld = int(x.stride(0)) * es if x.shape[0] > 1 else max(int(row_bytes), int(x.shape[1]) * es)
+    dev = x.device
+    bad = _BAD_FLAGS.get(dev)
+    if bad is None:
+        bad = _BAD_FLAGS[dev] = torch.zeros(1, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_peer_push(
+            n_dst, seg_arr, dst_arr, sig_arr, _ptr(idx), int(x.shape[0]), _ptr(x), x_ld, int(row_bytes),
+            int(dst_ld_bytes), 1 if to_bf16 else 0, _ptr(wait_flags),
+            int(wait_flags.numel()) if wait_flags is not None else 0, int(wait_value), int(signal_value),
+            _ptr(counter), _ptr(err), _ptr(bad), int(rotate), int(max_ctas), _stream()))
+
+
+def peer_signal(signal_addrs, value, device):
+    """dglb200_peer_signal: stream-ordered store of `value` into each listed flag word."""
+    lib = _lib.get_lib()
+    n = len(signal_addrs)
+    arr = (ctypes.c_void_p * n)(*[int(a) if a else None for a in signal_addrs])
+    with torch.cuda.device(device):
+        _lib.check_call(lib.dglb200_peer_signal(n, arr, int(value), _stream()))
+
+
+def peer_wait(flags, value, err=None):
+    """dglb200_peer_wait: kernels enqueued after this call on the current stream start only once every
+    word of the LOCAL int32 tensor `flags` is >= value."""
+    lib = _lib.get_lib()
+    _need_cuda(flags)
+    with torch.cuda.device(flags.device):
+        _lib.check_call(lib.dglb200_peer_wait(_ptr(flags), int(flags.numel()), int(value), _ptr(err), _stream()))
+
+
+def check_bad_ids():
+    """Raise DGLError if any gather / push since the last check saw an out-of-range row id (the kernels
+    skip such rows and raise a per-device flag; the reference's F.gather_row raises at once,
+    backend/pytorch/tensor.py:108-109).  Reads the flags: a device -> host sync per device."""
+    for dev, flag in list(_BAD_FLAGS.items()):
+        if int(flag.item()) != 0:
+            flag.zero_()
+            raise DGLError("gather_rows: a row id was out of range on %s (rows were skipped)" % (dev,))

@@ -349,6 +349,42 @@ int dglb200_ipc_get_handle(const void* dev_ptr, void* handle64_out, int64_t* off
 int dglb200_ipc_open(const void* handle64, void** ptr_out);
 int dglb200_ipc_close(void* ptr);
 
+/* ---- push + signal exchange over NVLink peer memory (multi-GPU halo / all-gather) ------------- */
+
+/*
+ * The engine's own transport for the 1-D row partition (no counterpart in the reference).
+ * ONE launch moves this rank's rows into every destination's exchange buffer (peer memory mapped with
+ * dglb200_ipc_open) and then sets one flag word per destination; consumers order their kernels behind
+ * dglb200_peer_wait on their own flag words.  No NCCL call and no host round trip on the data path.
+ *
+ *   destination q in [0, n_dst) receives rows idx[seg_ptr[q] .. seg_ptr[q+1]) of x (idx == NULL: the
+ *   segment's row i is x row i, i.e. a block copy) at dst_base[q] + i * dst_ld_bytes.  The three tables
+ *   are HOST arrays (n_dst <= 16; seg_ptr has n_dst + 1 entries); a destination with an empty segment may
+ *   have dst_base NULL (this is how a rank lists ITSELF so that its own flag is set as well).
+ *   convert_to_bf16 != 0: x rows are float32 and are rounded to bfloat16 (nearest even) on the way out
+ *   (row_bytes counts the float32 bytes, a multiple of 32; destination rows hold row_bytes / 2).
+ *   wait_flags (nullable): n_wait LOCAL flag words that must all be >= wait_value before the first store
+ *   (the destinations have finished reading what the previous exchange delivered).
+ *   signal_flags (nullable): per destination, the flag word that receives signal_value once every store
+ *   of the launch is visible system-wide (fence.sys + arrival counter; `counter` is a local int32 that is
+ *   0 on entry and is left 0).  Flags only grow; comparisons are wrap-safe.
+ *   A wait that sees no signal for 20 s sets *err_flag (nullable) and lets the kernel proceed: a wrong
+ *   result that the caller's checks catch, never a hung GPU.  bad_flag as in dglb200_gather_rows.
+ *   rotate: rotation of the destination order (pass the rank).  max_ctas: grid bound (0 = 2 per SM).
+ */
+int dglb200_peer_push(int n_dst, const int64_t* seg_ptr_host, void* const* dst_base_host,
+                      int32_t* const* signal_flags_host, const int64_t* idx, int64_t x_rows,
+                      const void* x, int64_t x_ld_bytes, int64_t row_bytes, int64_t dst_ld_bytes,
+                      int convert_to_bf16, const int32_t* wait_flags, int n_wait, int32_t wait_value,
+                      int32_t signal_value, int32_t* counter, int32_t* err_flag, int32_t* bad_flag,
+                      int rotate, int max_ctas, void* stream);
+/* Stream-ordered signal: once everything enqueued before it on `stream` has completed, `value` is
+ * stored to each of the n (<= 16) flag words listed in the HOST array (peer or local memory). */
+int dglb200_peer_signal(int n, int32_t* const* flags_host, int32_t value, void* stream);
+/* Stream-ordered wait: kernels enqueued after it on `stream` start only once the n LOCAL flag words
+ * flags[0..n) are all >= value (spin with back-off on one thread; time-out as above). */
+int dglb200_peer_wait(const int32_t* flags, int n, int32_t value, int32_t* err_flag, void* stream);
+
 /* ---- hook into the reference's PackedFunc registry ----------------------------------- */
 
 /*

@@ -92,7 +92,8 @@ void oracle_spmm_max(int64_t n_out, int64_t e, const int64_t* src, const int64_t
       if (msg_op == 0) m = x[src[i] * feat + f];
       else if (msg_op == 1) m = x[src[i] * feat + f] * w[i * w_width + f / group];
       else m = w[i * feat + f];
-      if (a[f] < 0 || m > o[f]) { o[f] = m; a[f] = i; }
+      /* NaN propagates (torch.max): the first NaN message wins and stays */
+      if (a[f] < 0 || m > o[f] || (m != m && o[f] == o[f])) { o[f] = m; a[f] = i; }
     }
   }
 }

@@ -132,7 +132,8 @@ def reduce_max(dst, msgs, n_out, eid=None):
     arg = np.full((n_out, flat.shape[1]), -1, dtype=np.int64)
     for e in range(E):  # small cases only
         v = dst[e]
-        better = (arg[v] < 0) | (flat[e] > out[v])
+        # NaN propagates like torch.max over the mailbox: the first NaN message wins and stays
+        better = (arg[v] < 0) | (flat[e] > out[v]) | (np.isnan(flat[e]) & ~np.isnan(out[v]))
         out[v] = np.where(better, flat[e], out[v])
         arg[v] = np.where(better, eid[e], arg[v])
     out[arg < 0] = 0.0

@@ -168,7 +168,8 @@ def _run(world, td, per_rank):
         raise [e for e in errs if e is not None][0]
 
 
-@pytest.mark.parametrize("mode,chunks,wire", [("push", 2, "f32"), ("push", 1, "f32"), ("perpeer", 1, "f32"),
+@pytest.mark.parametrize("mode,chunks,wire", [("signal", 3, "f32"), ("signal", 1, "f32"), ("signal", 2, "bf16"),
+                                              ("push", 2, "f32"), ("push", 1, "f32"), ("perpeer", 1, "f32"),
                                               ("fused", 2, "f32"), ("push", 3, "bf16")])
 def test_halo_partition_peer_transports(peers, monkeypatch, mode, chunks, wire):
     from dgl_b200 import dist as dmod
@@ -188,9 +189,9 @@ def test_halo_partition_peer_transports(peers, monkeypatch, mode, chunks, wire):
         part.enable_peer_transport(feat, like)
         xl = part.local_view("x", feat, like)
         dl = part.local_view("dy", feat, like)
-        for step in range(2):                        # buffers are reused across steps
-            xl.copy_(x[part.r0:part.r1] * (step + 1))
-            dl.copy_(dy[part.r0:part.r1] * (step + 1))
+        for step in range(3):                        # buffers are reused across steps (epochs 1..3)
+            xl.copy_(x[part.r0:part.r1] * (1 << step))
+            dl.copy_(dy[part.r0:part.r1] * (1 << step))
             y = part.forward(xl)
             dx = part.backward(dl)
         got_y[r], got_dx[r] = (part.r0, y.clone()), (part.r0, dx.clone())
@@ -199,19 +200,24 @@ def test_halo_partition_peer_transports(peers, monkeypatch, mode, chunks, wire):
     y = torch.cat([t for _, t in sorted(got_y, key=lambda p: p[0])])
     dx = torch.cat([t for _, t in sorted(got_dx, key=lambda p: p[0])])
     if wire == "f32":
-        assert torch.equal(y, 2 * want_y) and torch.equal(dx, 2 * want_dx)     # same slot order: bit-exact
+        assert torch.equal(y, 4 * want_y) and torch.equal(dx, 4 * want_dx)     # same slot order: bit-exact
     else:
         assert all(s[2] for s in stats)              # the staging buffer exists on every rank
-        for got, want in ((y, 2 * want_y), (dx, 2 * want_dx)):
+        for got, want in ((y, 4 * want_y), (dx, 4 * want_dx)):
             tol = 1e-2 * float(want.abs().max())
             assert float((got - want).abs().max()) <= tol
             assert not torch.equal(got, want)        # the halo really went through bf16
     assert sum(s[0] for s in stats) > 0              # there was a halo to exchange
 
 
-def test_row_partition_peer_all_gather(peers):
+@pytest.mark.parametrize("mode,feat,slab", [("signal", 8, 4), ("signal", 8, 64), ("signal", 5, 64), ("push", 8, 64)])
+def test_row_partition_peer_all_gather(peers, monkeypatch, mode, feat, slab):
+    """RowPartition over peer memory: the slab-pipelined push + flag signals (4-wide slabs of an 8-wide
+    row, one slab, a width the 16-byte push cannot move -> barrier transport) and round 1's block copies."""
     from dgl_b200 import dist as dmod
-    world, n, feat = 3, 70, 8
+    monkeypatch.setattr(dmod, "PULL_MODE", mode)
+    monkeypatch.setattr(dmod, "ALLGATHER_SLAB", slab)
+    world, n = 3, 70
     csr_in, csr_out = _graph(n, 500, 9)
     gen = torch.Generator().manual_seed(2)
     x, dy = torch.randn(n, feat, generator=gen), torch.randn(n, feat, generator=gen)
@@ -225,10 +231,56 @@ def test_row_partition_peer_all_gather(peers):
         part.enable_peer_transport(feat, like)
         xl = part.local_view("x", feat, like)
         dl = part.local_view("dy", feat, like)
-        xl.copy_(x[part.r0:part.r1])
-        dl.copy_(dy[part.r0:part.r1])
-        got[r] = (part.r0, part.forward(xl).clone(), part.backward(dl).clone())
+        for step in range(3):
+            xl.copy_(x[part.r0:part.r1] * (1 << step))
+            dl.copy_(dy[part.r0:part.r1] * (1 << step))
+            y, dx = part.forward(xl).clone(), part.backward(dl).clone()
+        got[r] = (part.r0, y / 4, dx / 4)
+        assert part.comm_errors() == 0
     _run(world, td, per_rank)
     got.sort(key=lambda p: p[0])
     assert torch.equal(torch.cat([g[1] for g in got]), want_y)
     assert torch.equal(torch.cat([g[2] for g in got]), want_dx)
+
+
+def test_two_widths_keep_their_own_peer_buffers(peers, monkeypatch):
+    """A 2-layer model aggregates at two widths through one partition: every (key, width) owns its
+    exchange buffer and peer mapping, nothing is reallocated under a live mapping (round-1 advisor
+    finding), and an unmapped width raises instead of silently exchanging through a stale mapping."""
+    from dgl_b200 import dist as dmod
+    from dgl_b200 import DGLError
+    monkeypatch.setattr(dmod, "PULL_MODE", "signal")
+    world, n = 3, 80
+    csr_in, csr_out = _graph(n, 600, 11)
+    gen = torch.Generator().manual_seed(3)
+    xs = {8: torch.randn(n, 8, generator=gen), 4: torch.randn(n, 4, generator=gen)}
+    want = {f: _reference(csr_in, csr_out, x, x) for f, x in xs.items()}
+    td = peers(world)
+    got = {8: [None] * world, 4: [None] * world}
+    raised = [False] * world
+
+    def per_rank(r):
+        for cls in (dmod.HaloPartition, dmod.RowPartition):
+            part = cls(csr_in, csr_out, rank=r, world=world)
+            like = torch.empty(0)
+            part.enable_peer_transport(8, like)
+            part.enable_peer_transport(4, like)
+            for _ in range(2):
+                for f in (8, 4, 8):
+                    xl = xs[f][part.r0:part.r1].contiguous()
+                    y = part.forward(xl).clone()
+                    dx = part.backward(xl).clone()
+                    got[f][r] = (part.r0, y, dx)
+            try:
+                part.forward(torch.randn(part.rows, 12))
+            except DGLError:
+                raised[r] = True
+            assert part.comm_errors() == 0
+            td._bar.wait()
+            for f in (8, 4):
+                ys = sorted(got[f], key=lambda p: p[0])
+                assert torch.equal(torch.cat([g[1] for g in ys]), want[f][0])
+                assert torch.equal(torch.cat([g[2] for g in ys]), want[f][1])
+            td._bar.wait()
+    _run(world, td, per_rank)
+    assert all(raised)

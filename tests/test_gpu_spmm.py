@@ -286,6 +286,31 @@ def test_max_with_minus_inf_messages(feat):
         assert np.array_equal(arg.cpu().numpy().astype(np.int64), warg)
 
 
+@pytest.mark.parametrize("feat", [4, 64])
+def test_max_propagates_nan(feat):
+    """The reference's fn.max is torch.max over the mailbox (function/reducer.py:45-46 ->
+    backend/pytorch/tensor.py:95-97), which PROPAGATES NaN: a destination that receives a NaN
+    message reads NaN on that feature, whatever else arrives (long-row slices included)."""
+    from dgl_b200 import ops
+    n = 100
+    src, dst = random_graph(n, 1200, 5 + feat, hubs=2, hub_deg=200, zero_deg_frac=0.2)
+    rng = np.random.RandomState(feat)
+    x = rng.randn(n, feat).astype(np.float32)
+    x[rng.rand(n, feat) < 0.02] = np.nan
+    msgs = oracle.message("copy_src", src, x)
+    want, _ = oracle.reduce_max(dst, msgs, n)
+    # the reference value, stated with torch itself on a few rows
+    for v in np.unique(dst)[:10]:
+        ref = torch.max(torch.from_numpy(msgs[dst == v]), 0)[0].numpy()
+        assert np.array_equal(ref, want[v], equal_nan=True)
+    assert np.isnan(want).any()
+    csr = _csr(src, dst, n)
+    for chunk in (0, 32):
+        y, arg = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_MAX, x=torch.from_numpy(x).cuda(),
+                          want_arg=True, chunk=chunk)
+        assert np.array_equal(y.cpu().numpy(), want, equal_nan=True)
+
+
 @pytest.mark.parametrize("feat", [41, 602, 90])
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_ragged_width_takes_padded_vector_path(feat, dtype):

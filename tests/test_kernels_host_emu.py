@@ -154,6 +154,10 @@ def test_spmm_backward_x_sum(emu, feat, w_width):
     t_spmm.test_backward_x_sum(feat, w_width)
 
 
+def test_spmm_max_propagates_nan(emu):
+    t_spmm.test_max_propagates_nan(4)
+
+
 def test_spmm_backward_x_max(emu):
     t_spmm.test_backward_x_max()
 

@@ -131,7 +131,7 @@ def _worker_autograd(rank, world, port, n, e, feat, q):
         y = b200dist.aggregate(part, xl, "wide")                 # two widths, one buffer key each
         z = b200dist.aggregate(part, (2 * y)[:, :5], "narrow")
         (z * torch.from_numpy(c[part.r0:part.r1])).sum().backward()
-        assert set(part._full) == {"xwide", "dywide", "xnarrow", "dynarrow"}
+        assert {k[0] for k in part._full} == {"xwide", "dywide", "xnarrow", "dynarrow"}   # one buffer per (key, width, dtype)
         q.put((rank, z.detach().numpy(), xl.grad.numpy()))
     finally:
         dist.destroy_process_group()
