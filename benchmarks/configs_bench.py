@@ -21,7 +21,15 @@ for p in (ROOT, os.path.join(ROOT, "dgl-1_b200")):
 from benchmarks import graphs  # noqa: E402
 from dgl_b200 import ops  # noqa: E402
 
-PEAK = 6540.5
+def _peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"])
+    except Exception:  # noqa: BLE001
+        return 6540.5
+
+
+PEAK = _peak()
 DEV = torch.device("cuda")
 
 
@@ -217,11 +225,119 @@ def c2_structure():
         report("C2", "spmm copy_src->sum F=%d f32" % feat, ms, graphs.spmm_alg_bytes(e, n, feat), n=n, e=e)
 
 
+def c3_at_c2_size():
+    """Kernel family (3) at scale (round-1 review: no measurement of any kind): the C2 graph (114.6M
+    edges, hubs of degree 22K) with 8 heads x 32 = 256 features - SDDMM add / dot, edge softmax forward
+    and backward, the fused GAT aggregation in both flavours."""
+    c = graphs.C2_REDDIT
+    n, e, heads, hid = c["n"], c["e"], 8, 32
+    src, dst = graphs.powerlaw_symmetric(n, e, c["seed"], DEV)
+    cin = ops.csr_build(dst, src, n, n)
+    del src, dst
+    a1 = torch.randn(n, heads, device=DEV)
+    a2 = torch.randn(n, heads, device=DEV)
+    ft = torch.randn(n, heads, hid, device=DEV)
+    ms = timeit(lambda: ops.sddmm(cin, ops.SDDMM_ADD, a1, a2, heads, 1), warm=2, iters=5)
+    report("C2x8h", "sddmm u+v H=8 D=1 (GAT scores)", ms, e * (2 * heads * 4 + 4 + heads * 4), n=n, e=e)
+    s = ops.sddmm(cin, ops.SDDMM_ADD, a1, a2, heads, 1)
+    ms = timeit(lambda: ops.edge_softmax(cin, s), warm=2, iters=5)
+    report("C2x8h", "edge_softmax H=8", ms, e * heads * 4 * 2 + e * 4, n=n, e=e)
+    alpha = ops.edge_softmax(cin, s)
+    ms = timeit(lambda: ops.edge_softmax_backward(cin, alpha, s), warm=2, iters=5)
+    report("C2x8h", "edge_softmax backward H=8", ms, e * heads * 4 * 3 + e * 4, n=n, e=e)
+    del s, alpha
+    u = ft.reshape(n, -1)
+    ms = timeit(lambda: ops.sddmm(cin, ops.SDDMM_DOT, u, u, heads, hid), warm=2, iters=5)
+    report("C2x8h", "sddmm u.v H=8 D=32", ms, e * (2 * heads * hid * 4 + 4 + heads * 4), n=n, e=e)
+    fused_bytes = e * (heads * hid * 4 + heads * 4 + 4) + n * heads * (hid + 2) * 4
+    for fl, name in ((ops.SOFTMAX_GAT_EXAMPLE, "example"), (ops.SOFTMAX_STABLE, "stable")):
+        ms = timeit(lambda: ops.gat_aggregate(cin, a1, a2, ft, 0.2, flavour=fl, want_edge=False), warm=1, iters=3)
+        report("C2x8h", "fused GAT aggregation (%s flavour) H=8 D=32" % name, ms, fused_bytes, n=n, e=e)
+
+
+def c5_kernel():
+    """C5 on one GPU: the SpMM kernel alone (N = 50M, E = 150M, F = 128), fp32 and bf16."""
+    c = graphs.C5_RMAT
+    n, e, feat = c["n"], c["e"], c["feat"]
+    src, dst = graphs.rmat(26, e, c["seed"], DEV, n=n)
+    cin = ops.csr_build(dst, src, n, n)
+    del src, dst
+    for dt, b in ((torch.float32, 4), (torch.bfloat16, 2)):
+        x = torch.empty(n, feat, device=DEV, dtype=dt)
+        for s0 in range(0, n, 1 << 22):
+            x[s0:s0 + (1 << 22)] = torch.randn(min(1 << 22, n - s0), feat, device=DEV).to(dt)
+        y = torch.empty(n, feat, device=DEV, dtype=dt)
+        ms = timeit(lambda: ops.spmm(cin, ops.MSG_COPY_SRC, ops.RED_SUM, x=x, out=y), warm=2, iters=6)
+        report("C5", "spmm copy_src->sum F=128 %s" % str(dt).split(".")[-1], ms,
+               graphs.spmm_alg_bytes(e, n, feat, elem=b), n=n, e=e,
+               min_bytes=graphs.spmm_min_bytes(e, n, n, feat, elem=b))
+        del x, y
+
+
+def cpu_layers():
+    """CPU baselines of the GAT and R-GCN example layers: the arithmetic the reference's
+    examples run per layer (examples/pytorch/gat/train.py:61-97 - gathers, leaky_relu, exp().clamp,
+    two incidence SpMMs, divide; examples/pytorch/rgcn/layers.py:86-100 - per-relation
+    src_mul_edge -> sum = th.sparse.mm per relation), with torch on the host cores."""
+    import time
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
+    c = graphs.C3_PUBMED
+    n, heads, hid = c["n"], c["heads"], c["hidden"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], "cpu", self_loops=True)
+    e = src.shape[0]
+    ft = torch.randn(n, heads, hid)
+    a1, a2 = torch.randn(n, heads, 1), torch.randn(n, heads, 1)
+    inc = torch.sparse_coo_tensor(torch.stack([dst, torch.arange(e)]), torch.ones(e), (n, e))
+
+    def gat_layer():
+        a = torch.nn.functional.leaky_relu(a1[src] + a2[dst], 0.2).exp().clamp(-10, 10)      # (E, H, 1)
+        m = ft[src] * a                                                                        # (E, H, D)
+        num = torch.sparse.mm(inc, m.reshape(e, -1)).reshape(n, heads, hid)
+        z = torch.sparse.mm(inc, a.reshape(e, -1)).reshape(n, heads, 1)
+        return num / z
+    gat_layer()
+    ts = []
+    for _ in range(5):
+        t0 = time.perf_counter()
+        gat_layer()
+        ts.append(time.perf_counter() - t0)
+    fused_bytes = e * (heads * hid * 4 + heads * 4 + 4) + n * heads * (hid + 2) * 4
+    report("C3", "CPU BASELINE: GAT layer edge path (torch, %d threads)" % torch.get_num_threads(),
+           sorted(ts)[2] * 1e3, fused_bytes, n=n, e=e)
+    c = graphs.C4_AIFB
+    n, hid, rels = c["n"], c["hidden"], c["rels"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], "cpu")
+    e = src.shape[0]
+    g = torch.Generator().manual_seed(c["seed"])
+    rel = torch.randint(0, rels, (e,), generator=g)
+    x = torch.randn(n, hid)
+    w = torch.rand(e)
+    adjs = []
+    for r in range(rels):
+        m = rel == r
+        adjs.append(torch.sparse_coo_tensor(torch.stack([dst[m], src[m]]), w[m], (n, n)))
+
+    def rgcn_layer():
+        acc = torch.zeros(n, hid)
+        for a in adjs:
+            acc += torch.sparse.mm(a, x)
+        return acc
+    rgcn_layer()
+    ts = []
+    for _ in range(5):
+        t0 = time.perf_counter()
+        rgcn_layer()
+        ts.append(time.perf_counter() - t0)
+    report("C4", "CPU BASELINE: R-GCN layer, 90 per-relation th.sparse.mm (torch, %d threads)" % torch.get_num_threads(),
+           sorted(ts)[2] * 1e3, graphs.spmm_alg_bytes(e, n, hid, weights=True), n=n, e=e)
+
+
 if __name__ == "__main__":
-    sections = dict(c1=c1, c3=c3, c4=c4, c4rel=c4_per_relation, c2=c2_structure, c2ref=c2_torch_sparse)
+    sections = dict(c1=c1, c3=c3, c4=c4, c4rel=c4_per_relation, c2=c2_structure, c2ref=c2_torch_sparse,
+                    c3big=c3_at_c2_size, c5=c5_kernel, cpu=cpu_layers)
     for name in (sys.argv[1:] or list(sections)):
         sections[name]()
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-    with open(os.path.join(ROOT, "gpurun_out", "configs.jsonl"), "w") as f:
+    with open(os.path.join(ROOT, "gpurun_out", os.environ.get("CONFIGS_OUT", "configs.jsonl")), "w") as f:
         for r in OUT:
             f.write(json.dumps(r) + "\n")

@@ -46,6 +46,11 @@ SIGNATURES = {
     "dglb200_widen_i32_to_i64": (c_int, [c_i64, c_vp, c_vp, c_vp]),
     "dglb200_degrees_from_indptr": (c_int, [c_i64, c_vp, c_vp, c_vp]),
     "dglb200_csr_row_ids": (c_int, [c_i64, c_i64, c_vp, c_vp, c_vp]),
+    "dglb200_csr_select_workspace_bytes": (c_int, [c_i64, ctypes.POINTER(c_sz)]),
+    "dglb200_csr_select_offsets": (c_int, [c_i64, c_vp, c_i64, c_vp, c_vp, ctypes.POINTER(c_i64), c_vp, c_sz, c_vp]),
+    "dglb200_csr_select_expand": (c_int, [c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                          c_vp, c_vp]),
+    "dglb200_degrees_of": (c_int, [c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "dglb200_spmm_plan_workspace_bytes": (c_int, [c_i64, ctypes.POINTER(c_sz)]),
     "dglb200_spmm_plan": (c_int, [c_i64, c_vp, c_i32, c_i64, c_vp, c_vp, ctypes.POINTER(c_i64),
                                   c_vp, c_sz, c_vp]),

@@ -215,25 +215,21 @@ class DGLGraph(object):
 
     def in_degrees(self, v=ALL):
         """Graph::InDegrees (graph.cc:412-424)."""
-        deg = ops.degrees(self.in_csr())
-        return deg if is_all(v) else deg[_as_ids(v, self._device)]
+        if is_all(v):
+            return ops.degrees(self.in_csr())
+        return ops.degrees_of(self.in_csr(), _as_ids(v, self._need_device()))
 
     def out_degrees(self, v=ALL):
-        deg = ops.degrees(self.out_csr())
-        return deg if is_all(v) else deg[_as_ids(v, self._device)]
+        if is_all(v):
+            return ops.degrees(self.out_csr())
+        return ops.degrees_of(self.out_csr(), _as_ids(v, self._need_device()))
 
     # ---- edge queries used by the subset entry points ---------------------------------------
     @staticmethod
     def _rows_of(csr, nodes):
-        """Slots of the CSR rows `nodes` (in the order given): (row position, slot) int64."""
-        lo = csr.indptr[nodes]
-        cnt = csr.indptr[nodes + 1] - lo
-        total = int(cnt.sum())
-        which = torch.repeat_interleave(torch.arange(nodes.numel(), device=nodes.device), cnt,
-                                        output_size=total)
-        start = torch.cumsum(cnt, 0) - cnt
-        slot = lo[which] + (torch.arange(total, device=nodes.device) - start[which])
-        return which, slot
+        """Slots of the CSR rows `nodes` (in the order given): (row position, slot) int64 - one scan +
+        one expand kernel on the device (dglb200_csr_select_*)."""
+        return ops.csr_select(csr, nodes, want=("which", "slot"))
 
     def in_edges(self, v):
         """(u, v, eid) of the in-edges of nodes v, per node in edge-id order

@@ -19,6 +19,7 @@ SDDMM_DOT, SDDMM_ADD, SDDMM_MUL, SDDMM_COPY_U, SDDMM_COPY_V = 0, 1, 2, 3, 4
 SOFTMAX_STABLE, SOFTMAX_GAT_EXAMPLE = 0, 1
 
 DEFAULT_CHUNK = 512
+_BAD_FLAGS = {}      # per device: int32 flag the gather / select kernels raise on an out-of-range id
 
 
 def _stream():
@@ -125,6 +126,51 @@ def csr_row_ids(csr):
     out = torch.empty(csr.nnz, dtype=torch.int64, device=csr.device)
     with torch.cuda.device(csr.device):
         _lib.check_call(_lib.get_lib().dglb200_csr_row_ids(csr.n_rows, csr.nnz, _ptr(csr.indptr), _ptr(out), _stream()))
+    return out
+
+
+def csr_select(csr, rows, want=("which", "slot")):
+    """Edge lists of the CSR rows `rows` (int64 CUDA, in the order given): dglb200_csr_select_offsets +
+    dglb200_csr_select_expand.  `want` names the outputs, returned in that order: "which" (position in
+    `rows`), "slot" (CSR slot), "row" (= rows[which]), "col" (column id), "eid" (edge id); all int64."""
+    lib = _lib.get_lib()
+    _need_cuda(rows, csr.indptr)
+    rows = rows.contiguous()
+    if rows.dtype != torch.int64:
+        raise DGLError("csr_select: ids must be int64")
+    dev = csr.device
+    n_sel = int(rows.shape[0])
+    nbytes = ctypes.c_size_t(0)
+    _lib.check_call(lib.dglb200_csr_select_workspace_bytes(n_sel, ctypes.byref(nbytes)))
+    ws = _workspace(nbytes.value, dev)
+    offsets = torch.empty(n_sel + 1, dtype=torch.int64, device=dev)
+    total = ctypes.c_int64(0)
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_csr_select_offsets(n_sel, _ptr(rows), csr.n_rows, _ptr(csr.indptr),
+                                                       _ptr(offsets), ctypes.byref(total), _ptr(ws),
+                                                       nbytes.value, _stream()))
+    total = int(total.value)
+    outs = {k: (torch.empty(total, dtype=torch.int64, device=dev) if k in want else None)
+            for k in ("which", "slot", "row", "col", "eid")}
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_csr_select_expand(
+            n_sel, total, _ptr(rows), _ptr(offsets), _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids),
+            _ptr(outs["which"]), _ptr(outs["slot"]), _ptr(outs["row"]), _ptr(outs["col"]), _ptr(outs["eid"]),
+            _stream()))
+    return tuple(outs[k] for k in want)
+
+
+def degrees_of(csr, rows):
+    """Degrees of the CSR rows `rows` (int64 CUDA): dglb200_degrees_of."""
+    _need_cuda(rows, csr.indptr)
+    rows = rows.contiguous()
+    out = torch.empty(rows.shape[0], dtype=torch.int64, device=csr.device)
+    bad = _BAD_FLAGS.get(csr.device)
+    if bad is None:
+        bad = _BAD_FLAGS[csr.device] = torch.zeros(1, dtype=torch.int32, device=csr.device)
+    with torch.cuda.device(csr.device):
+        _lib.check_call(_lib.get_lib().dglb200_degrees_of(int(rows.shape[0]), _ptr(rows), csr.n_rows,
+                                                          _ptr(csr.indptr), _ptr(out), _ptr(bad), _stream()))
     return out
 
 
@@ -413,9 +459,6 @@ def unique_sorted(ids, id_bound, want_inverse=True):
         _lib.check_call(lib.dglb200_unique_sorted(n, int(id_bound), _ptr(ids), _ptr(uniq), _ptr(inv),
                                                   counts, _ptr(ws), nbytes.value, _stream()))
     return uniq[:int(counts[0])], inv
-
-
-_BAD_FLAGS = {}
 
 
 def gather_rows(x, idx, out=None, max_ctas=0):

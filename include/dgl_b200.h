@@ -103,6 +103,34 @@ int dglb200_degrees_from_indptr(int64_t n_rows, const int64_t* indptr, int64_t* 
 int dglb200_csr_row_ids(int64_t n_rows, int64_t nnz, const int64_t* indptr, int64_t* row_of_slot,
                         void* stream);
 
+/*
+ * Edge lists of a SET of rows of a cached CSR, on the device: Graph::InEdges(IdArray) / OutEdges(IdArray)
+ * (src/graph/graph.cc:294-365; PackedFuncs _CAPI_DGLGraphInEdges_2 / OutEdges_2,
+ * src/graph/graph_apis.cc:284-306) and the slot lists pull / push / send_and_recv build their
+ * sub-adjacency from (python/dgl/runtime/spmv.py:154-227).  Two steps because the output size is data
+ * dependent:
+ *   csr_select_offsets: offsets[i] = number of slots of rows[0..i) (offsets has n_sel + 1 entries),
+ *     *total_host = offsets[n_sel].  An id outside [0, n_rows) is an error ("Invalid vertex", like the
+ *     reference's CHECK, graph.cc:299).  Syncs the stream (returns the total).
+ *   csr_select_expand: for output position p in [0, total), owned by selection i (offsets[i] <= p):
+ *     which[p] = i, slot[p] = indptr[rows[i]] + (p - offsets[i]), out_row[p] = rows[i],
+ *     out_col[p] = indices[slot], out_eid[p] = eids[slot] (slot itself when eids == NULL).
+ *     Every output is nullable.  Per row the slots keep the CSR's order (ascending edge id on an
+ *     order-0 CSR = the reference's adjacency-list order).  Does not sync.
+ */
+int dglb200_csr_select_workspace_bytes(int64_t n_sel, size_t* bytes_host);
+int dglb200_csr_select_offsets(int64_t n_sel, const int64_t* rows, int64_t n_rows, const int64_t* indptr,
+                               int64_t* offsets, int64_t* total_host,
+                               void* workspace, size_t workspace_bytes, void* stream);
+int dglb200_csr_select_expand(int64_t n_sel, int64_t total, const int64_t* rows, const int64_t* offsets,
+                              const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                              int64_t* which, int64_t* slot, int64_t* out_row, int64_t* out_col,
+                              int64_t* out_eid, void* stream);
+/* deg[i] = indptr[rows[i]+1] - indptr[rows[i]] (Graph::InDegrees(IdArray), graph.cc:412-424); an id
+ * outside [0, n_rows) sets *bad_flag (nullable) and yields 0.  Does not sync. */
+int dglb200_degrees_of(int64_t n_sel, const int64_t* rows, int64_t n_rows, const int64_t* indptr,
+                       int64_t* deg, int32_t* bad_flag, void* stream);
+
 /* ---- (1)(2) SpMM: generalised message -> reduce over a CSR -------------------------- */
 
 /*

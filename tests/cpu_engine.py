@@ -44,6 +44,24 @@ def _csr_row_ids(csr):
     return torch.repeat_interleave(torch.arange(csr.n_rows, dtype=torch.int64), _degrees(csr))
 
 
+def _csr_select(csr, rows, want=("which", "slot")):
+    if rows.numel() and (int(rows.min()) < 0 or int(rows.max()) >= csr.n_rows):
+        raise ops.DGLError("Invalid vertex")
+    lo = csr.indptr[rows]
+    cnt = csr.indptr[rows + 1] - lo
+    total = int(cnt.sum())
+    which = torch.repeat_interleave(torch.arange(rows.numel()), cnt, output_size=total)
+    start = torch.cumsum(cnt, 0) - cnt
+    slot = lo[which] + (torch.arange(total) - start[which])
+    outs = {"which": which, "slot": slot, "row": rows[which], "col": csr.indices[slot].long(),
+            "eid": csr.eids[slot].long() if csr.eids is not None else slot}
+    return tuple(outs[k] for k in want)
+
+
+def _degrees_of(csr, rows):
+    return csr.indptr[rows + 1] - csr.indptr[rows]
+
+
 def _slot_edge(csr):
     return csr.eids.long() if csr.eids is not None else torch.arange(csr.nnz, dtype=torch.int64)
 
@@ -193,7 +211,7 @@ _PATCHES = {
     "unique_sorted": _unique_sorted, "degree_bucketing": _degree_bucketing,
     "gather_rows": _gather_rows, "edge_data_to_slots": _edge_data_to_slots,
     "edge_softmax": _edge_softmax, "edge_softmax_backward": _edge_softmax_backward,
-    "gat_aggregate": _gat_aggregate,
+    "gat_aggregate": _gat_aggregate, "csr_select": _csr_select, "degrees_of": _degrees_of,
 }
 
 
