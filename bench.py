@@ -770,6 +770,9 @@ def c5_record(args, ctx):
     if hasattr(part, "release"):
         part.release()
     del part, m
+    if world > 1:
+        from dgl_b200 import dist as b200dist
+        b200dist.release_peer_memory()       # exported buffers stay allocated until every importer unmaps them
     torch.cuda.empty_cache()
     return rec
 
@@ -952,6 +955,8 @@ def run_b200(args):
                               "xchg_bytes", "launches", "clocks", "check", "steps")}
     part.release()
     del part, g, loc_in, loc_out, m
+    if world > 1:
+        b200dist.release_peer_memory()
     torch.cuda.empty_cache()
     c5 = None
     if not args.no_c5 and args.workload == "c2":

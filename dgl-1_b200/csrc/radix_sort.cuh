@@ -39,16 +39,26 @@ radix_hist(const uint32_t* __restrict__ keys, int64_t n, int shift, int32_t* __r
   ghist[(int64_t)threadIdx.x * tiles + blockIdx.x] = hist[threadIdx.x];
 }
 
+// Stable scatter of one tile.  The tile's pairs are first put in DIGIT ORDER in shared memory (their
+// rank inside the tile), then written out by consecutive threads: elements of one digit are
+// consecutive in shared memory AND in the output, so a warp's 32 stores fall into a few long runs
+// instead of up to 32 different sectors (round 1 stored straight from the ranks: 0.14 of the HBM
+// roofline).
 static __global__ void __launch_bounds__(kSortThreads)
 radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
               uint32_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int64_t n,
               int shift, const int32_t* __restrict__ goff, int64_t tiles) {
   __shared__ int32_t wcnt[kSortWarps][kRadix];
+  __shared__ int32_t gbase[kRadix];          // global position of a pair = gbase[digit] + rank in tile
+  __shared__ int32_t scan_smem[33];
+  __shared__ uint32_t skey[kSortTile];
+  __shared__ uint32_t sval[kSortTile];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   for (int i = threadIdx.x; i < kSortWarps * kRadix; i += kSortThreads) (&wcnt[0][0])[i] = 0;
   __syncthreads();
 
-  const int64_t base = (int64_t)blockIdx.x * kSortTile + warp * kSortWarpSpan + lane;
+  const int64_t tile0 = (int64_t)blockIdx.x * kSortTile;
+  const int64_t base = tile0 + warp * kSortWarpSpan + lane;
   uint32_t key[kSortRounds];
   const uint32_t lt_mask = (1u << lane) - 1;
 
@@ -65,10 +75,15 @@ radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__
   }
   __syncthreads();
 
-  // phase 2: turn counts into global start offsets, warp-major inside the tile
+  // phase 2: counts -> start ranks inside the tile (digit-major, warp-major inside a digit)
   {
     const int d = threadIdx.x;
-    int32_t run = goff[(int64_t)d * tiles + blockIdx.x];
+    int32_t tot = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) tot += wcnt[w][d];
+    int32_t tile_total;
+    int32_t run = block_exclusive_scan<int32_t>(tot, &tile_total, scan_smem);
+    gbase[d] = goff[(int64_t)d * tiles + blockIdx.x] - run;
 #pragma unroll
     for (int w = 0; w < kSortWarps; ++w) {
       const int32_t c = wcnt[w][d];
@@ -78,7 +93,7 @@ radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__
   }
   __syncthreads();
 
-  // phase 3: stable scatter
+  // phase 3: stable placement in shared memory
 #pragma unroll
   for (int r = 0; r < kSortRounds; ++r) {
     const int64_t i = base + r * 32;
@@ -91,9 +106,19 @@ radix_scatter(const uint32_t* __restrict__ keys_in, const uint32_t* __restrict__
     if (ok && (peers & lt_mask) == 0) wcnt[warp][d] += __popc(peers);
     __syncwarp();
     if (ok) {
-      keys_out[pos] = key[r];
-      vals_out[pos] = vals_in ? vals_in[i] : (uint32_t)i;
+      skey[pos] = key[r];
+      sval[pos] = vals_in ? vals_in[i] : (uint32_t)i;
     }
+  }
+  __syncthreads();
+
+  // phase 4: coalesced write-out in rank order
+  const int tile_n = (int)min((int64_t)kSortTile, n - tile0);
+  for (int j = threadIdx.x; j < tile_n; j += kSortThreads) {
+    const uint32_t k = skey[j];
+    const int32_t pos = gbase[(k >> shift) & (kRadix - 1)] + j;
+    keys_out[pos] = k;
+    vals_out[pos] = sval[j];
   }
 }
 

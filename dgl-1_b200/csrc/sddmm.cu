@@ -145,6 +145,148 @@ __device__ __forceinline__ float warp_sum(float v) {
   return v;
 }
 
+// Rows of H scores are contiguous (score[e, 0:H]): a lane owns whole slots and reads the H heads of a
+// slot as ONE vector (H = 8: one 32-byte sector, every byte used; round 1 looped heads outermost and
+// used 4 of every 32 bytes, three times).  A warp owns a destination row: rows of <= 32 slots keep
+// their scores in registers (one read), longer rows make the max / sum / normalise passes over
+// scores that stay in L1/L2; rows longer than kSoftmaxLongRow are left to the whole CTA (8 warps,
+// shared-memory combine) so that a 22K-degree hub is not one warp's 700-iteration chain.
+constexpr int kSoftmaxLongRow = 4096;
+constexpr int kSoftmaxWarps = 8;
+
+template <int H>
+struct HeadVec {
+  float v[H];
+  __device__ __forceinline__ void load(const float* p) {
+    if constexpr (H % 4 == 0) {
+#pragma unroll
+      for (int i = 0; i < H; i += 4) {
+        const float4 t = *reinterpret_cast<const float4*>(p + i);
+        v[i] = t.x; v[i + 1] = t.y; v[i + 2] = t.z; v[i + 3] = t.w;
+      }
+    } else if constexpr (H == 2) {
+      const float2 t = *reinterpret_cast<const float2*>(p);
+      v[0] = t.x; v[1] = t.y;
+    } else {
+#pragma unroll
+      for (int i = 0; i < H; ++i) v[i] = p[i];
+    }
+  }
+  __device__ __forceinline__ void store(float* p) const {
+    if constexpr (H % 4 == 0) {
+#pragma unroll
+      for (int i = 0; i < H; i += 4) *reinterpret_cast<float4*>(p + i) = make_float4(v[i], v[i + 1], v[i + 2], v[i + 3]);
+    } else if constexpr (H == 2) {
+      *reinterpret_cast<float2*>(p) = make_float2(v[0], v[1]);
+    } else {
+#pragma unroll
+      for (int i = 0; i < H; ++i) p[i] = v[i];
+    }
+  }
+};
+
+// Combine a per-thread value over the `nthreads`-wide team (a warp, or the CTA through smem).
+template <bool CTA, bool MAX>
+__device__ __forceinline__ float team_reduce(float v, float* smem /*[kSoftmaxWarps + 1]*/) {
+  v = MAX ? warp_max(v) : warp_sum(v);
+  if constexpr (CTA) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __syncthreads();                      // smem free again
+    if (lane == 0) smem[warp] = v;
+    __syncthreads();
+    float r = smem[0];
+#pragma unroll
+    for (int w = 1; w < kSoftmaxWarps; ++w) r = MAX ? fmaxf(r, smem[w]) : r + smem[w];
+    v = r;
+  }
+  return v;
+}
+
+// One row by a team of lanes (tid in [0, nthreads)).  BWD == false: alpha = softmax(score);
+// BWD == true: dscore = alpha * (dalpha - sum(alpha * dalpha)) with a = alpha, b = dalpha.
+template <int H, bool CTA, bool BWD>
+__device__ __forceinline__ void softmax_row(int64_t s, int64_t e, int tid, int nthreads,
+                                            const int32_t* __restrict__ eids, const float* __restrict__ a,
+                                            const float* __restrict__ b, float* __restrict__ out, float* smem) {
+  auto eid_of = [&](int64_t p) { return eids ? (int64_t)eids[p] : p; };
+  if (!CTA && e - s <= 32) {              // registers: one slot per lane
+    const int64_t p = s + tid;
+    const bool ok = p < e;
+    const int64_t ed = ok ? eid_of(p) : 0;
+    HeadVec<H> x, y;
+    if (ok) x.load(a + ed * H);
+    if (BWD && ok) y.load(b + ed * H);
+#pragma unroll
+    for (int h = 0; h < H; ++h) {
+      if constexpr (!BWD) {
+        const float m = warp_max(ok ? x.v[h] : -INFINITY);
+        const float ex = ok ? expf(x.v[h] - m) : 0.f;
+        const float z = warp_sum(ex);
+        x.v[h] = ex / z;
+      } else {
+        const float dot = warp_sum(ok ? x.v[h] * y.v[h] : 0.f);
+        x.v[h] = x.v[h] * (y.v[h] - dot);
+      }
+    }
+    if (ok) x.store(out + ed * H);
+    return;
+  }
+  float m[H], z[H];
+#pragma unroll
+  for (int h = 0; h < H; ++h) { m[h] = -INFINITY; z[h] = 0.f; }
+  if constexpr (!BWD) {
+    for (int64_t p = s + tid; p < e; p += nthreads) {
+      HeadVec<H> x;
+      x.load(a + eid_of(p) * H);
+#pragma unroll
+      for (int h = 0; h < H; ++h) m[h] = fmaxf(m[h], x.v[h]);
+    }
+#pragma unroll
+    for (int h = 0; h < H; ++h) m[h] = team_reduce<CTA, true>(m[h], smem);
+  }
+  for (int64_t p = s + tid; p < e; p += nthreads) {
+    const int64_t ed = eid_of(p);
+    HeadVec<H> x, y;
+    x.load(a + ed * H);
+    if constexpr (BWD) y.load(b + ed * H);
+#pragma unroll
+    for (int h = 0; h < H; ++h) z[h] += BWD ? x.v[h] * y.v[h] : expf(x.v[h] - m[h]);
+  }
+#pragma unroll
+  for (int h = 0; h < H; ++h) z[h] = team_reduce<CTA, false>(z[h], smem);
+  for (int64_t p = s + tid; p < e; p += nthreads) {
+    const int64_t ed = eid_of(p);
+    HeadVec<H> x, y;
+    x.load(a + ed * H);
+    if constexpr (BWD) y.load(b + ed * H);
+#pragma unroll
+    for (int h = 0; h < H; ++h) x.v[h] = BWD ? x.v[h] * (y.v[h] - z[h]) : expf(x.v[h] - m[h]) / z[h];
+    x.store(out + ed * H);
+  }
+}
+
+template <int H, bool BWD>
+__global__ void __launch_bounds__(kSoftmaxWarps * 32)
+edge_softmax_rows_kernel(int64_t n_rows, const int64_t* __restrict__ indptr, const int32_t* __restrict__ eids,
+                         const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ out) {
+  __shared__ float smem[kSoftmaxWarps + 1];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t row0 = (int64_t)blockIdx.x * kSoftmaxWarps;
+  const int64_t r = row0 + warp;
+  if (r < n_rows) {
+    const int64_t s = indptr[r], e = indptr[r + 1];
+    if (e > s && e - s <= kSoftmaxLongRow) softmax_row<H, false, BWD>(s, e, lane, 32, eids, a, b, out, smem);
+  }
+  // long rows of this CTA's window: the whole CTA, one row after another (uniform control flow)
+  for (int w = 0; w < kSoftmaxWarps; ++w) {
+    const int64_t rr = row0 + w;
+    if (rr >= n_rows) break;
+    const int64_t s = indptr[rr], e = indptr[rr + 1];
+    if (e - s > kSoftmaxLongRow) softmax_row<H, true, BWD>(s, e, threadIdx.x, kSoftmaxWarps * 32, eids, a, b, out, smem);
+  }
+}
+
+// generic head count (not 1, 2, 4, 8, 16): round 1's head-outermost kernel
 __global__ void __launch_bounds__(256)
 edge_softmax_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
                     const int32_t* __restrict__ eids, int64_t heads,
@@ -196,6 +338,30 @@ edge_softmax_backward_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
       dscore[ed * heads + h] = alpha[ed * heads + h] * (dalpha[ed * heads + h] - dot);
     }
   }
+}
+
+template <bool BWD>
+int launch_edge_softmax(int64_t n_rows, const int64_t* indptr, const int32_t* eids, int64_t heads,
+                        const float* a, const float* b, float* out, cudaStream_t stream) {
+  const bool al = ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(out) |
+                    reinterpret_cast<uintptr_t>(b)) & 15) == 0;
+  const unsigned blocks = (unsigned)ceil_div(n_rows, kSoftmaxWarps);
+#define DGLB200_SOFTMAX_H(HH)                                                                          \
+  if (heads == HH && (al || HH == 1)) {                                                                \
+    edge_softmax_rows_kernel<HH, BWD><<<blocks, kSoftmaxWarps * 32, 0, stream>>>(n_rows, indptr, eids, a, b, out); \
+    DGLB200_POST_LAUNCH("edge_softmax_rows_kernel");                                                   \
+    return 0;                                                                                          \
+  }
+  DGLB200_SOFTMAX_H(1) DGLB200_SOFTMAX_H(2) DGLB200_SOFTMAX_H(4) DGLB200_SOFTMAX_H(8) DGLB200_SOFTMAX_H(16)
+#undef DGLB200_SOFTMAX_H
+  if constexpr (!BWD) {
+    edge_softmax_kernel<<<(unsigned)ceil_div(n_rows * 32, 256), 256, 0, stream>>>(n_rows, indptr, eids, heads, a, out);
+    DGLB200_POST_LAUNCH("edge_softmax_kernel");
+  } else {
+    edge_softmax_backward_kernel<<<(unsigned)ceil_div(n_rows * 32, 256), 256, 0, stream>>>(n_rows, indptr, eids, heads, a, b, out);
+    DGLB200_POST_LAUNCH("edge_softmax_backward_kernel");
+  }
+  return 0;
 }
 
 // ---- fused GAT aggregation -------------------------------------------------------------------
@@ -338,6 +504,10 @@ int dglb200_sddmm_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr, const 
   DGLB200_REQUIRE(u != nullptr || op == DGLB200_SDDMM_COPY_V, "sddmm_csr: u is NULL");
   DGLB200_REQUIRE(v != nullptr || op == DGLB200_SDDMM_COPY_U, "sddmm_csr: v is NULL");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (op != DGLB200_SDDMM_DOT) {   // element-wise ops ignore head boundaries: one flat row of heads * dim
+    dim *= heads;                  // elements, so (E, 8, 1) GAT scores move as 16-byte vectors too
+    heads = 1;
+  }
   return dtype == DGLB200_F32
              ? launch_sddmm<float, 4>(n_rows, nnz, indptr, indices, eids, op, u, v, heads, dim, out, st)
              : launch_sddmm<__nv_bfloat16, 8>(n_rows, nnz, indptr, indices, eids, op, u, v, heads, dim, out, st);
@@ -350,10 +520,7 @@ int dglb200_edge_softmax_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr,
   DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && heads >= 1, "edge_softmax_csr: bad sizes");
   if (nnz == 0 || n_rows == 0) return 0;
   DGLB200_REQUIRE(indptr && score && alpha, "edge_softmax_csr: NULL pointer");
-  edge_softmax_kernel<<<(unsigned)ceil_div(n_rows * 32, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      n_rows, indptr, eids, heads, score, alpha);
-  DGLB200_POST_LAUNCH("edge_softmax_kernel");
-  return 0;
+  return launch_edge_softmax<false>(n_rows, indptr, eids, heads, score, nullptr, alpha, static_cast<cudaStream_t>(stream));
 }
 
 int dglb200_edge_softmax_backward_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr,
@@ -363,10 +530,7 @@ int dglb200_edge_softmax_backward_csr(int64_t n_rows, int64_t nnz, const int64_t
   DGLB200_REQUIRE(n_rows >= 0 && nnz >= 0 && heads >= 1, "edge_softmax_backward_csr: bad sizes");
   if (nnz == 0 || n_rows == 0) return 0;
   DGLB200_REQUIRE(indptr && alpha && dalpha && dscore, "edge_softmax_backward_csr: NULL pointer");
-  edge_softmax_backward_kernel<<<(unsigned)ceil_div(n_rows * 32, 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(
-      n_rows, indptr, eids, heads, alpha, dalpha, dscore);
-  DGLB200_POST_LAUNCH("edge_softmax_backward_kernel");
-  return 0;
+  return launch_edge_softmax<true>(n_rows, indptr, eids, heads, alpha, dalpha, dscore, static_cast<cudaStream_t>(stream));
 }
 
 int dglb200_gat_aggregate_csr(int64_t n_rows, int64_t nnz, const int64_t* indptr,

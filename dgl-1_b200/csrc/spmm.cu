@@ -42,7 +42,7 @@ __global__ void plan_emit(const int32_t* is_long, const int32_t* long_pos, const
 template <typename T, int RED>
 __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, int n_long,
                            const float* partial, const int32_t* partial_arg, int64_t feat, int64_t y_ld,
-                           T* y, int32_t* arg) {
+                           T* y, int32_t* arg, int accumulate) {
   const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int lr = blockIdx.y;
   if (f >= feat || lr >= n_long) return;
@@ -59,6 +59,10 @@ __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, i
     }
   }
   const int64_t row = long_rows[lr];
+  if (RED == DGLB200_RED_SUM && accumulate) {
+    if (sizeof(T) == 4) acc += reinterpret_cast<float*>(y)[row * y_ld + f];
+    else acc += __bfloat162float(reinterpret_cast<__nv_bfloat16*>(y)[row * y_ld + f]);
+  }
   if (RED == DGLB200_RED_MAX && arg) arg[row * feat + f] = best;
   if (sizeof(T) == 4) reinterpret_cast<float*>(y)[row * y_ld + f] = acc;
   else reinterpret_cast<__nv_bfloat16*>(y)[row * y_ld + f] = __float2bfloat16_rn(acc);
@@ -178,6 +182,13 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
                          (msg == DGLB200_MSG_SRC_MUL_EDGE && a.w_mode == kWScalar);
   bool vec = ragged ? (ragged_ok && x_ok && a.x_ld >= a.feat + 1) : (x_ok && a.y_vec);
   if (a.w != nullptr && (a.w_mode == kWFull || msg == DGLB200_MSG_COPY_EDGE)) vec = vec && aligned16(a.w);
+  DGLB200_REQUIRE(!(a.accumulate && red != DGLB200_RED_SUM), "spmm: accumulate needs the SUM reducer");
+  if (a.x_halo != nullptr) {
+    DGLB200_REQUIRE(dtype == DGLB200_F32 && msg == DGLB200_MSG_COPY_SRC && red == DGLB200_RED_SUM,
+                    "spmm: a bf16 halo operand needs fp32 copy_src -> sum");
+    DGLB200_REQUIRE(vec && !ragged && aligned16(a.x_halo) && a.feat % 8 == 0 && a.halo_first >= 0,
+                    "spmm: a bf16 halo operand needs 16-byte aligned operands and feat a multiple of 8");
+  }
   a.slab_chunks = 0;
   if (vec && msg != DGLB200_MSG_COPY_EDGE && x_rows > 0)
     a.slab_chunks = pick_slab_chunks(x_rows, nnz, (size_t)a.feat * (dtype == DGLB200_F32 ? 4 : 2));
@@ -208,7 +219,7 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
 #define FIX(T, R)                                                                          \
   spmm_fixup<T, R><<<grid, 128, 0, stream>>>(a.long_rows + base, a.chunk_ptr + base, n,    \
                                              a.partial, a.partial_arg, a.feat, a.y_ld,     \
-                                             static_cast<T*>(a.y), a.arg)
+                                             static_cast<T*>(a.y), a.arg, a.accumulate)
       if (dtype == DGLB200_F32) {
         if (red == DGLB200_RED_SUM) FIX(float, DGLB200_RED_SUM); else FIX(float, DGLB200_RED_MAX);
       } else {
@@ -305,6 +316,15 @@ int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz, const 
                              int dtype, const void* x, int64_t x_ld, int64_t feat, const void* w,
                              int64_t w_width, void* y, int64_t y_ld, int32_t* arg,
                              const dglb200_spmm_plan_t* plan, void* stream) {
+  return dglb200_spmm_csr_ext(n_rows, x_rows, nnz, indptr, indices, eids, msg_op, reduce_op, dtype, x, x_ld,
+                              feat, w, w_width, y, y_ld, arg, plan, nullptr, stream);
+}
+
+int dglb200_spmm_csr_ext(int64_t n_rows, int64_t x_rows, int64_t nnz, const int64_t* indptr,
+                         const int32_t* indices, const int32_t* eids, int msg_op, int reduce_op,
+                         int dtype, const void* x, int64_t x_ld, int64_t feat, const void* w,
+                         int64_t w_width, void* y, int64_t y_ld, int32_t* arg,
+                         const dglb200_spmm_plan_t* plan, const dglb200_spmm_ext_t* ext, void* stream) {
   clear_error();
   DGLB200_REQUIRE(x_ld >= feat && y_ld >= feat, "spmm_csr: leading dimensions (%lld, %lld) < feat %lld",
                   (long long)x_ld, (long long)y_ld, (long long)feat);
@@ -341,6 +361,11 @@ int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz, const 
     a.w = nullptr;
   }
   if (reduce_op != DGLB200_RED_MAX) a.arg = nullptr;
+  if (ext != nullptr) {
+    a.accumulate = ext->accumulate != 0;
+    a.x_halo = ext->x_halo;
+    a.halo_first = ext->halo_first;
+  }
   return run_spmm(a, msg_op, reduce_op, dtype, plan, x_rows, nnz, static_cast<cudaStream_t>(stream));
 }
 

@@ -61,6 +61,9 @@ struct SpmmArgs {
   int w_slab_scalar;       // per-head weights, every feature pass inside one head: scalar variant
   int64_t nnz;
   int rows_per_group;      // consecutive row steps a group walks (launch_one; >= 1)
+  int accumulate;          // SUM: y += result (the caller sums several column blocks of the operand)
+  const void* x_halo;      // H16 kernels: bf16 rows of the column ids >= halo_first (multi-GPU halo kept
+  int64_t halo_first;      //   in wire precision: no widening pass, half the gather bytes), dense in feat
 };
 
 constexpr int kSpmmThreads = 128;  // measured: 128 > 256 > 512 on C2 at every slab width
@@ -95,8 +98,10 @@ constexpr int spmm_min_blocks(int msg, int red, int nt, int tiles, int elem_byte
 }
 
 template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads,
-          int WM = kWmAny>
+          int WM = kWmAny, bool H16 = false>
 __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)sizeof(T))) spmm_kernel(const SpmmArgs a) {
+  static_assert(!H16 || (std::is_same<T, float>::value && VEC == 4 && MSG == DGLB200_MSG_COPY_SRC),
+                "the mixed-precision halo gather exists for fp32 copy_src only");
   constexpr bool WS = (WM == kWmScalar);
   constexpr bool CW = (WM == kWmChunk);
   constexpr int RPW = 32 / G;  // items per warp
@@ -184,6 +189,13 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
     xb[t] = static_cast<const char*>(MSG == DGLB200_MSG_COPY_EDGE ? a.w : a.x) + fo * (int64_t)sizeof(T);
     wb[t] = static_cast<const char*>(a.w) + (CW ? fo / a.w_group : fo) * (int64_t)sizeof(T);
   }
+  // H16: column ids >= halo_first live in a bf16 array (2 bytes per element, dense rows)
+  const char* hb[TILES];
+  const uint32_t h_row_bytes = (uint32_t)(a.feat * 2);
+  const uint32_t h_first = (uint32_t)a.halo_first;
+#pragma unroll
+  for (int t = 0; t < TILES; ++t)
+    hb[t] = static_cast<const char*>(a.x_halo) + (fvalid[t] ? foff[t] : 0) * 2;
   const uint32_t wc_row_bytes = (uint32_t)(a.w_width * (int64_t)sizeof(T));   // kWmChunk: (E, H) rows
   const bool w_scalar = kMul && !CW && a.w != nullptr && (WS || a.w_mode == kWScalar);
   // kWmScalar also serves per-head weights when a feature pass never straddles two heads: the
@@ -243,7 +255,17 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
           for (int v = 0; v < VEC; ++v) st.xv[k][t][v] = kMax ? -INFINITY : 0.f;
         }
         if (ok) {
-          Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(xb[t], gid, row_bytes)), st.xv[k][t]);
+          if constexpr (H16) {
+            if (gid >= h_first) {      // halo row in wire precision: 8 bytes -> 4 floats (exact widening)
+              const uint2 hv = __ldg(reinterpret_cast<const uint2*>(row_ptr(hb[t], gid - h_first, h_row_bytes)));
+              st.xv[k][t][0] = bf16_lo(hv.x); st.xv[k][t][1] = bf16_hi(hv.x);
+              st.xv[k][t][2] = bf16_lo(hv.y); st.xv[k][t][3] = bf16_hi(hv.y);
+            } else {
+              Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(xb[t], gid, row_bytes)), st.xv[k][t]);
+            }
+          } else {
+            Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(xb[t], gid, row_bytes)), st.xv[k][t]);
+          }
           if constexpr (CW) {
             st.wc[k][t] = to_float(*reinterpret_cast<const T*>(row_ptr(wb[t], (uint32_t)st.e[k], wc_row_bytes)));
           }
@@ -407,6 +429,22 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
             if (v < nv) da[v] = best[t][v];
         }
       }
+      if (!kMax && a.accumulate) {      // y += result: add what is there, in one rounding per element
+        if (VEC == 1 || (nv == VEC && a.y_vec)) {
+          float old[VEC];
+          Chunk<T, VEC>::load(y + out_row * a.y_ld + foff[t], old);
+#pragma unroll
+          for (int v = 0; v < VEC; ++v) acc[t][v] += old[v];
+        } else {
+#pragma unroll
+          for (int v = 0; v < VEC; ++v)
+            if (v < nv) {
+              float one[1];
+              Chunk<T, 1>::load(y + out_row * a.y_ld + foff[t] + v, one);
+              acc[t][v] += one[0];
+            }
+        }
+      }
       if (VEC == 1 || (nv == VEC && a.y_vec)) {
         Chunk<T, VEC>::store(y + out_row * a.y_ld + foff[t], acc[t]);
       } else {
@@ -435,7 +473,7 @@ SpmmTuning& spmm_tuning();
 // ---- dispatch over (G, TILES, MSG, RED) for one storage type -----------------------------------
 
 template <typename T, int VEC, int G, int TILES, int MSG, int RED, int UCAP = 0, int NT = kSpmmThreads,
-          int WM = kWmAny>
+          int WM = kWmAny, bool H16 = false>
 int launch_one(const SpmmArgs& a, cudaStream_t stream) {
   constexpr int RPW = 32 / G;
   SpmmArgs args = a;
@@ -457,7 +495,7 @@ int launch_one(const SpmmArgs& a, cudaStream_t stream) {
                   (long long)blocks, (long long)slabs);
   if (blocks == 0) return 0;
   dim3 grid((unsigned)blocks, (unsigned)slabs);
-  spmm_kernel<T, VEC, G, TILES, MSG, RED, UCAP, NT, WM><<<grid, NT, 0, stream>>>(args);
+  spmm_kernel<T, VEC, G, TILES, MSG, RED, UCAP, NT, WM, H16><<<grid, NT, 0, stream>>>(args);
   DGLB200_POST_LAUNCH("spmm_kernel");
   return 0;
 }
@@ -499,6 +537,16 @@ int launch_shape(const SpmmArgs& a, cudaStream_t stream) {
   // L2-residency slabbing (run_spmm): a narrower pass keeps one feature slab of every source row
   // in the 126 MB L2 while all destination rows are visited; the slab index is blockIdx.y.
   if (a.slab_chunks > 0 && VEC > 1 && a.slab_chunks < chunks) chunks = a.slab_chunks;
+  if constexpr (std::is_same<T, float>::value && VEC == 4 && MSG == DGLB200_MSG_COPY_SRC &&
+                RED == DGLB200_RED_SUM && WM == kWmAny) {
+    if (a.x_halo != nullptr) {     // mixed-precision halo gather (multi-GPU bf16 wire)
+      if (chunks <= 4) return launch_one<T, VEC, 4, 1, MSG, RED, 0, kSpmmThreads, WM, true>(a, stream);
+      if (chunks <= 8) return launch_one<T, VEC, 8, 1, MSG, RED, 0, kSpmmThreads, WM, true>(a, stream);
+      if (chunks <= 16) return launch_one<T, VEC, 16, 1, MSG, RED, 0, kSpmmThreads, WM, true>(a, stream);
+      if (chunks <= 32) return launch_one<T, VEC, 32, 1, MSG, RED, 0, kSpmmThreads, WM, true>(a, stream);
+      return launch_one<T, VEC, 32, 2, MSG, RED, 0, kSpmmThreads, WM, true>(a, stream);
+    }
+  }
   if (chunks <= 4) return launch_one<T, VEC, 4, 1, MSG, RED, 0, kSpmmThreads, WM>(a, stream);
   if (chunks <= 8) return launch_one<T, VEC, 8, 1, MSG, RED, 0, kSpmmThreads, WM>(a, stream);
   if (chunks <= 16) return launch_one<T, VEC, 16, 1, MSG, RED, 0, kSpmmThreads, WM>(a, stream);

@@ -33,6 +33,11 @@ class SpmmPlanStruct(ctypes.Structure):
     ]
 
 
+class SpmmExtStruct(ctypes.Structure):
+    """Mirror of dglb200_spmm_ext_t (include/dgl_b200.h)."""
+    _fields_ = [("accumulate", c_i32), ("reserved", c_i32), ("x_halo", c_vp), ("halo_first", c_i64)]
+
+
 # name -> (restype, argtypes); must list every symbol of include/dgl_b200.h
 SIGNATURES = {
     "dglb200_abi_version": (c_int, []),
@@ -60,6 +65,9 @@ SIGNATURES = {
     "dglb200_spmm_csr_strided": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_int, c_int,
                                          c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
                                          ctypes.POINTER(SpmmPlanStruct), c_vp]),
+    "dglb200_spmm_csr_ext": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_int, c_int,
+                                     c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
+                                     ctypes.POINTER(SpmmPlanStruct), ctypes.POINTER(SpmmExtStruct), c_vp]),
     "dglb200_edge_data_to_slots": (c_int, [c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "dglb200_spmm_csr_backward_x": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_vp, c_i64,
                                             c_vp, c_i64, c_vp, c_vp,

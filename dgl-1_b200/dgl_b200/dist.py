@@ -46,7 +46,36 @@ PUSH_CTAS_PIPELINED = 128   # "push" mode: grid of a push that runs beside the S
 PUSH_CTAS = int(os.environ.get("DGL_B200_PUSH_CTAS", "0"))   # "signal" mode: grid bound of a push (0 = 2 CTAs per SM)
 TIMING = bool(int(os.environ.get("DGL_B200_TIMING", "0")))   # record events around the halo transfers
 COMM_PRIORITY = -1      # side stream of the exchange: higher priority than the compute stream
+# bf16 wire: the SpMM gathers the halo rows straight from the bf16 staging buffer (dglb200_spmm_csr_ext,
+# mixed-precision operand) instead of widening them into the fp32 buffer first: no extra pass over the
+# halo and half the gather bytes for 7/8 of the edges at 8 ranks
+MIXED_HALO = bool(int(os.environ.get("DGL_B200_MIXED_HALO", "1")))
+# all-gather partition: sum the column block of the rank's OWN source rows first (needs no exchange, so it
+# runs while every slab is still in flight), then add the remote column block slab by slab
+SPLIT_LOCAL = bool(int(os.environ.get("DGL_B200_SPLIT_LOCAL", "1")))
 ALLGATHER_SLAB = int(os.environ.get("DGL_B200_AG_SLAB", "64"))   # feature-slab width (elements) of the pipelined all-gather
+
+
+def chunk_fractions(chunks):
+    """Cumulative edge fractions at which a row block is cut into pipeline chunks.  The exchange is the
+    critical path on sparse graphs (C5 x 8: 3.3 ms of pushes against 2.5 ms of SpMM per op), so what is
+    left exposed is the first chunk's push and the LAST chunk's SpMM: both are kept small, the middle
+    chunks carry the bulk.  DGL_B200_CHUNK_FRACS="0.15,0.4,0.7,0.9,1" overrides."""
+    env = os.environ.get("DGL_B200_CHUNK_FRACS")
+    if env:
+        fr = [float(v) for v in env.split(",")]
+        if len(fr) == chunks and abs(fr[-1] - 1.0) < 1e-9 and all(b > a for a, b in zip(fr, fr[1:])):
+            return fr
+    if chunks <= 2:
+        return [(k + 1) / chunks for k in range(chunks)]
+    # first and last chunk half the weight of the middle ones
+    w = [0.5] + [1.0] * (chunks - 2) + [0.5]
+    tot, acc, fr = sum(w), 0.0, []
+    for v in w:
+        acc += v
+        fr.append(acc / tot)
+    fr[-1] = 1.0
+    return fr
 
 
 def transport_name(exchange):
@@ -141,6 +170,22 @@ def close_peer_mappings():
         _lib.check_call(lib.dglb200_ipc_close(ctypes.c_void_p(base)))
 
 
+def release_peer_memory(group=None):
+    """Collective: after every rank has dropped the exchange buffers it exported (part.release()), unmap
+    the peers' buffers here.  An exported allocation stays physically allocated until EVERY importer has
+    closed its mapping, so a process that rebuilds partitions (benchmarks, sweeps) must call this
+    between them or the exporters' memory accumulates."""
+    if dist.is_initialized():
+        dist.barrier(group=group)
+    if torch.cuda.is_available():
+        torch.cuda.synchronize()
+    close_peer_mappings()
+    if torch.cuda.is_available():
+        torch.cuda.empty_cache()
+    if dist.is_initialized():
+        dist.barrier(group=group)
+
+
 class PeerSignals(object):
     """Flag words of one exchange channel: `slots` x world int32 in THIS rank's memory, mapped into
     every peer.  Word [slot, q] is written by rank q only (and only ever grows: it carries the epoch
@@ -211,6 +256,8 @@ class RowPartition(object):
         else:
             self.loc_in, self.loc_out = csr_in, csr_out
         self._spmm = spmm_fn or (lambda csr, x, out: ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=x, out=out)[0])
+        self._spmm_is_default = spmm_fn is None
+        self._splits = {}         # id(csr) -> (own-column CSR, remote-column CSR)
         self._full = {}           # (key, feat, dtype) -> _Channel
         self._last = {}           # key -> channel of the last exchange under that key
         self._barrier = None
@@ -260,7 +307,7 @@ class RowPartition(object):
         return [full[self.bounds[p]:self.bounds[p + 1]] for p in range(self.world)]
 
     def release(self):
-        """Drop the exchange buffers (the peer mappings stay open until close_peer_mappings())."""
+        """Drop the exchange buffers (the peer mappings stay open until release_peer_memory())."""
         self._full.clear()
         self._last.clear()
         self._peer_on = False
@@ -340,6 +387,27 @@ class RowPartition(object):
             return [(0, feat)]
         return [(s0, w) for s0 in range(0, feat, w)]
 
+    def _split(self, csr):
+        """The row block cut by SOURCE owner: (edges whose source this rank owns, all other edges), both
+        over the global column space and with every row's slot order kept.  Plan-time integer work."""
+        key = id(csr)
+        sp = self._splits.get(key)
+        if sp is None:
+            cols = csr.indices
+            own = (cols >= self.r0) & (cols < self.r1)
+            rows = ops.csr_row_ids(csr)
+            parts = []
+            for m in (own, ~own):
+                cnt = torch.bincount(rows[m], minlength=csr.n_rows)
+                indptr = torch.zeros(csr.n_rows + 1, dtype=torch.int64, device=cols.device)
+                indptr[1:] = torch.cumsum(cnt, 0)
+                sub = ops.CSR(csr.n_rows, csr.n_cols, indptr, cols[m].contiguous(),
+                              csr.eids[m].contiguous() if csr.eids is not None else None)
+                sub.plan()
+                parts.append(sub)
+            sp = self._splits[key] = (parts[0], parts[1], csr)     # keep csr alive: id() is the key
+        return sp
+
     def _signal_push(self, ch, slabs, on_comm=True):
         """Enqueue the pushes of a new epoch: for every column slab ONE launch stores this rank's block
         into every peer's gather buffer and sets the slab's flag word on every rank.  The first launch
@@ -382,12 +450,18 @@ class RowPartition(object):
                 out = torch.empty((csr.n_rows, feat), dtype=local.dtype, device=local.device)
             slabs = self._slabs(feat, local.dtype)
             self._signal_push(ch, slabs)
+            split = self._split(csr) if (SPLIT_LOCAL and self._spmm_is_default) else None
+            if split is not None:
+                # own-source edges first: their operand rows are already here, the pushes run meanwhile
+                ops.spmm(split[0], ops.MSG_COPY_SRC, ops.RED_SUM, x=full, out=out)
+                csr = split[1]
             for i, (s0, w) in enumerate(slabs):
                 ops.peer_wait(ch.sig.local(i), ch.epoch, ch.sig.err)
-                if len(slabs) == 1:
-                    self._spmm(csr, full, out)
+                xs, os_ = (full, out) if len(slabs) == 1 else (full[:, s0:s0 + w], out[:, s0:s0 + w])
+                if split is not None:
+                    ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=xs, out=os_, accumulate=True)
                 else:
-                    self._spmm(csr, full[:, s0:s0 + w], out[:, s0:s0 + w])
+                    self._spmm(csr, xs, os_)
             ops.peer_signal(ch.sig.remote(ch.sig.slots - 1), ch.epoch, full.device)   # buffer released
             torch.cuda.current_stream(full.device).wait_stream(self._comm)   # my block may be rewritten only after my pushes
             return out
@@ -487,7 +561,8 @@ class HaloExchange(object):
         self.chunks = max(1, int(chunks)) if world > 1 else 1
         # edge-balanced row chunks of the block
         ip = csr_block.indptr
-        tgt = torch.arange(1, self.chunks, dtype=torch.float64, device=dev) * (float(ip[-1]) / self.chunks)
+        fr = chunk_fractions(self.chunks)
+        tgt = torch.tensor(fr[:-1], dtype=torch.float64, device=dev) * float(ip[-1])
         cuts = torch.searchsorted(ip.to(torch.float64), tgt).clamp_(max=self.rows).tolist()
         self.row_cuts = [0] + [int(c) for c in cuts] + [self.rows]
         for i in range(1, len(self.row_cuts)):
@@ -564,6 +639,7 @@ class HaloExchange(object):
             self._rows_of_rank = [int(objs[r][2]) for r in range(world)]
         self.chunk_csr = None
         self.timing = []
+        self.timeline = []        # TIMING: per op [op start, wait_0 done, spmm_0 done, wait_1 done, ...] events (compute stream)
         self._chan = {}           # (feat, dtype) -> _Channel
         self._cur = None          # channel of the last call
         self._peer_on = False
@@ -712,6 +788,19 @@ class HaloExchange(object):
             ops.gather_rows_convert(ch.wire[h0:h0 + cnt], None,
                                     out=ch.buf[self.chunk_start[k]:self.chunk_start[k] + cnt])
 
+    def _mixed(self, ch):
+        return ch.wire is not None and MIXED_HALO and ch.buf.shape[1] % 8 == 0
+
+    def chunk_spmm(self, ch, k, csr_k, out_k, spmm_fn):
+        """The SpMM over one row chunk once its halo has landed.  bf16 wire: the kernel reads own rows
+        from the fp32 block and halo rows from the bf16 staging buffer (k = None: the whole block)."""
+        if self._mixed(ch):
+            return ops.spmm(csr_k, ops.MSG_COPY_SRC, ops.RED_SUM, x=ch.buf[:self.rows], out=out_k,
+                            x_halo=ch.wire, halo_first=self.rows)[0]
+        if ch.wire is not None and k is not None:
+            self._widen_chunk(k, ch)
+        return spmm_fn(csr_k, ch.buf, out_k)
+
     def _own_rows(self, ch, x_local):
         own = ch.buf[:self.rows]
         if own.data_ptr() != x_local.data_ptr():
@@ -767,7 +856,7 @@ class HaloExchange(object):
             return self._aggregate_pushed(ch, x_local, spmm_fn, out)
         buf = ch.buf
         self._own_rows(ch, x_local)
-        if not x_local.is_cuda:                                   # CPU (gloo tests): same schedule, no streams
+        if not x_local.is_cuda and ch.peer is None:               # CPU (gloo tests): same schedule, no streams
             for k, csr_k in enumerate(self.row_chunks()):
                 self._fetch_chunk(k, ch)
                 if csr_k.n_rows:
@@ -819,11 +908,28 @@ class HaloExchange(object):
                     b.record()
                     self.timing.append((a, b))
         chunk_csrs = self.row_chunks() if self.chunks > 1 else [self.csr]
+        tl = [] if TIMING else None
+        if TIMING:
+            e0 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            tl.append(e0)
         for k, csr_k in enumerate(chunk_csrs):
             ops.peer_wait(ch.sig.local(k), ch.epoch, ch.sig.err)
-            self._widen_chunk(k, ch)
+            if TIMING:
+                ew = torch.cuda.Event(enable_timing=True)
+                ew.record()
+                tl.append(ew)
             if csr_k.n_rows:
-                spmm_fn(csr_k, buf, out[self.row_cuts[k]:self.row_cuts[k + 1]] if self.chunks > 1 else out)
+                self.chunk_spmm(ch, k, csr_k, out[self.row_cuts[k]:self.row_cuts[k + 1]] if self.chunks > 1 else out,
+                                spmm_fn)
+            elif ch.wire is not None and not self._mixed(ch):
+                self._widen_chunk(k, ch)
+            if TIMING:
+                es = torch.cuda.Event(enable_timing=True)
+                es.record()
+                tl.append(es)
+        if TIMING:
+            self.timeline.append(tl)
         ops.peer_signal(ch.sig.remote(ch.sig.slots - 1), ch.epoch, buf.device)    # my buffer is free again
         cur.wait_stream(self._comm)        # my block may be rewritten only after my pushes have read it
         return out
@@ -885,6 +991,12 @@ class HaloPartition(RowPartition):
 
     def operand(self, key, feat, like):
         return self._halo(key).buffer(feat, like)
+
+    def local_spmm(self, csr, x, out):
+        h = self.halo_in if csr is self.loc_in else self.halo_out
+        if h._cur is not None and h._mixed(h._cur):
+            return h.chunk_spmm(h._cur, None, csr, out, self._spmm)
+        return self._spmm(csr, x, out)
 
     def release(self):
         self.halo_in.release()

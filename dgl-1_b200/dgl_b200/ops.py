@@ -268,10 +268,12 @@ def _slot_ordered_weights(csr, w, w_width, feat, need_eids):
 
 
 def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chunk=DEFAULT_CHUNK,
-         out=None):
+         out=None, accumulate=False, x_halo=None, halo_first=0):
     """y[r] = reduce over row r of msg(x[indices], w[eids]); 2-D (rows, feat) tensors.
 
     Returns (y, arg) where arg is int32 (rows, feat) for RED_MAX with want_arg, else None.
+    accumulate: y (= out) += result (SUM).  x_halo / halo_first: column ids >= halo_first are rows of the
+    bfloat16 tensor x_halo (fp32 copy_src -> sum only; dglb200_spmm_csr_ext).
     """
     lib = _lib.get_lib()
     ref = x if x is not None else w
@@ -288,8 +290,11 @@ def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chun
     if x is not None:
         if not rows_ok(x):
             x = x.contiguous()
-        if x.shape[0] != csr.n_cols:
+        if x_halo is None and x.shape[0] != csr.n_cols:
             raise DGLError("spmm: x has %d rows, CSR has %d columns" % (x.shape[0], csr.n_cols))
+        if x_halo is not None and (x_halo.dtype != torch.bfloat16 or not x_halo.is_contiguous()
+                                   or x_halo.shape[1] != x.shape[1] or halo_first > x.shape[0]):
+            raise DGLError("spmm: x_halo must be a contiguous bfloat16 (rows, feat) tensor and halo_first <= len(x)")
     if w is not None:
         w = w.contiguous()
         if w.dtype != ref.dtype:
@@ -314,11 +319,20 @@ def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chun
     eids = csr.eids
     if msg_op == MSG_SRC_MUL_EDGE:
         w, eids = _slot_ordered_weights(csr, w, w_width, feat, need_eids=arg is not None)
+    ext_ref = None
+    if accumulate or x_halo is not None:
+        if accumulate and out is None:
+            raise DGLError("spmm: accumulate needs `out`")
+        ext = _lib.SpmmExtStruct()
+        ext.accumulate = 1 if accumulate else 0
+        ext.x_halo = x_halo.data_ptr() if x_halo is not None else None
+        ext.halo_first = int(halo_first)
+        ext_ref = ctypes.byref(ext)
     with torch.cuda.device(ref.device):
-        _lib.check_call(lib.dglb200_spmm_csr_strided(
+        _lib.check_call(lib.dglb200_spmm_csr_ext(
             csr.n_rows, csr.n_cols, csr.nnz, _ptr(csr.indptr), _ptr(csr.indices), _ptr(eids),
             msg_op, reduce_op, dt, _ptr(x), max(x_ld, feat), feat, _ptr(w), w_width, _ptr(y),
-            max(y_ld, feat), _ptr(arg), plan_ref, _stream()))
+            max(y_ld, feat), _ptr(arg), plan_ref, ext_ref, _stream()))
     return y, arg
 
 

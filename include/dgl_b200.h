@@ -203,6 +203,30 @@ int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz,
                              const dglb200_spmm_plan_t* plan, void* stream);
 
 /*
+ * Extended form for the multi-GPU row partition (dgl_b200/dist.py; no counterpart in the reference):
+ *   accumulate != 0  SUM only: y += result.  A rank sums the column block of its OWN source rows first
+ *                    (no exchange needed) and adds the remote column blocks as their rows arrive.
+ *   x_halo != NULL   fp32 copy_src -> sum only: column ids >= halo_first are rows of a SECOND operand kept
+ *                    in bfloat16 (row id - halo_first, dense [*, feat], feat a multiple of 8): the halo
+ *                    rows stay in the precision they crossed NVLink in (DGL_B200_WIRE=bf16), accumulation
+ *                    is fp32; results within the bf16 bar (1e-2), own rows exact.
+ * ext == NULL is dglb200_spmm_csr_strided.
+ */
+typedef struct dglb200_spmm_ext_t {
+  int32_t accumulate;
+  int32_t reserved;
+  const void* x_halo;
+  int64_t halo_first;
+} dglb200_spmm_ext_t;
+int dglb200_spmm_csr_ext(int64_t n_rows, int64_t x_rows, int64_t nnz,
+                         const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                         int msg_op, int reduce_op, int dtype,
+                         const void* x, int64_t x_ld, int64_t feat,
+                         const void* w, int64_t w_width,
+                         void* y, int64_t y_ld, int32_t* arg,
+                         const dglb200_spmm_plan_t* plan, const dglb200_spmm_ext_t* ext, void* stream);
+
+/*
  * Narrow edge data (a scalar or one weight per head) in edge-id order -> CSR slot order:
  * out[p, :] = w[eids[p], :], p in [0, nnz), rows of row_bytes bytes (even, <= 4096).
  * The SpMM kernels index edge data with e(p) = eids[p], or p itself when eids == NULL; on a large

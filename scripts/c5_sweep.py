@@ -64,30 +64,39 @@ def main():
     del ref
     torch.cuda.empty_cache()
 
-    grid = []
-    chunk_list = (4,) if args.quick else (1, 2, 4, 8)
-    for chunks in chunk_list:
-        for mode in ("signal", "push"):
-            for wire in ("f32", "bf16"):
-                for ctas in ((0,) if (mode == "push" or args.quick) else (0, 148, 592)):
-                    if mode == "push" and chunks not in (1, 4):
-                        continue
-                    grid.append((chunks, mode, wire, ctas))
-    part, part_chunks = None, None
+    # (chunks, chunk fractions or None = default, transport, wire, push grid)
+    if args.quick:
+        grid = [(4, None, "signal", "f32", 0), (4, None, "signal", "bf16", 0)]
+    else:
+        grid = [(1, None, "signal", "f32", 0),
+                (4, None, "signal", "f32", 0), (4, "0.25,0.5,0.75,1", "signal", "f32", 0),
+                (4, "0.1,0.35,0.7,1", "signal", "f32", 0), (4, None, "signal", "f32", 592),
+                (6, None, "signal", "f32", 0), (8, None, "signal", "f32", 0),
+                (8, "0.05,0.15,0.3,0.45,0.6,0.75,0.9,1", "signal", "f32", 0),
+                (1, None, "signal", "bf16", 0), (2, None, "signal", "bf16", 0),
+                (4, None, "signal", "bf16", 0), (4, "0.1,0.35,0.7,1", "signal", "bf16", 0),
+                (8, None, "signal", "bf16", 0),
+                (4, None, "push", "f32", 0)]
+    part, part_key = None, None
     dmod.TIMING = True
-    for chunks, mode, wire, ctas in grid:
-        if part is None or part_chunks != chunks:
-            if part is not None:
-                part.release()
+    for chunks, fracs, mode, wire, ctas in grid:
+        if part is not None:
+            part.release()
+            dmod.release_peer_memory()
+        if part is None or part_key != (chunks, fracs):
+            part = None
+            torch.cuda.empty_cache()
+            if fracs:
+                os.environ["DGL_B200_CHUNK_FRACS"] = fracs
+            else:
+                os.environ.pop("DGL_B200_CHUNK_FRACS", None)
             t0 = time.time()
             part = dmod.HaloPartition(csr_in, csr_out, rank=rank, world=world, chunks=chunks)
             part.loc_in.plan()
             part.loc_out.plan()
             torch.cuda.synchronize()
             plan_s = time.time() - t0
-            part_chunks = chunks
-        else:
-            part.release()
+            part_key = (chunks, fracs)
         torch.cuda.empty_cache()
         dmod.PULL_MODE, dmod.WIRE, dmod.PUSH_CTAS = mode, wire, ctas
         part.enable_peer_transport(feat, like)
@@ -109,8 +118,9 @@ def main():
         ok = ok and part.comm_errors() == 0
         flag = torch.tensor([1 if ok else 0], device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-        part.halo_in.timing.clear()
-        part.halo_out.timing.clear()
+        for h in (part.halo_in, part.halo_out):
+            h.timing.clear()
+            h.timeline.clear()
         dist.barrier()
         torch.cuda.synchronize()
         a, b = ev(), ev()
@@ -131,6 +141,15 @@ def main():
         kb.record()
         torch.cuda.synchronize()
         k_ms = ka.elapsed_time(kb) / 3
+        # timeline of the last forward op on this rank (ms after the op's start on the compute stream):
+        # push k [start, end] on the exchange stream; chunk k [halo landed, SpMM done] on the compute stream
+        tl = None
+        if part.halo_in.timeline:
+            evs = part.halo_in.timeline[-1]
+            pushes = part.halo_in.timing[-chunks:]
+            tl = {"push": [[round(evs[0].elapsed_time(p), 3), round(evs[0].elapsed_time(q), 3)] for p, q in pushes],
+                  "chunk": [[round(evs[0].elapsed_time(evs[1 + 2 * k]), 3), round(evs[0].elapsed_time(evs[2 + 2 * k]), 3)]
+                            for k in range(chunks)]}
         tm = [p.elapsed_time(q) for h in (part.halo_in, part.halo_out) for p, q in h.timing]
         push_ms = sum(tm) / max(len(tm), 1) * chunks          # per SpMM op: all chunks
         t = torch.tensor([ms, k_ms, push_ms], device=dev, dtype=torch.float64)
@@ -142,7 +161,9 @@ def main():
                    "kernel_ms_per_step_by_rank": [round(float(v[1]), 3) for v in allt],
                    "push_ms_per_op_by_rank": [round(float(v[2]), 3) for v in allt],
                    "halo_bytes_per_rank_per_op": part.exchange_bytes(feat), "plan_s": round(plan_s, 1),
-                   "checked": int(flag.item()) == 1}
+                   "chunk_fracs": fracs, "rows_per_chunk": [part.halo_in.row_cuts[k + 1] - part.halo_in.row_cuts[k] for k in range(chunks)],
+                   "halo_rows_per_chunk": [sum(c) for c in part.halo_in.recv_counts],
+                   "timeline_fwd_rank0_ms": tl, "checked": int(flag.item()) == 1}
             print(json.dumps(rec), flush=True)
             out_lines.append(rec)
         del x_loc, dy_loc, y, dx

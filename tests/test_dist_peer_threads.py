@@ -239,8 +239,11 @@ def test_row_partition_peer_all_gather(peers, monkeypatch, mode, feat, slab):
         assert part.comm_errors() == 0
     _run(world, td, per_rank)
     got.sort(key=lambda p: p[0])
-    assert torch.equal(torch.cat([g[1] for g in got]), want_y)
-    assert torch.equal(torch.cat([g[2] for g in got]), want_dx)
+    for have, want in ((torch.cat([g[1] for g in got]), want_y), (torch.cat([g[2] for g in got]), want_dx)):
+        # signal transport: own-source block first, remote block accumulated (one more rounding)
+        assert float((have - want).abs().max()) <= 1e-5 * float(want.abs().max())
+        if mode != "signal" or feat % 4:
+            assert torch.equal(have, want)
 
 
 def test_two_widths_keep_their_own_peer_buffers(peers, monkeypatch):
@@ -279,8 +282,11 @@ def test_two_widths_keep_their_own_peer_buffers(peers, monkeypatch):
             td._bar.wait()
             for f in (8, 4):
                 ys = sorted(got[f], key=lambda p: p[0])
-                assert torch.equal(torch.cat([g[1] for g in ys]), want[f][0])
-                assert torch.equal(torch.cat([g[2] for g in ys]), want[f][1])
+                for col in (1, 2):
+                    have, ref = torch.cat([g[col] for g in ys]), want[f][col - 1]
+                    assert float((have - ref).abs().max()) <= 1e-5 * float(ref.abs().max())
+                    if cls is dmod.HaloPartition:
+                        assert torch.equal(have, ref)
             td._bar.wait()
     _run(world, td, per_rank)
     assert all(raised)

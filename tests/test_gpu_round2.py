@@ -207,9 +207,13 @@ def _two_rank_worker(rank, world, port, ret):
                 dx = part.backward(dl)
             torch.cuda.synchronize()
             wy, wdx = 4 * want_y[part.r0:part.r1], 4 * want_dx[part.r0:part.r1]
-            if wire == "f32":
+            if wire == "f32" and not (kind == "row" and mode == "signal"):
                 # halo: the remapped CSR keeps every row's slot order -> bit-exact; row partition too
                 ok = torch.equal(y, wy) and torch.equal(dx, wdx)
+            elif wire == "f32":
+                # own-source block first, remote block accumulated: one more rounding per element
+                tol = 1e-5 * float(wy.abs().max())
+                ok = float((y - wy).abs().max()) <= tol and float((dx - wdx).abs().max()) <= tol
             else:
                 tol = 1e-2 * float(wy.abs().max())
                 ok = float((y - wy).abs().max()) <= tol and float((dx - wdx).abs().max()) <= tol

@@ -387,3 +387,45 @@ def test_multi_head_weights_max_bf16_gradient(heads, dim):
     finally:
         ops.SLOT_ORDER_MIN_NNZ = old
     assert torch.equal(y0, y1) and torch.equal(dx, dx1)
+
+
+@pytest.mark.parametrize("feat", [8, 64, 128, 256])
+@pytest.mark.parametrize("chunk", [0, 64])
+def test_accumulate_and_bf16_halo_operand(feat, chunk):
+    """dglb200_spmm_csr_ext, the two extensions of the multi-GPU row partition: (a) accumulate - the sum
+    over two column blocks of the operand, second call adding into the first's output, is bit for bit
+    y_a + y_b and within 1e-5 of the oracle over all edges; (b) column ids >= halo_first read from a
+    bfloat16 second operand: identical bits to the fp32 kernel over the same rows widened beforehand."""
+    from dgl_b200 import ops
+    n, own = 400, 250
+    src, dst = random_graph(n, 7000, 31 + feat, hubs=2, hub_deg=900, zero_deg_frac=0.2)
+    rng = np.random.RandomState(feat)
+    x = rng.randn(n, feat).astype(np.float32)
+    xt = torch.from_numpy(x).cuda()
+    # (a) split the edges by source: [0, own) and [own, n)
+    local = src < own
+    csr_a = _csr(src[local], dst[local], n)
+    csr_b = _csr(src[~local], dst[~local], n)
+    ya = ops.spmm(csr_a, ops.MSG_COPY_SRC, ops.RED_SUM, x=xt, chunk=chunk)[0]
+    yb = ops.spmm(csr_b, ops.MSG_COPY_SRC, ops.RED_SUM, x=xt, chunk=chunk)[0]
+    acc = ya.clone()
+    ops.spmm(csr_b, ops.MSG_COPY_SRC, ops.RED_SUM, x=xt, chunk=chunk, out=acc, accumulate=True)
+    assert torch.equal(acc, ya + yb)
+    _close(acc, oracle.update_all(src, dst, n, "copy_src", "sum", x=x), RTOL_F32)
+    # a strided column block of a wider output, accumulated in place
+    wide = torch.zeros(n, feat + 8, device="cuda")
+    wide[:, 4:4 + feat] = ya
+    if feat % 4 == 0:
+        ops.spmm(csr_b, ops.MSG_COPY_SRC, ops.RED_SUM, x=xt, chunk=chunk, out=wide[:, 4:4 + feat], accumulate=True)
+        assert torch.equal(wide[:, 4:4 + feat], ya + yb) and float(wide[:, :4].abs().max()) == 0.0
+    with pytest.raises(Exception):
+        ops.spmm(csr_b, ops.MSG_COPY_SRC, ops.RED_MAX, x=xt, out=acc, accumulate=True)
+    # (b) rows [own, n) of the operand live in bf16
+    csr = _csr(src, dst, n)
+    halo = xt[own:].bfloat16().contiguous()
+    widened = torch.cat([xt[:own], halo.float()])
+    want = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=widened, chunk=chunk)[0]
+    got = ops.spmm(csr, ops.MSG_COPY_SRC, ops.RED_SUM, x=xt[:own].contiguous(), chunk=chunk, x_halo=halo,
+                   halo_first=own)[0]
+    assert torch.equal(got, want)
+    _close(got, oracle.update_all(src, dst, n, "copy_src", "sum", x=x), RTOL_BF16)

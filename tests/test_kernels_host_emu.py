@@ -158,6 +158,11 @@ def test_spmm_max_propagates_nan(emu):
     t_spmm.test_max_propagates_nan(4)
 
 
+@pytest.mark.parametrize("feat,chunk", [(8, 0), (128, 64)])
+def test_spmm_accumulate_and_bf16_halo(emu, feat, chunk):
+    t_spmm.test_accumulate_and_bf16_halo_operand(feat, chunk)
+
+
 def test_spmm_backward_x_max(emu):
     t_spmm.test_backward_x_max()
 
