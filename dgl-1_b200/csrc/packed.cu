@@ -22,45 +22,11 @@
 
 #include "common.cuh"
 
+#include "packed_common.cuh"
+
 namespace dglb200 {
-namespace {
+namespace packed {
 
-// --- minimal mirror of the C types of c_runtime_api.h / dlpack.h (ABI, not code) ---
-typedef union {
-  int64_t v_int64;
-  double v_float64;
-  void* v_handle;
-  const char* v_str;
-} RefValue;  // DGLValue (c_runtime_api.h:122-129); the two struct members are 8 bytes as well
-
-enum { kRefInt = 0, kRefFloat = 2, kRefHandle = 3, kRefNull = 4, kRefArrayHandle = 7,
-       kRefFuncHandle = 10, kRefNDArrayContainer = 13 };  // c_runtime_api.h:66-91
-
-struct RefDLTensor {  // dlpack.h DLTensor
-  void* data;
-  int32_t device_type;
-  int32_t device_id;
-  int32_t ndim;
-  uint8_t code;
-  uint8_t bits;
-  uint16_t lanes;
-  int64_t* shape;
-  int64_t* strides;
-  uint64_t byte_offset;
-};
-
-typedef int (*PackedCFunc)(RefValue* args, int* type_codes, int num_args, void* ret, void* resource);
-typedef void (*PackedCFuncFinalizer)(void* resource);
-
-struct LibDgl {
-  int (*FuncCreateFromCFunc)(PackedCFunc, void*, PackedCFuncFinalizer, void**) = nullptr;
-  int (*FuncRegisterGlobal)(const char*, void*, int) = nullptr;
-  int (*FuncFree)(void*) = nullptr;
-  int (*CFuncSetReturn)(void*, RefValue*, int*, int) = nullptr;
-  void (*APISetLastError)(const char*) = nullptr;
-  int (*ArrayAlloc)(const int64_t*, int, int, int, int, int, int, RefDLTensor**) = nullptr;
-  int (*ArrayFree)(RefDLTensor*) = nullptr;
-};
 LibDgl g_dgl;
 
 int fail(const char* where) {
@@ -84,6 +50,26 @@ int ret_int(void* ret, int64_t value) {
   int code = kRefInt;
   return g_dgl.CFuncSetReturn(ret, &v, &code, 1);
 }
+
+int register_one(const char* name, PackedCFunc fn, int override_existing) {
+  void* h = nullptr;
+  if (g_dgl.FuncCreateFromCFunc(fn, nullptr, nullptr, &h) != 0) {
+    set_error("DGLFuncCreateFromCFunc failed for %s", name);
+    return -1;
+  }
+  if (g_dgl.FuncRegisterGlobal(name, h, override_existing) != 0) {
+    set_error("DGLFuncRegisterGlobal failed for %s", name);
+    g_dgl.FuncFree(h);
+    return -1;
+  }
+  g_dgl.FuncFree(h);  // the registry holds its own copy (src/runtime/registry.cc:129-135)
+  return 0;
+}
+
+}  // namespace packed
+
+using namespace packed;
+namespace {
 
 int pf_version(RefValue*, int*, int, void* ret, void*) { return ret_int(ret, dglb200_abi_version()); }
 int pf_launch_count(RefValue*, int*, int, void* ret, void*) { return ret_int(ret, dglb200_launch_count()); }
@@ -206,21 +192,6 @@ int pf_degree_bucketing(RefValue* a, int* c, int n, void* ret, void*) {
   return rc;
 }
 
-int register_one(const char* name, PackedCFunc fn, int override_existing) {
-  void* h = nullptr;
-  if (g_dgl.FuncCreateFromCFunc(fn, nullptr, nullptr, &h) != 0) {
-    set_error("DGLFuncCreateFromCFunc failed for %s", name);
-    return -1;
-  }
-  if (g_dgl.FuncRegisterGlobal(name, h, override_existing) != 0) {
-    set_error("DGLFuncRegisterGlobal failed for %s", name);
-    g_dgl.FuncFree(h);
-    return -1;
-  }
-  g_dgl.FuncFree(h);  // the registry holds its own copy (src/runtime/registry.cc:129-135)
-  return 0;
-}
-
 }  // namespace
 }  // namespace dglb200
 
@@ -239,6 +210,8 @@ extern "C" int dglb200_register_packed_funcs(void* libdgl_handle, int override_r
   DGLB200_SYM(APISetLastError, "DGLAPISetLastError");
   DGLB200_SYM(ArrayAlloc, "DGLArrayAlloc");
   DGLB200_SYM(ArrayFree, "DGLArrayFree");
+  DGLB200_SYM(FuncGetGlobal, "DGLFuncGetGlobal");
+  DGLB200_SYM(FuncCall, "DGLFuncCall");
 #undef DGLB200_SYM
   int n = 0;
   if (register_one("b200._CAPI_DGLB200Version", pf_version, 1) != 0) return -1; ++n;
@@ -249,6 +222,10 @@ extern "C" int dglb200_register_packed_funcs(void* libdgl_handle, int override_r
   if (override_reference) {
     if (register_one("runtime.degree_bucketing._CAPI_DGLDegreeBucketing", pf_degree_bucketing, 1) != 0) return -1;
     ++n;
+    // device-resident graph index behind the reference's own names (packed_graph.cu)
+    const int g = register_graph_overrides();
+    if (g < 0) return -1;
+    n += g;
   }
   return n;
 }

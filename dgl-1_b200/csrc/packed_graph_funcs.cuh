@@ -1,0 +1,248 @@
+// Second half of packed_graph.cu (one translation unit): the PackedFunc bodies and their registration.
+#pragma once
+
+namespace dglb200 {
+namespace packed {
+namespace {
+
+// ---- _CAPI_DGLGraphGetAdj(handle, transpose, fmt) ---------------------------------------------------
+int pf_get_adj(RefValue* a, int* c, int n, void* ret, void*) {
+  const char* who = "graph_index._CAPI_DGLGraphGetAdj[b200]";
+  if (n != 3 || c[2] != kRefStr) { set_error("expects (handle, transpose, fmt)"); return fail(who); }
+  void* handle = as_ptr(a[0], c[0]);
+  const bool transpose = as_int(a[1], c[1]) != 0;
+  const std::string fmt = a[2].v_str ? a[2].v_str : "";
+  DevIndex* ix = get_index(handle);
+  if (ix == nullptr) return fail(who);
+  ArrayList* res = new ArrayList();
+  if (fmt == "coo") {
+    // idx[2E] = [dst | src] (transpose: [src | dst]) in edge-id order + the identity eid (graph.cc:509-524)
+    RefDLTensor* idx = cpu_ids(2 * ix->e);
+    if (idx && ix->e > 0) {
+      const int64_t* first = transpose ? ix->src.as<int64_t>() : ix->dst.as<int64_t>();
+      const int64_t* second = transpose ? ix->dst.as<int64_t>() : ix->src.as<int64_t>();
+      int64_t* h = static_cast<int64_t*>(idx->data);
+      if (cudaMemcpy(h, first, (size_t)ix->e * 8, cudaMemcpyDeviceToHost) != cudaSuccess ||
+          cudaMemcpy(h + ix->e, second, (size_t)ix->e * 8, cudaMemcpyDeviceToHost) != cudaSuccess) {
+        set_error("cudaMemcpy D2H failed");
+        g_dgl.ArrayFree(idx);
+        idx = nullptr;
+      }
+    }
+    res->arr = {idx, iota(ix->e)};
+  } else if (fmt == "csr") {
+    // rows = dst (in-edges; transpose: rows = src), adjacency-list order inside a row (graph.cc:525-549)
+    const DevCsr& csr = transpose ? ix->out : ix->in;
+    DevMem wide;
+    if (wide.alloc((size_t)ix->e * 8) != 0) { delete res; set_error("cudaMalloc failed"); return fail(who); }
+    RefDLTensor* indptr = from_device(csr.ptr.as<int64_t>(), ix->n + 1);
+    RefDLTensor *indices = nullptr, *eid = nullptr;
+    if (dglb200_widen_i32_to_i64(ix->e, csr.idx.as<int32_t>(), wide.as<int64_t>(), nullptr) == 0)
+      indices = from_device(wide.as<int64_t>(), ix->e);
+    if (dglb200_widen_i32_to_i64(ix->e, csr.eid.as<int32_t>(), wide.as<int64_t>(), nullptr) == 0)
+      eid = from_device(wide.as<int64_t>(), ix->e);
+    res->arr = {indptr, indices, eid};
+  } else {
+    delete res;
+    set_error("unsupported format");      // LOG(FATAL) << "unsupported format", graph.cc:551
+    return fail(who);
+  }
+  if (return_list(res, ret) != 0) return fail(who);
+  return 0;
+}
+
+// ---- _CAPI_DGLGraphInEdges_2 / OutEdges_2 (handle, vids) -> {src, dst, eid} ------------------------
+int edges_of(RefValue* a, int* c, int n, void* ret, bool in_edges, const char* who) {
+  if (n != 2) { set_error("expects (handle, vids)"); return fail(who); }
+  const RefDLTensor* vids = static_cast<const RefDLTensor*>(a[1].v_handle);
+  if (!(c[1] == kRefArrayHandle || c[1] == kRefNDArrayContainer) || !valid_ids(vids)) {
+    set_error("Invalid vertex id array.");
+    return fail(who);
+  }
+  DevIndex* ix = get_index(as_ptr(a[0], c[0]));
+  if (ix == nullptr) return fail(who);
+  const int64_t k = vids->shape[0];
+  const DevCsr& csr = in_edges ? ix->in : ix->out;
+  size_t ws_bytes = 0;
+  dglb200_csr_select_workspace_bytes(k, &ws_bytes);
+  DevMem d_v, d_off, ws, d_row, d_col, d_eid;
+  if (d_v.alloc((size_t)k * 8) || d_off.alloc((size_t)(k + 1) * 8) || ws.alloc(ws_bytes)) {
+    set_error("cudaMalloc failed");
+    return fail(who);
+  }
+  if (k > 0) cudaMemcpy(d_v.p, (char*)vids->data + vids->byte_offset, (size_t)k * 8, cudaMemcpyHostToDevice);
+  int64_t total = 0;
+  if (dglb200_csr_select_offsets(k, d_v.as<int64_t>(), ix->n, csr.ptr.as<int64_t>(), d_off.as<int64_t>(), &total,
+                                 ws.p, ws_bytes, nullptr) != 0)
+    return fail(who);                       // "Invalid vertex: ..." like the reference's CHECK (graph.cc:299)
+  if (d_row.alloc((size_t)total * 8) || d_col.alloc((size_t)total * 8) || d_eid.alloc((size_t)total * 8)) {
+    set_error("cudaMalloc failed");
+    return fail(who);
+  }
+  if (dglb200_csr_select_expand(k, total, d_v.as<int64_t>(), d_off.as<int64_t>(), csr.ptr.as<int64_t>(),
+                                csr.idx.as<int32_t>(), csr.eid.as<int32_t>(), nullptr, nullptr,
+                                d_row.as<int64_t>(), d_col.as<int64_t>(), d_eid.as<int64_t>(), nullptr) != 0)
+    return fail(who);
+  ArrayList* res = new ArrayList();
+  RefDLTensor* rows = from_device(d_row.as<int64_t>(), total);
+  RefDLTensor* cols = from_device(d_col.as<int64_t>(), total);
+  RefDLTensor* eids = from_device(d_eid.as<int64_t>(), total);
+  // in-edges: the selected node is the DESTINATION (src = column); out-edges: it is the source
+  res->arr = in_edges ? std::vector<RefDLTensor*>{cols, rows, eids} : std::vector<RefDLTensor*>{rows, cols, eids};
+  if (return_list(res, ret) != 0) return fail(who);
+  return 0;
+}
+int pf_in_edges(RefValue* a, int* c, int n, void* ret, void*) {
+  return edges_of(a, c, n, ret, true, "graph_index._CAPI_DGLGraphInEdges_2[b200]");
+}
+int pf_out_edges(RefValue* a, int* c, int n, void* ret, void*) {
+  return edges_of(a, c, n, ret, false, "graph_index._CAPI_DGLGraphOutEdges_2[b200]");
+}
+
+// ---- _CAPI_DGLGraphEdges(handle, order) -> {src, dst, eid} ------------------------------------------
+int pf_edges(RefValue* a, int* c, int n, void* ret, void*) {
+  const char* who = "graph_index._CAPI_DGLGraphEdges[b200]";
+  if (n != 2 || c[1] != kRefStr) { set_error("expects (handle, order)"); return fail(who); }
+  const std::string order = a[1].v_str ? a[1].v_str : "";
+  DevIndex* ix = get_index(as_ptr(a[0], c[0]));
+  if (ix == nullptr) return fail(who);
+  ArrayList* res = new ArrayList();
+  if (order == "srcdst") {
+    // sorted by (src, dst); ties (parallel edges) in ascending edge id - the reference's std::sort leaves
+    // them unspecified (graph.cc:374-389)
+    {
+      std::lock_guard<std::mutex> lock(g_mu);
+      if (!ix->has_sorted) {
+        if (build_csr(ix->src.as<int64_t>(), ix->dst.as<int64_t>(), ix->n, ix->e, 1, &ix->by_src_dst) != 0) {
+          delete res;
+          return fail(who);
+        }
+        ix->has_sorted = true;
+      }
+    }
+    DevMem wide;
+    if (wide.alloc((size_t)ix->e * 8) != 0) { delete res; set_error("cudaMalloc failed"); return fail(who); }
+    RefDLTensor *src = nullptr, *dst = nullptr, *eid = nullptr;
+    if (dglb200_csr_row_ids(ix->n, ix->e, ix->by_src_dst.ptr.as<int64_t>(), wide.as<int64_t>(), nullptr) == 0)
+      src = from_device(wide.as<int64_t>(), ix->e);
+    if (dglb200_widen_i32_to_i64(ix->e, ix->by_src_dst.idx.as<int32_t>(), wide.as<int64_t>(), nullptr) == 0)
+      dst = from_device(wide.as<int64_t>(), ix->e);
+    if (dglb200_widen_i32_to_i64(ix->e, ix->by_src_dst.eid.as<int32_t>(), wide.as<int64_t>(), nullptr) == 0)
+      eid = from_device(wide.as<int64_t>(), ix->e);
+    res->arr = {src, dst, eid};
+  } else {
+    res->arr = {from_device(ix->src.as<int64_t>(), ix->e), from_device(ix->dst.as<int64_t>(), ix->e), iota(ix->e)};
+  }
+  if (return_list(res, ret) != 0) return fail(who);
+  return 0;
+}
+
+// ---- _CAPI_DGLGraphInDegrees / OutDegrees (handle, vids) -> degrees ---------------------------------
+int degrees_of_vids(RefValue* a, int* c, int n, void* ret, bool in_deg, const char* who) {
+  if (n != 2) { set_error("expects (handle, vids)"); return fail(who); }
+  const RefDLTensor* vids = static_cast<const RefDLTensor*>(a[1].v_handle);
+  if (!(c[1] == kRefArrayHandle || c[1] == kRefNDArrayContainer) || !valid_ids(vids)) {
+    set_error("Invalid vertex id array.");
+    return fail(who);
+  }
+  DevIndex* ix = get_index(as_ptr(a[0], c[0]));
+  if (ix == nullptr) return fail(who);
+  const int64_t k = vids->shape[0];
+  DevMem d_v, d_deg, d_bad;
+  if (d_v.alloc((size_t)k * 8) || d_deg.alloc((size_t)k * 8) || d_bad.alloc(8)) { set_error("cudaMalloc failed"); return fail(who); }
+  cudaMemset(d_bad.p, 0, 8);
+  if (k > 0) cudaMemcpy(d_v.p, (char*)vids->data + vids->byte_offset, (size_t)k * 8, cudaMemcpyHostToDevice);
+  const DevCsr& csr = in_deg ? ix->in : ix->out;
+  if (dglb200_degrees_of(k, d_v.as<int64_t>(), ix->n, csr.ptr.as<int64_t>(), d_deg.as<int64_t>(), d_bad.as<int32_t>(), nullptr) != 0)
+    return fail(who);
+  RefDLTensor* out = from_device(d_deg.as<int64_t>(), k);
+  int32_t bad = 0;
+  cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost);
+  if (out == nullptr || bad != 0) {
+    if (out) g_dgl.ArrayFree(out);
+    if (bad) set_error("Invalid vertex: an id is outside [0, %lld)", (long long)ix->n);   // graph.cc:421
+    return fail(who);
+  }
+  RefValue v;
+  v.v_handle = out;
+  int code = kRefNDArrayContainer;
+  const int rc = g_dgl.CFuncSetReturn(ret, &v, &code, 1);
+  g_dgl.ArrayFree(out);             // RetValue took its own reference
+  return rc;
+}
+int pf_in_degrees(RefValue* a, int* c, int n, void* ret, void*) {
+  return degrees_of_vids(a, c, n, ret, true, "graph_index._CAPI_DGLGraphInDegrees[b200]");
+}
+int pf_out_degrees(RefValue* a, int* c, int n, void* ret, void*) {
+  return degrees_of_vids(a, c, n, ret, false, "graph_index._CAPI_DGLGraphOutDegrees[b200]");
+}
+
+// ---- mutators: drop the cached index, then the reference's original -----------------------------------
+int pf_forward_mutator(RefValue* a, int* c, int n, void* ret, void* original) {
+  if (n >= 1) drop_index(as_ptr(a[0], c[0]));
+  RefValue r;
+  int rcode = kRefNull;
+  if (g_dgl.FuncCall(original, a, c, n, &r, &rcode) != 0) return -1;     // libdgl's message stands
+  if (rcode != kRefNull) return g_dgl.CFuncSetReturn(ret, &r, &rcode, 1);
+  return 0;
+}
+
+int wrap_mutator(const char* name) {
+  void* orig = nullptr;
+  if (get_global(name, &orig) != 0) return -1;
+  // NOTE: `orig` is a global handle owned by the registry entry; overriding the name replaces the
+  // registry's PackedFunc object in place (registry.cc:47-60 set_body), so the wrapper must hold its
+  // OWN copy of the original: fetch the original through a private alias registered first.
+  const std::string alias = std::string("b200.orig.") + name;
+  if (g_dgl.FuncRegisterGlobal(alias.c_str(), orig, 1) != 0) { set_error("cannot alias %s", name); return -1; }
+  void* kept = nullptr;
+  if (get_global(alias.c_str(), &kept) != 0) return -1;
+  void* h = nullptr;
+  if (g_dgl.FuncCreateFromCFunc(pf_forward_mutator, kept, nullptr, &h) != 0) return -1;
+  const int rc = g_dgl.FuncRegisterGlobal(name, h, 1);
+  g_dgl.FuncFree(h);
+  return rc;
+}
+
+int keep_original(const char* name, void** out) {
+  void* orig = nullptr;
+  if (get_global(name, &orig) != 0) return -1;
+  const std::string alias = std::string("b200.orig.") + name;
+  if (g_dgl.FuncRegisterGlobal(alias.c_str(), orig, 1) != 0) { set_error("cannot alias %s", name); return -1; }
+  return get_global(alias.c_str(), out);
+}
+
+}  // namespace
+
+int register_graph_overrides() {
+  static bool done = false;
+  if (done) return 0;
+  // originals this file keeps calling (copies under private aliases: the overrides below replace the names)
+  if (keep_original("graph_index._CAPI_DGLGraphEdges", &g_orig.edges) != 0) return -1;
+  if (keep_original("graph_index._CAPI_DGLGraphNumVertices", &g_orig.num_vertices) != 0) return -1;
+  if (keep_original("graph_index._CAPI_DGLGraphNumEdges", &g_orig.num_edges) != 0) return -1;
+  int n = 0;
+  for (const char* m : {"graph_index._CAPI_DGLGraphAddVertices", "graph_index._CAPI_DGLGraphAddEdge",
+                        "graph_index._CAPI_DGLGraphAddEdges", "graph_index._CAPI_DGLGraphClear",
+                        "graph_index._CAPI_DGLGraphFree"}) {
+    if (wrap_mutator(m) != 0) return -1;
+    ++n;
+  }
+  struct { const char* name; PackedCFunc fn; } table[] = {
+      {"graph_index._CAPI_DGLGraphGetAdj", pf_get_adj},
+      {"graph_index._CAPI_DGLGraphInEdges_2", pf_in_edges},
+      {"graph_index._CAPI_DGLGraphOutEdges_2", pf_out_edges},
+      {"graph_index._CAPI_DGLGraphEdges", pf_edges},
+      {"graph_index._CAPI_DGLGraphInDegrees", pf_in_degrees},
+      {"graph_index._CAPI_DGLGraphOutDegrees", pf_out_degrees},
+  };
+  for (auto& t : table) {
+    if (register_one(t.name, t.fn, 1) != 0) return -1;
+    ++n;
+  }
+  done = true;
+  return n;
+}
+
+}  // namespace packed
+}  // namespace dglb200

@@ -256,10 +256,13 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
         }
         if (ok) {
           if constexpr (H16) {
-            if (gid >= h_first) {      // halo row in wire precision: 8 bytes -> 4 floats (exact widening)
+            // halo row in wire precision: 8 bytes land RAW in the first two stage registers and are
+            // widened when the stage is consumed - nothing here may wait on a load, or the U loads of
+            // the step would issue one after another (measured: 13.7 ms instead of 9.8 ms at C5 x 2)
+            if (gid >= h_first) {
               const uint2 hv = __ldg(reinterpret_cast<const uint2*>(row_ptr(hb[t], gid - h_first, h_row_bytes)));
-              st.xv[k][t][0] = bf16_lo(hv.x); st.xv[k][t][1] = bf16_hi(hv.x);
-              st.xv[k][t][2] = bf16_lo(hv.y); st.xv[k][t][3] = bf16_hi(hv.y);
+              st.xv[k][t][0] = __uint_as_float(hv.x);
+              st.xv[k][t][1] = __uint_as_float(hv.y);
             } else {
               Chunk<T, VEC>::load(reinterpret_cast<const T*>(row_ptr(xb[t], gid, row_bytes)), st.xv[k][t]);
             }
@@ -296,6 +299,19 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
     for (int k = 0; k < U; ++k) {
 #pragma unroll
       for (int t = 0; t < TILES; ++t) {
+        if constexpr (H16) {
+          // exact widening of a halo row's 4 bf16 values (own rows pass through)
+          const bool is_h = (uint32_t)st.s[k] >= h_first && st.s[k] >= 0;
+          const uint32_t b0 = __float_as_uint(st.xv[k][t][0]), b1 = __float_as_uint(st.xv[k][t][1]);
+          const float2 lo = __fadd2_rn(make_float2(acc[t][0], acc[t][1]),
+                                       is_h ? make_float2(bf16_lo(b0), bf16_hi(b0))
+                                            : make_float2(st.xv[k][t][0], st.xv[k][t][1]));
+          const float2 hi = __fadd2_rn(make_float2(acc[t][2], acc[t][3]),
+                                       is_h ? make_float2(bf16_lo(b1), bf16_hi(b1))
+                                            : make_float2(st.xv[k][t][2], st.xv[k][t][3]));
+          acc[t][0] = lo.x; acc[t][1] = lo.y; acc[t][2] = hi.x; acc[t][3] = hi.y;
+          continue;
+        }
         if constexpr (kPackedAdd) {
           // copy_src -> sum: the hot loop is issue-bound (SHFL + address + LDG.128 + 4 FADD per
           // edge-lane); sm_100's packed add.f32x2 halves the FADD count.  Same rounding (rn), same

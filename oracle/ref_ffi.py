@@ -168,6 +168,33 @@ class RefGraph(object):
         return get_global("graph_index._CAPI_DGLGraphInDegrees")(self.handle, np.asarray(v, np.int64))
 
 
+def _edge_array(name, handle, arg):
+    rst = get_global(name)(handle, arg)
+    return rst(0), rst(1), rst(2)
+
+
+def graph_in_edges(g, v):
+    """Graph::InEdges(IdArray) -> (src, dst, eid), src/graph/graph.cc:294-319."""
+    return _edge_array("graph_index._CAPI_DGLGraphInEdges_2", g.handle, np.asarray(v, np.int64))
+
+
+def graph_out_edges(g, v):
+    return _edge_array("graph_index._CAPI_DGLGraphOutEdges_2", g.handle, np.asarray(v, np.int64))
+
+
+def graph_edges(g, order=""):
+    """Graph::Edges(order) -> (src, dst, eid), src/graph/graph.cc:368-409 ("srcdst" sorts)."""
+    return _edge_array("graph_index._CAPI_DGLGraphEdges", g.handle, order)
+
+
+def graph_out_degrees(g, v):
+    return get_global("graph_index._CAPI_DGLGraphOutDegrees")(g.handle, np.asarray(v, np.int64))
+
+
+def graph_add_edges(g, src, dst):
+    get_global("graph_index._CAPI_DGLGraphAddEdges")(g.handle, np.asarray(src, np.int64), np.asarray(dst, np.int64))
+
+
 def degree_bucketing(msg_ids, vids, recv_ids):
     """sched::DegreeBucketing in the reference's own (unordered_map) order: 5 int64 arrays."""
     b = get_global("runtime.degree_bucketing._CAPI_DGLDegreeBucketing")(

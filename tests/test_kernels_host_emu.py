@@ -46,8 +46,6 @@ def emu_lib():
     from tests.native.cuda_emu import build
     lib = ctypes.CDLL(build.build())
     for name, (res, args) in _lib.SIGNATURES.items():
-        if name == "dglb200_register_packed_funcs":       # packed.cu is not part of the emulation build
-            continue
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
