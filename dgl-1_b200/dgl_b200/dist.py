@@ -46,10 +46,12 @@ PUSH_CTAS_PIPELINED = 128   # "push" mode: grid of a push that runs beside the S
 PUSH_CTAS = int(os.environ.get("DGL_B200_PUSH_CTAS", "0"))   # "signal" mode: grid bound of a push (0 = 2 CTAs per SM)
 TIMING = bool(int(os.environ.get("DGL_B200_TIMING", "0")))   # record events around the halo transfers
 COMM_PRIORITY = -1      # side stream of the exchange: higher priority than the compute stream
-# bf16 wire: the SpMM gathers the halo rows straight from the bf16 staging buffer (dglb200_spmm_csr_ext,
-# mixed-precision operand) instead of widening them into the fp32 buffer first: no extra pass over the
-# halo and half the gather bytes for 7/8 of the edges at 8 ranks
-MIXED_HALO = bool(int(os.environ.get("DGL_B200_MIXED_HALO", "1")))
+# bf16 wire: the SpMM can gather the halo rows straight from the bf16 staging buffer (dglb200_spmm_csr_ext,
+# mixed-precision operand) instead of widening them into the fp32 buffer first.  OFF by default - measured
+# on a real C5 rank block (8-way, 6.0M rows + 4.0M halo rows, 19.2M edges): 4.0 ms against 2.5 ms for the
+# fp32 gather (the widening adds ~10 instructions per gathered 16 bytes to a loop that already runs at 59 %
+# issue utilisation, and at 64 registers it spills); the separate widening pass costs 0.6 ms per op
+MIXED_HALO = bool(int(os.environ.get("DGL_B200_MIXED_HALO", "0")))
 # all-gather partition: sum the column block of the rank's OWN source rows first (needs no exchange, so it
 # runs while every slab is still in flight), then add the remote column block slab by slab
 SPLIT_LOCAL = bool(int(os.environ.get("DGL_B200_SPLIT_LOCAL", "1")))
