@@ -1,6 +1,7 @@
 // C-ABI entry points of the SpMM path: plan (long-row split table), forward, backward-x,
 // and the slice fix-up kernel.  See include/dgl_b200.h for the contracts and
 // spmm_kernel.cuh for the kernel design.
+#include <mutex>
 #include <string>
 
 #include "scan.cuh"
@@ -233,6 +234,33 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
   return 0;
 }
 
+// ---- scratch of the allocation-free entry point (dglb200_spmm_csr_static_scratch) -----------------------
+// The long-row slices of an SpMM write fp32 partials that the fix-up kernel combines: normally the caller
+// hands that scratch in (plan->partial).  Here it is a file-scope device array, so the call allocates
+// nothing.  Every GPU that loads the library holds these DGLB200_STATIC_SCRATCH_BYTES until exit.
+static __device__ __align__(256) float g_static_partial[DGLB200_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+constexpr int kMaxScratchDevices = 64;
+
+// Device address of g_static_partial on the CURRENT device (in host code the array's name is only a
+// host-side stand-in, not a device address): resolved once per device with that device current.
+static int static_partial_address(float** out) {
+  static std::mutex mu;
+  static float* addr[kMaxScratchDevices] = {nullptr};
+  int dev = -1;
+  DGLB200_CUDA(cudaGetDevice(&dev));
+  DGLB200_REQUIRE(dev >= 0 && dev < kMaxScratchDevices, "static scratch: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (addr[dev] == nullptr) {
+    void* p = nullptr;
+    DGLB200_CUDA(cudaGetSymbolAddress(&p, g_static_partial));
+    DGLB200_REQUIRE(p != nullptr, "static scratch: cudaGetSymbolAddress returned NULL");
+    addr[dev] = static_cast<float*>(p);
+  }
+  *out = addr[dev];
+  return 0;
+}
+
 }  // namespace dglb200
 
 using namespace dglb200;
@@ -416,6 +444,34 @@ int dglb200_spmm_csr_backward_x(int64_t n_rows, int64_t dy_rows, int64_t nnz, co
   }
   int msg = (arg != nullptr) ? (int)kMsgMasked : (w != nullptr ? (int)DGLB200_MSG_SRC_MUL_EDGE : (int)DGLB200_MSG_COPY_SRC);
   return run_spmm(a, msg, DGLB200_RED_SUM, dtype, plan, dy_rows, nnz, static_cast<cudaStream_t>(stream));
+}
+
+int dglb200_spmm_csr_static_scratch(int64_t n_rows, int64_t x_rows, int64_t nnz, const int64_t* indptr,
+                                    const int32_t* indices, const int32_t* eids, int msg_op, int reduce_op,
+                                    int dtype, const void* x, int64_t feat, const void* w, int64_t w_width,
+                                    void* y, const dglb200_spmm_plan_t* plan, void* stream) {
+  clear_error();
+  // no argmax output here: MAX with arg would need a second (int32) scratch of the same size
+  if (plan == nullptr || plan->n_long_rows <= 0)     // no long rows: no scratch is used at all
+    return dglb200_spmm_csr_strided(n_rows, x_rows, nnz, indptr, indices, eids, msg_op, reduce_op, dtype, x, feat,
+                                    feat, w, w_width, y, feat, nullptr, nullptr, stream);
+  DGLB200_REQUIRE(feat >= 1 && plan->n_chunks >= 0, "spmm_csr_static_scratch: bad sizes");
+  const unsigned long long need = (unsigned long long)plan->n_chunks * (unsigned long long)feat * sizeof(float);
+  DGLB200_REQUIRE(need <= (unsigned long long)DGLB200_STATIC_SCRATCH_BYTES,
+                  "spmm_csr_static_scratch: %lld long-row slices x %lld features need %llu bytes of scratch, the "
+                  "static scratch holds %llu (DGLB200_STATIC_SCRATCH_BYTES); use dglb200_spmm_csr with a "
+                  "caller-provided plan->partial", (long long)plan->n_chunks, (long long)feat, need,
+                  (unsigned long long)DGLB200_STATIC_SCRATCH_BYTES);
+  float* scratch = nullptr;
+  if (static_partial_address(&scratch) != 0) return -1;
+  dglb200_spmm_plan_t local = *plan;                 // the caller's tables, our scratch
+  local.partial = scratch;
+  local.partial_arg = nullptr;
+  local.partial_bytes = DGLB200_STATIC_SCRATCH_BYTES;
+  // every slice writes all of its `feat` partials before the fix-up kernel (same stream) reads them: nothing
+  // in the scratch has to start at zero, so the previous call's contents need no clearing
+  return dglb200_spmm_csr_strided(n_rows, x_rows, nnz, indptr, indices, eids, msg_op, reduce_op, dtype, x, feat,
+                                  feat, w, w_width, y, feat, nullptr, &local, stream);
 }
 
 }  // extern "C"

@@ -68,6 +68,9 @@ SIGNATURES = {
     "dglb200_spmm_csr_ext": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_int, c_int,
                                      c_vp, c_i64, c_i64, c_vp, c_i64, c_vp, c_i64, c_vp,
                                      ctypes.POINTER(SpmmPlanStruct), ctypes.POINTER(SpmmExtStruct), c_vp]),
+    "dglb200_spmm_csr_static_scratch": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_int, c_int,
+                                                c_vp, c_i64, c_vp, c_i64, c_vp,
+                                                ctypes.POINTER(SpmmPlanStruct), c_vp]),
     "dglb200_edge_data_to_slots": (c_int, [c_i64, c_vp, c_i64, c_i64, c_vp, c_vp, c_vp, c_vp]),
     "dglb200_spmm_csr_backward_x": (c_int, [c_i64, c_i64, c_i64, c_vp, c_vp, c_vp, c_int, c_vp, c_i64,
                                             c_vp, c_i64, c_vp, c_vp,

@@ -227,6 +227,30 @@ int dglb200_spmm_csr_ext(int64_t n_rows, int64_t x_rows, int64_t nnz,
                          const dglb200_spmm_plan_t* plan, const dglb200_spmm_ext_t* ext, void* stream);
 
 /*
+ * Allocation-free variant of dglb200_spmm_csr.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  Same semantics as dglb200_spmm_csr with arg == NULL, but
+ * the fp32 scratch of the long-row slices (plan->partial) is NOT taken from the caller: it lives in a
+ * file-scope `static __device__` array of DGLB200_STATIC_SCRATCH_BYTES inside the library (every GPU that
+ * loads the library holds it until exit).  plan->long_rows / chunk_ptr / chunk / n_long_rows / n_chunks are
+ * the caller's tables as made by dglb200_spmm_plan; plan->partial, partial_arg and partial_bytes are ignored.
+ * The call performs no cudaMalloc / cudaFree and calls no allocating library routine; it does not sync.
+ *   - n_chunks * feat * 4 bytes must be <= DGLB200_STATIC_SCRATCH_BYTES, else -1 with a message that
+ *     states both sizes (use dglb200_spmm_csr with your own plan->partial then).
+ *   - ALL calls on a GPU share the one array, which keeps the previous call's contents (nothing has to start
+ *     at zero: every slice is fully written before it is read).  Calls that OVERLAP on the GPU (different
+ *     streams, or graph branches that may run concurrently) race on it; calls on one stream are safe.
+ *   - MAX with an argmax output is not offered (it would need a second, int32 scratch).
+ */
+#define DGLB200_STATIC_SCRATCH_BYTES (4u << 20)
+int dglb200_spmm_csr_static_scratch(int64_t n_rows, int64_t x_rows, int64_t nnz,
+                                    const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                                    int msg_op, int reduce_op, int dtype,
+                                    const void* x, int64_t feat,
+                                    const void* w, int64_t w_width,
+                                    void* y, const dglb200_spmm_plan_t* plan, void* stream);
+
+/*
  * Narrow edge data (a scalar or one weight per head) in edge-id order -> CSR slot order:
  * out[p, :] = w[eids[p], :], p in [0, nnz), rows of row_bytes bytes (even, <= 4096).
  * The SpMM kernels index edge data with e(p) = eids[p], or p itself when eids == NULL; on a large

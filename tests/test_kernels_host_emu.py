@@ -29,6 +29,7 @@ from tests import test_gpu_spmm as t_spmm
 from tests import test_sendrecv_gpu as t_msg
 from tests import test_uopv_edge_ops_gpu as t_edge
 from tests import test_wire_convert_gpu as t_wire
+from tests import test_zz_no_alloc as t_noalloc
 
 pytestmark = pytest.mark.timeout(900)     # a lost rendezvous must fail the test, not hang the tier
 
@@ -82,7 +83,7 @@ def emu(monkeypatch, emu_lib):
         monkeypatch.setattr(torch, name, wrapped)
     real_gen = torch.Generator
     monkeypatch.setattr(torch, "Generator", lambda device="cpu": real_gen(device=_cpu_device(device)))
-    for mod in (t_msg, t_edge):
+    for mod in (t_msg, t_edge, t_noalloc):
         monkeypatch.setattr(mod, "device", lambda: torch.device("cpu"))
     launches0 = emu_lib.dglb200_launch_count()
     yield emu_lib
@@ -237,3 +238,10 @@ def test_edge_ops_on_emulated_kernels(emu):
         t_edge.test_sddmm_forward_and_gradients(op, (4, 8))
     t_edge.test_edge_softmax_forward_and_gradient()
     t_edge.test_gat_attention_matches_udf_formulation_with_gradients()
+
+
+def test_static_scratch_entry_point_on_emulated_kernels(emu):
+    """dglb200_spmm_csr_static_scratch (the operators' allocation-free variant) on the host emulation: the
+    `static __device__` scratch is then a host array and cudaGetSymbolAddress its address."""
+    t_noalloc.test_static_scratch_spmm_equals_existing_entry_point_twice_in_a_row()
+    t_noalloc.test_static_scratch_rejects_sizes_beyond_the_maximum_and_handles_no_long_rows()
