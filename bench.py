@@ -190,15 +190,20 @@ class GCNModel(object):
         self.dropout = dropout
         self.opt = torch.optim.Adam(self.params, lr=1e-2, weight_decay=5e-4)
 
-    def forward(self, x, norm, aggregate):
+    def forward(self, x, norm, aggregate, fused_layer=None):
         drop = torch.nn.functional.dropout
+        if fused_layer is not None:
+            # dgl_b200.fused: destination norm, bias and ReLU in the SpMM's store epilogue, source norm in the
+            # transposed SpMM's epilogue on the way back (examples/pytorch/gcn/gcn_spmv.py:45-62 in 2 kernels)
+            h = fused_layer(torch.mm(drop(x, self.dropout), self.w1), self.b1, True)
+            return fused_layer(torch.mm(drop(h, self.dropout), self.w2), self.b2, False)
         h = torch.mm(drop(x, self.dropout), self.w1) * norm
         h = torch.relu(aggregate(h, "h") * norm + self.b1)
         h = torch.mm(drop(h, self.dropout), self.w2) * norm
         return aggregate(h, "c") * norm + self.b2
 
-    def epoch(self, x, labels, norm, aggregate, n_total, allreduce=None):
-        logits = self.forward(x, norm, aggregate)
+    def epoch(self, x, labels, norm, aggregate, n_total, allreduce=None, fused_layer=None):
+        logits = self.forward(x, norm, aggregate, fused_layer)
         loss = torch.nn.functional.cross_entropy(logits, labels, reduction="sum") / n_total
         self.opt.zero_grad(set_to_none=True)
         loss.backward()
@@ -913,6 +918,7 @@ def run_b200(args):
         xg = torch.randn(rows, feat_in, device=dev, generator=gen)
         labels = torch.randint(0, classes, (rows,), device=dev, generator=gen)
         model = GCNModel(feat_in, hidden, classes, dev)
+        fused_layer = None
         if world == 1:
             g.set_csr(loc_in, loc_out)
 
@@ -921,6 +927,10 @@ def run_b200(args):
                 g.update_all(fn.copy_src("h", "m"), fn.sum("m", "h"))
                 return g.ndata.pop("h")
             allreduce = None
+            if not args.no_fused:
+                from dgl_b200 import fused as b200fused
+                adj_, norm1 = g.adjacency(), norm.reshape(-1).contiguous()
+                fused_layer = lambda hw, b, relu: b200fused.gcn_aggregate(adj_, hw, norm1, bias=b, relu=relu)  # noqa: E731
         else:
             if args.transport == "peer":
                 part.enable_peer_transport(hidden, like, keys=("xh", "dyh"))
@@ -928,14 +938,14 @@ def run_b200(args):
             agg = lambda h, tag: b200dist.aggregate(part, h, tag)  # noqa: E731
             allreduce = lambda t: dist.all_reduce(t)  # noqa: E731
         for _ in range(3):
-            model.epoch(xg, labels, norm, agg, n, allreduce)
+            model.epoch(xg, labels, norm, agg, n, allreduce, fused_layer)
         barrier()
         k = max(3, min(args.steps, 10))
         l1 = _lib.launch_count()
         a, b = ev(), ev()
         a.record()
         for _ in range(k):
-            loss = model.epoch(xg, labels, norm, agg, n, allreduce)
+            loss = model.epoch(xg, labels, norm, agg, n, allreduce, fused_layer)
         b.record()
         barrier()
         ms = a.elapsed_time(b) / k
@@ -945,7 +955,8 @@ def run_b200(args):
             ms = float(t.item())
         gcn = {"ms": ms, "edges": int(e), "edges_per_s": e / (ms * 1e-3), "epochs": k,
                "model": "GCN %d-%d-%d, dropout 0.5, Adam" % (feat_in, hidden, classes),
-               "loss": float(loss.item()), "engine_launches_per_epoch": (_lib.launch_count() - l1) / k}
+               "loss": float(loss.item()), "engine_launches_per_epoch": (_lib.launch_count() - l1) / k,
+               "layer": "fused (norm / bias / relu in the SpMM epilogue)" if fused_layer is not None else "unfused"}
         del xg, labels, model
         torch.cuda.empty_cache()
 
@@ -1009,6 +1020,7 @@ def main():
     ap.add_argument("--no-check", action="store_true",
                     help="skip the self-check (N=1: slab path vs column blocks bit for bit + sampled rows vs the "
                          "oracle; N>1: the exchange against the all-gather path)")
+    ap.add_argument("--no-fused", action="store_true", help="GCN epoch with the unfused layer (4 eager passes around the SpMM)")
     ap.add_argument("--no-c5", action="store_true", help="skip the C5 record measured beside the C2 headline")
     ap.add_argument("--ref-budget", type=float, default=150.0,
                     help="--impl reference: seconds of timed CPU passes over the full configuration")

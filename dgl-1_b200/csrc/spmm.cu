@@ -43,7 +43,8 @@ __global__ void plan_emit(const int32_t* is_long, const int32_t* long_pos, const
 template <typename T, int RED>
 __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, int n_long,
                            const float* partial, const int32_t* partial_arg, int64_t feat, int64_t y_ld,
-                           T* y, int32_t* arg, int accumulate) {
+                           T* y, int32_t* arg, int accumulate, const float* row_scale,
+                           const float* bias, int relu) {
   const int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   const int lr = blockIdx.y;
   if (f >= feat || lr >= n_long) return;
@@ -65,6 +66,10 @@ __global__ void spmm_fixup(const int32_t* long_rows, const int64_t* chunk_ptr, i
     else acc += __bfloat162float(reinterpret_cast<__nv_bfloat16*>(y)[row * y_ld + f]);
   }
   if (RED == DGLB200_RED_MAX && arg) arg[row * feat + f] = best;
+  if (RED == DGLB200_RED_SUM && (row_scale != nullptr || bias != nullptr || relu)) {
+    acc = acc * (row_scale ? row_scale[row] : 1.f) + (bias ? bias[f] : 0.f);
+    if (relu) acc = fmaxf(acc, 0.f);
+  }
   if (sizeof(T) == 4) reinterpret_cast<float*>(y)[row * y_ld + f] = acc;
   else reinterpret_cast<__nv_bfloat16*>(y)[row * y_ld + f] = __float2bfloat16_rn(acc);
 }
@@ -184,6 +189,8 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
   bool vec = ragged ? (ragged_ok && x_ok && a.x_ld >= a.feat + 1) : (x_ok && a.y_vec);
   if (a.w != nullptr && (a.w_mode == kWFull || msg == DGLB200_MSG_COPY_EDGE)) vec = vec && aligned16(a.w);
   DGLB200_REQUIRE(!(a.accumulate && red != DGLB200_RED_SUM), "spmm: accumulate needs the SUM reducer");
+  DGLB200_REQUIRE(!((a.row_scale || a.bias || a.relu) && red != DGLB200_RED_SUM),
+                  "spmm: the row_scale / bias / relu epilogue needs the SUM reducer");
   if (a.x_halo != nullptr) {
     DGLB200_REQUIRE(dtype == DGLB200_F32 && msg == DGLB200_MSG_COPY_SRC && red == DGLB200_RED_SUM,
                     "spmm: a bf16 halo operand needs fp32 copy_src -> sum");
@@ -220,7 +227,7 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
 #define FIX(T, R)                                                                          \
   spmm_fixup<T, R><<<grid, 128, 0, stream>>>(a.long_rows + base, a.chunk_ptr + base, n,    \
                                              a.partial, a.partial_arg, a.feat, a.y_ld,     \
-                                             static_cast<T*>(a.y), a.arg, a.accumulate)
+                                             static_cast<T*>(a.y), a.arg, a.accumulate, a.row_scale, a.bias, a.relu)
       if (dtype == DGLB200_F32) {
         if (red == DGLB200_RED_SUM) FIX(float, DGLB200_RED_SUM); else FIX(float, DGLB200_RED_MAX);
       } else {
@@ -393,6 +400,9 @@ int dglb200_spmm_csr_ext(int64_t n_rows, int64_t x_rows, int64_t nnz, const int6
     a.accumulate = ext->accumulate != 0;
     a.x_halo = ext->x_halo;
     a.halo_first = ext->halo_first;
+    a.row_scale = ext->row_scale;
+    a.bias = ext->bias;
+    a.relu = ext->relu != 0;
   }
   return run_spmm(a, msg_op, reduce_op, dtype, plan, x_rows, nnz, static_cast<cudaStream_t>(stream));
 }

@@ -62,6 +62,9 @@ struct SpmmArgs {
   int64_t nnz;
   int rows_per_group;      // consecutive row steps a group walks (launch_one; >= 1)
   int accumulate;          // SUM: y += result (the caller sums several column blocks of the operand)
+  const float* row_scale;  // SUM epilogue (fused GCN layer): y = act(row_scale[r] * sum + bias[f]); each nullable
+  const float* bias;
+  int relu;
   const void* x_halo;      // H16 kernels: bf16 rows of the column ids >= halo_first (multi-GPU halo kept
   int64_t halo_first;      //   in wire precision: no widening pass, half the gather bytes), dense in feat
 };
@@ -459,6 +462,16 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
               Chunk<T, 1>::load(y + out_row * a.y_ld + foff[t] + v, one);
               acc[t][v] += one[0];
             }
+        }
+      }
+      if (!kMax && (a.row_scale != nullptr || a.bias != nullptr || a.relu)) {
+        // fused layer epilogue (examples/pytorch/gcn/gcn_spmv.py:55-60: h * norm, + bias, activation)
+        const float rs = a.row_scale ? a.row_scale[out_row] : 1.f;
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) {
+          float r = acc[t][v] * rs;
+          if (a.bias != nullptr && v < nv) r += a.bias[foff[t] + v];
+          acc[t][v] = a.relu ? fmaxf(r, 0.f) : r;
         }
       }
       if (VEC == 1 || (nv == VEC && a.y_vec)) {

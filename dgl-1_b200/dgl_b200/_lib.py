@@ -35,7 +35,8 @@ class SpmmPlanStruct(ctypes.Structure):
 
 class SpmmExtStruct(ctypes.Structure):
     """Mirror of dglb200_spmm_ext_t (include/dgl_b200.h)."""
-    _fields_ = [("accumulate", c_i32), ("reserved", c_i32), ("x_halo", c_vp), ("halo_first", c_i64)]
+    _fields_ = [("accumulate", c_i32), ("relu", c_i32), ("x_halo", c_vp), ("halo_first", c_i64),
+                ("row_scale", c_vp), ("bias", c_vp)]
 
 
 # name -> (restype, argtypes); must list every symbol of include/dgl_b200.h

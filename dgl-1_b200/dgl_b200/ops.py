@@ -268,12 +268,13 @@ def _slot_ordered_weights(csr, w, w_width, feat, need_eids):
 
 
 def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chunk=DEFAULT_CHUNK,
-         out=None, accumulate=False, x_halo=None, halo_first=0):
+         out=None, accumulate=False, x_halo=None, halo_first=0, row_scale=None, bias=None, relu=False):
     """y[r] = reduce over row r of msg(x[indices], w[eids]); 2-D (rows, feat) tensors.
 
     Returns (y, arg) where arg is int32 (rows, feat) for RED_MAX with want_arg, else None.
     accumulate: y (= out) += result (SUM).  x_halo / halo_first: column ids >= halo_first are rows of the
     bfloat16 tensor x_halo (fp32 copy_src -> sum only; dglb200_spmm_csr_ext).
+    row_scale (rows,) / bias (feat,) fp32 / relu: the SUM epilogue y = relu(row_scale[r] * sum + bias[f]).
     """
     lib = _lib.get_lib()
     ref = x if x is not None else w
@@ -320,13 +321,19 @@ def spmm(csr, msg_op, reduce_op, x=None, w=None, w_width=1, want_arg=False, chun
     if msg_op == MSG_SRC_MUL_EDGE:
         w, eids = _slot_ordered_weights(csr, w, w_width, feat, need_eids=arg is not None)
     ext_ref = None
-    if accumulate or x_halo is not None:
+    if accumulate or x_halo is not None or row_scale is not None or bias is not None or relu:
+        for t_, n_, name in ((row_scale, csr.n_rows, "row_scale"), (bias, feat, "bias")):
+            if t_ is not None and (t_.dtype != torch.float32 or not t_.is_contiguous() or t_.numel() != n_):
+                raise DGLError("spmm: %s must be a contiguous float32 tensor of %d elements" % (name, n_))
         if accumulate and out is None:
             raise DGLError("spmm: accumulate needs `out`")
         ext = _lib.SpmmExtStruct()
         ext.accumulate = 1 if accumulate else 0
         ext.x_halo = x_halo.data_ptr() if x_halo is not None else None
         ext.halo_first = int(halo_first)
+        ext.row_scale = row_scale.data_ptr() if row_scale is not None else None
+        ext.bias = bias.data_ptr() if bias is not None else None
+        ext.relu = 1 if relu else 0
         ext_ref = ctypes.byref(ext)
     with torch.cuda.device(ref.device):
         _lib.check_call(lib.dglb200_spmm_csr_ext(

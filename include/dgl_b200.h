@@ -210,13 +210,18 @@ int dglb200_spmm_csr_strided(int64_t n_rows, int64_t x_rows, int64_t nnz,
  *                    in bfloat16 (row id - halo_first, dense [*, feat], feat a multiple of 8): the halo
  *                    rows stay in the precision they crossed NVLink in (DGL_B200_WIRE=bf16), accumulation
  *                    is fp32; results within the bf16 bar (1e-2), own rows exact.
+ *   row_scale / bias / relu   SUM only: the layer epilogue y = relu(row_scale[r] * sum + bias[f]) applied in
+ *                    the store (each part optional; with accumulate it is applied to the accumulated value,
+ *                    so only the LAST of several accumulating calls may carry it).
  * ext == NULL is dglb200_spmm_csr_strided.
  */
 typedef struct dglb200_spmm_ext_t {
   int32_t accumulate;
-  int32_t reserved;
+  int32_t relu;            /* SUM epilogue: y = max(., 0) last */
   const void* x_halo;
   int64_t halo_first;
+  const float* row_scale;  /* SUM epilogue: y[r, :] = row_scale[r] * sum (nullable) ... */
+  const float* bias;       /* ... + bias[f] (nullable): the fused GCN layer, examples/pytorch/gcn/gcn_spmv.py:55-60 */
 } dglb200_spmm_ext_t;
 int dglb200_spmm_csr_ext(int64_t n_rows, int64_t x_rows, int64_t nnz,
                          const int64_t* indptr, const int32_t* indices, const int32_t* eids,

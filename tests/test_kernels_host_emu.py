@@ -30,6 +30,7 @@ from tests import test_sendrecv_gpu as t_msg
 from tests import test_uopv_edge_ops_gpu as t_edge
 from tests import test_wire_convert_gpu as t_wire
 from tests import test_zz_no_alloc as t_noalloc
+from tests import test_fused_gcn_gpu as t_fused
 
 pytestmark = pytest.mark.timeout(900)     # a lost rendezvous must fail the test, not hang the tier
 
@@ -83,7 +84,7 @@ def emu(monkeypatch, emu_lib):
         monkeypatch.setattr(torch, name, wrapped)
     real_gen = torch.Generator
     monkeypatch.setattr(torch, "Generator", lambda device="cpu": real_gen(device=_cpu_device(device)))
-    for mod in (t_msg, t_edge, t_noalloc):
+    for mod in (t_msg, t_edge, t_noalloc, t_fused):
         monkeypatch.setattr(mod, "device", lambda: torch.device("cpu"))
     launches0 = emu_lib.dglb200_launch_count()
     yield emu_lib
@@ -245,3 +246,8 @@ def test_static_scratch_entry_point_on_emulated_kernels(emu):
     `static __device__` scratch is then a host array and cudaGetSymbolAddress its address."""
     t_noalloc.test_static_scratch_spmm_equals_existing_entry_point_twice_in_a_row()
     t_noalloc.test_static_scratch_rejects_sizes_beyond_the_maximum_and_handles_no_long_rows()
+
+
+def test_fused_gcn_layer_against_reference_example(emu):
+    t_fused.test_fused_layer_matches_reference_example_layer(t_fused.GOLDEN[0])
+    t_fused.test_epilogue_on_long_rows_ragged_width_and_empty_rows()
