@@ -110,6 +110,8 @@ edge_data_to_slots_kernel(int64_t nnz, const int32_t* __restrict__ eids, int64_t
   }
 }
 
+void set_peer_push_tma(int v);   // peer.cu
+
 SpmmTuning& spmm_tuning() {
   static SpmmTuning t;
   return t;
@@ -283,6 +285,7 @@ int dglb200_set_tuning(const char* key, int64_t value) {
   else if (k == "spmm_slab_chunks") t.slab_chunks = (int)value;
   else if (k == "spmm_threads") t.threads = (int)value;
   else if (k == "spmm_rows_per_group") t.rows_per_group = (int)value;
+  else if (k == "peer_push_tma") set_peer_push_tma((int)value);
   else {
     set_error("set_tuning: unknown key '%s'", key);
     return -1;

@@ -80,10 +80,25 @@ def chunk_fractions(chunks):
     return fr
 
 
+# How a push reaches the peer (csrc/peer.cu): 0 = every thread's st.global (a push CTA then moves only ~5 GB/s,
+# the link needs ~300 CTAs and the SpMM sharing the SMs slows down); 1 = threads gather (+ bf16 rounding) into
+# shared memory, ONE thread hands each stage to the TMA (cp.async.bulk shared -> peer global); 2 = TMA both ways
+# (bulk gathers global -> shared behind an mbarrier, bulk stores to the peer; fp32 wire only, else 1).
+# Measured, C5 x 8, 4 chunks, ms/step: fp32 wire 10.79 / 10.44 / 10.39; bf16 wire 9.30 / 9.00 / -
+PUSH_TMA = int(os.environ.get("DGL_B200_PUSH_TMA", "2"))
+
+
+def apply_tuning():
+    """Hand the transport knobs that live in the library to it (dglb200_set_tuning)."""
+    from . import _lib
+    _lib.check_call(_lib.get_lib().dglb200_set_tuning(b"peer_push_tma", int(PUSH_TMA)))
+
+
 def transport_name(exchange):
     """Human-readable name of the peer transport in use (bench.py's `config.parallelism`)."""
     if PULL_MODE == "signal":
-        return "push + flag signals (own kernels, no NCCL on the data path)"
+        return "push (%s) + flag signals (own kernels, no NCCL on the data path)" % (
+            {0: "thread stores", 1: "TMA bulk stores", 2: "TMA bulk gathers + stores"}.get(PUSH_TMA, "?"))
     return PULL_MODE if exchange == "halo" else "block copies between NCCL stream barriers"
 
 
@@ -194,6 +209,7 @@ class PeerSignals(object):
     of the last exchange rank q completed for that slot) and read by this rank only."""
 
     def __init__(self, slots, rank, world, device, group=None):
+        apply_tuning()
         self.rank, self.world, self.slots = rank, world, slots
         self.flags = torch.zeros((slots, world), dtype=torch.int32, device=device)
         self.counter = torch.zeros(max(slots, 1), dtype=torch.int32, device=device)

@@ -77,6 +77,8 @@ def main():
                 (4, None, "signal", "bf16", 0), (4, "0.1,0.35,0.7,1", "signal", "bf16", 0),
                 (8, None, "signal", "bf16", 0),
                 (4, None, "push", "f32", 0)]
+    if os.environ.get("C5_SWEEP_GRID"):       # e.g. '[[4,null,"signal","f32",64],[4,null,"signal-lsu","bf16",0]]'
+        grid = [tuple(g) for g in json.loads(os.environ["C5_SWEEP_GRID"])]
     part, part_key = None, None
     dmod.TIMING = True
     for chunks, fracs, mode, wire, ctas in grid:
@@ -98,6 +100,10 @@ def main():
             plan_s = time.time() - t0
             part_key = (chunks, fracs)
         torch.cuda.empty_cache()
+        # "signal-lsu": every thread stores to the peer; "signal-tma1": thread gather + TMA store; "signal": TMA both ways
+        dmod.PUSH_TMA = 0 if mode.endswith("-lsu") else (1 if mode.endswith("-tma1") else 2)
+        mode = mode.replace("-lsu", "").replace("-tma1", "")
+        dmod.apply_tuning()
         dmod.PULL_MODE, dmod.WIRE, dmod.PUSH_CTAS = mode, wire, ctas
         part.enable_peer_transport(feat, like)
         x_loc, dy_loc = part.local_view("x", feat, like), part.local_view("dy", feat, like)
@@ -156,7 +162,7 @@ def main():
         allt = [torch.empty_like(t) for _ in range(world)]
         dist.all_gather(allt, t)
         if rank == 0:
-            rec = {"world": world, "workload": args.workload, "chunks": chunks, "mode": mode, "wire": wire,
+            rec = {"world": world, "workload": args.workload, "chunks": chunks, "mode": mode + {0: "-lsu", 1: "-tma1", 2: ""}[dmod.PUSH_TMA], "wire": wire,
                    "push_ctas": ctas, "ms_per_step": round(max(float(v[0]) for v in allt), 3),
                    "kernel_ms_per_step_by_rank": [round(float(v[1]), 3) for v in allt],
                    "push_ms_per_op_by_rank": [round(float(v[2]), 3) for v in allt],
