@@ -727,13 +727,20 @@ def c5_n1_reference():
         return None, "unavailable"
 
 
-def c5_record(args, ctx):
+def c5_record(args, ctx, wire=None):
     """The north-star's multi-GPU configuration (C5: RMAT 50M nodes / 150M edges, F = 128) measured in
     the same invocation as the headline and reported beside it (`c5` key); `value` / `config` of the
     line stay the C2 headline."""
     world, rank = ctx["world"], ctx["rank"]
     cfg = workload_cfg("c5")
-    m = measure_workload(args, cfg, ctx, full=False)
+    from dgl_b200 import dist as b200dist_
+    saved_wire = b200dist_.WIRE
+    if wire is not None:
+        b200dist_.WIRE = wire            # "bf16": halo rows cross NVLink as bfloat16 (1e-2 bar), fp32 accumulate
+    try:
+        m = measure_workload(args, cfg, ctx, full=False)
+    finally:
+        b200dist_.WIRE = saved_wire
     peak, peak_kind = measured_peak()
     rec = None
     if rank == 0:
@@ -969,10 +976,13 @@ def run_b200(args):
     if world > 1:
         b200dist.release_peer_memory()
     torch.cuda.empty_cache()
-    c5 = None
+    c5 = c5_bf16 = None
     if not args.no_c5 and args.workload == "c2":
         barrier()
         c5 = c5_record(args, ctx)
+        if world > 1:        # second lever of SURVEY 8e, reported beside the fp32-wire (parity-mode) record
+            barrier()
+            c5_bf16 = c5_record(args, ctx, wire="bf16")
 
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -996,7 +1006,7 @@ def run_b200(args):
             "edge_feat_per_s": 2 * e * feat / (ms_step * 1e-3),
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": keep["launches"], "clocks": keep["clocks"], "gcn_epoch": gcn,
-            "checked": bool(keep["check"] and keep["check"]["ok"]), "check": keep["check"], "c5": c5,
+            "checked": bool(keep["check"] and keep["check"]["ok"]), "check": keep["check"], "c5": c5, "c5_bf16_wire": c5_bf16,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

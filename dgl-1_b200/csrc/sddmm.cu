@@ -411,27 +411,54 @@ gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
   if (flavour == DGLB200_SOFTMAX_STABLE) {
 #pragma unroll
     for (int t = 0; t < TILES; ++t) mx[t] = -INFINITY;
-    for (int64_t p = start; p < end; ++p) {
-      const int64_t s = indices[p];
+    for (int64_t p = start; p < end; p += 4) {          // 4 independent id -> score chains per step
+      int64_t s4[4];
 #pragma unroll
-      for (int t = 0; t < TILES; ++t)
-        if (fvalid[t]) mx[t] = fmaxf(mx[t], gat_score(a_src[s * heads + head[t]], adst[t], slope));
+      for (int u = 0; u < 4; ++u) s4[u] = (p + u < end) ? (int64_t)indices[p + u] : -1;
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+#pragma unroll
+        for (int t = 0; t < TILES; ++t)
+          if (s4[u] >= 0 && fvalid[t]) mx[t] = fmaxf(mx[t], gat_score(a_src[s4[u] * heads + head[t]], adst[t], slope));
     }
   }
-  for (int64_t p = start; p < end; ++p) {
-    const int64_t s = indices[p];
+  // Main pass, U edges per step: all U column ids, then all U x TILES score + feature loads are issued
+  // before anything is consumed (round 1 walked one edge at a time: every iteration waited a full
+  // id -> row dependent-load chain, 53 ms at the C2-sized 8-head case against 32 ms for the three unfused
+  // kernels).  Accumulation stays in slot order.
+  constexpr int U = TILES >= 4 ? 2 : 4;
+  for (int64_t p = start; p < end; p += U) {
+    int64_t sidx[U];
+    float as[U][TILES];
+    float xv[U][TILES][VEC];
 #pragma unroll
-    for (int t = 0; t < TILES; ++t) {
-      if (!fvalid[t]) continue;
-      const float sc = gat_score(a_src[s * heads + head[t]], adst[t], slope);
-      float a;
-      if (flavour == DGLB200_SOFTMAX_STABLE) a = expf(sc - mx[t]);
-      else a = fminf(fmaxf(expf(sc), -10.f), 10.f);
-      float x[VEC];
-      Chunk<float, VEC>::load(ft + s * feat + foff[t], x);
-      z[t] += a;
+    for (int u = 0; u < U; ++u) sidx[u] = (p + u < end) ? (int64_t)indices[p + u] : -1;
 #pragma unroll
-      for (int v = 0; v < VEC; ++v) acc[t][v] = fmaf(a, x[v], acc[t][v]);
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int t = 0; t < TILES; ++t) {
+        as[u][t] = 0.f;
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) xv[u][t][v] = 0.f;
+        if (sidx[u] >= 0 && fvalid[t]) {
+          as[u][t] = a_src[sidx[u] * heads + head[t]];
+          Chunk<float, VEC>::load(ft + sidx[u] * feat + foff[t], xv[u][t]);
+        }
+      }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      if (sidx[u] < 0) continue;
+#pragma unroll
+      for (int t = 0; t < TILES; ++t) {
+        if (!fvalid[t]) continue;
+        const float sc = gat_score(as[u][t], adst[t], slope);
+        float a;
+        if (flavour == DGLB200_SOFTMAX_STABLE) a = expf(sc - mx[t]);
+        else a = fminf(fmaxf(expf(sc), -10.f), 10.f);
+        z[t] += a;
+#pragma unroll
+        for (int v = 0; v < VEC; ++v) acc[t][v] = fmaf(a, xv[u][t][v], acc[t][v]);
+      }
     }
   }
 #pragma unroll

@@ -190,6 +190,7 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
                          (msg == DGLB200_MSG_SRC_MUL_EDGE && a.w_mode == kWScalar);
   bool vec = ragged ? (ragged_ok && x_ok && a.x_ld >= a.feat + 1) : (x_ok && a.y_vec);
   if (a.w != nullptr && (a.w_mode == kWFull || msg == DGLB200_MSG_COPY_EDGE)) vec = vec && aligned16(a.w);
+  a.epi = (a.accumulate ? 1 : 0) | ((a.row_scale || a.bias || a.relu) ? 2 : 0);
   DGLB200_REQUIRE(!(a.accumulate && red != DGLB200_RED_SUM), "spmm: accumulate needs the SUM reducer");
   DGLB200_REQUIRE(!((a.row_scale || a.bias || a.relu) && red != DGLB200_RED_SUM),
                   "spmm: the row_scale / bias / relu epilogue needs the SUM reducer");

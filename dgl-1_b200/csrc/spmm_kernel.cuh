@@ -62,6 +62,7 @@ struct SpmmArgs {
   int64_t nnz;
   int rows_per_group;      // consecutive row steps a group walks (launch_one; >= 1)
   int accumulate;          // SUM: y += result (the caller sums several column blocks of the operand)
+  int epi;                 // host-computed: bit 0 accumulate, bit 1 row_scale / bias / relu (0 = plain store)
   const float* row_scale;  // SUM epilogue (fused GCN layer): y = act(row_scale[r] * sum + bias[f]); each nullable
   const float* bias;
   int relu;
@@ -137,6 +138,7 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
   // Sparse graphs (C5: mean degree 3, 75 % of the rows empty) are bound by CTA launch rate when a
   // warp retires after one short row (measured: an empty row cost as much as 3.65 edges), so a
   // group then walks `rows_per_group` rows; at every step the warp covers RPW consecutive rows.
+  const int epi = kMax ? 0 : a.epi;   // read once: sparse graphs run this epilogue once per 3 edges
   const int n_items = gw < a.n_chunk_warps ? 1 : a.rows_per_group;
 #pragma unroll 1
   for (int item_i = 0; item_i < n_items; ++item_i) {
@@ -448,7 +450,7 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
             if (v < nv) da[v] = best[t][v];
         }
       }
-      if (!kMax && a.accumulate) {      // y += result: add what is there, in one rounding per element
+      if (epi & 1) {      // y += result: add what is there, in one rounding per element
         if (VEC == 1 || (nv == VEC && a.y_vec)) {
           float old[VEC];
           Chunk<T, VEC>::load(y + out_row * a.y_ld + foff[t], old);
@@ -464,7 +466,7 @@ __global__ void __launch_bounds__(NT, spmm_min_blocks(MSG, RED, NT, TILES, (int)
             }
         }
       }
-      if (!kMax && (a.row_scale != nullptr || a.bias != nullptr || a.relu)) {
+      if (epi & 2) {
         // fused layer epilogue (examples/pytorch/gcn/gcn_spmv.py:55-60: h * norm, + bias, activation)
         const float rs = a.row_scale ? a.row_scale[out_row] : 1.f;
 #pragma unroll

@@ -55,7 +55,10 @@ MIXED_HALO = bool(int(os.environ.get("DGL_B200_MIXED_HALO", "0")))
 # all-gather partition: sum the column block of the rank's OWN source rows first (needs no exchange, so it
 # runs while every slab is still in flight), then add the remote column block slab by slab
 SPLIT_LOCAL = bool(int(os.environ.get("DGL_B200_SPLIT_LOCAL", "1")))
-ALLGATHER_SLAB = int(os.environ.get("DGL_B200_AG_SLAB", "64"))   # feature-slab width (elements) of the pipelined all-gather
+# feature-slab width (elements) of the pipelined all-gather; 0 = by rank count: 64 (the SpMM's own L2 slab at C2)
+# up to 2 ranks, 128 beyond - measured on C2 x 8 (ms/step): 64 -> 2.49, 128 -> 2.12, 256 (one push) -> 2.16: at 8
+# ranks an op is ~1 ms and the per-slab launches (push, wait, SpMM, fix-up) start to bound it
+ALLGATHER_SLAB = int(os.environ.get("DGL_B200_AG_SLAB", "0"))
 
 
 def chunk_fractions(chunks):
@@ -400,7 +403,7 @@ class RowPartition(object):
     def _slabs(self, feat, dtype):
         """Column blocks [(s0, width)] of the pipelined push all-gather: the SpMM's own L2 slab width
         (64 fp32 at C2), so that the per-slab launches do the work of the one slabbed launch."""
-        w = ALLGATHER_SLAB
+        w = ALLGATHER_SLAB if ALLGATHER_SLAB > 0 else (64 if self.world <= 2 else 128)
         if w <= 0 or feat <= w or feat % w or (w * torch.empty(0, dtype=dtype).element_size()) % 16:
             return [(0, feat)]
         return [(s0, w) for s0 in range(0, feat, w)]
