@@ -196,28 +196,30 @@ class SpmmPlan(object):
                                                   _ptr(ws), nbytes.value, _stream()))
         self.n_long_rows = int(counts[0])
         self.n_chunks = int(counts[1])
-        self._partial = None
-        self._partial_arg = None
 
     def struct(self, feat, want_arg):
-        """Fill a dglb200_spmm_plan_t for a call with `feat` features (None if no long rows)."""
+        """Fill a dglb200_spmm_plan_t for a call with `feat` features (None if no long rows).  The fp32
+        scratch of the long-row slices is allocated PER CALL from torch's stream-aware caching allocator
+        (a cached block, no cudaMalloc in steady state): two SpMMs over the same CSR issued on different
+        streams (the exchange pipelines of dist.py, user streams) no longer share one buffer (round-1 advisor
+        finding).  The struct keeps the tensors alive until the caller has enqueued the kernels; the
+        allocator then reuses the block in stream order."""
         if self.n_long_rows == 0:
             return None
         need = self.n_chunks * feat
         dev = self.csr.device
-        if self._partial is None or self._partial.numel() < need:
-            self._partial = torch.empty(need, dtype=torch.float32, device=dev)
-        if want_arg and (self._partial_arg is None or self._partial_arg.numel() < need):
-            self._partial_arg = torch.empty(need, dtype=torch.int32, device=dev)
+        partial = torch.empty(need, dtype=torch.float32, device=dev)
+        partial_arg = torch.empty(need, dtype=torch.int32, device=dev) if want_arg else None
         st = _lib.SpmmPlanStruct()
         st.chunk = self.chunk
         st.n_long_rows = self.n_long_rows
         st.n_chunks = self.n_chunks
         st.long_rows = self.long_rows.data_ptr()
         st.chunk_ptr = self.chunk_ptr.data_ptr()
-        st.partial = self._partial.data_ptr()
-        st.partial_arg = self._partial_arg.data_ptr() if want_arg else None
-        st.partial_bytes = self._partial.numel() * 4
+        st.partial = partial.data_ptr()
+        st.partial_arg = partial_arg.data_ptr() if want_arg else None
+        st.partial_bytes = need * 4
+        st._keep = (partial, partial_arg)
         return st
 
 

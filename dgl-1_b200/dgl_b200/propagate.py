@@ -15,15 +15,15 @@ def prop_edges(graph, edges_generator, message_func="default", reduce_func="defa
     graph.prop_edges(edges_generator, message_func, reduce_func, apply_node_func)
 
 
-def prop_nodes_bfs(graph, source, reversed=False, message_func="default", reduce_func="default",
+def prop_nodes_bfs(graph, source, reverse=False, message_func="default", reduce_func="default",
                    apply_node_func="default"):
     """python/dgl/propagate.py:57-86."""
-    prop_nodes(graph, trv.bfs_nodes_generator(graph, source, reversed), message_func, reduce_func,
+    prop_nodes(graph, trv.bfs_nodes_generator(graph, source, reverse), message_func, reduce_func,
                apply_node_func)
 
 
-def prop_nodes_topo(graph, reversed=False, message_func="default", reduce_func="default",
+def prop_nodes_topo(graph, reverse=False, message_func="default", reduce_func="default",
                     apply_node_func="default"):
     """python/dgl/propagate.py:88-114."""
-    prop_nodes(graph, trv.topological_nodes_generator(graph, reversed), message_func, reduce_func,
+    prop_nodes(graph, trv.topological_nodes_generator(graph, reverse), message_func, reduce_func,
                apply_node_func)

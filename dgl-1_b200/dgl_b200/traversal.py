@@ -16,10 +16,10 @@ from .base import DGLError
 from .graph import _as_ids
 
 
-def _next_hops(graph, frontier, reversed):
+def _next_hops(graph, frontier, reverse):
     """(neighbour, edge id) lists of the frontier: successors along out-edges, or predecessors along
-    in-edges when reversed (Graph::SuccVec / PredVec, OutEdgeVec / InEdgeVec)."""
-    if reversed:
+    in-edges when reverse (Graph::SuccVec / PredVec, OutEdgeVec / InEdgeVec)."""
+    if reverse:
         u, _, eid = graph.in_edges(frontier)
         return u, eid
     _, v, eid = graph.out_edges(frontier)
@@ -30,7 +30,7 @@ def _order_by(uniq, key):
     return uniq[torch.sort(key, stable=True)[1]]
 
 
-def bfs_nodes_generator(graph, source, reversed=False):
+def bfs_nodes_generator(graph, source, reverse=False):
     """Node frontiers of a breadth-first search from `source` (traversal.h:26-60)."""
     dev = graph._need_device()
     n = graph.number_of_nodes()
@@ -39,7 +39,7 @@ def bfs_nodes_generator(graph, source, reversed=False):
     visited[frontier] = True
     frontiers = [frontier]
     while True:
-        nxt, _ = _next_hops(graph, frontier, reversed)
+        nxt, _ = _next_hops(graph, frontier, reverse)
         nxt = nxt[~visited[nxt]]
         if nxt.numel() == 0:
             return frontiers
@@ -52,7 +52,7 @@ def bfs_nodes_generator(graph, source, reversed=False):
         frontiers.append(frontier)
 
 
-def bfs_edges_generator(graph, source, reversed=False):
+def bfs_edges_generator(graph, source, reverse=False):
     """Edge frontiers of a breadth-first search: the tree edge through which every node is first
     reached (traversal.h:78-118)."""
     dev = graph._need_device()
@@ -62,7 +62,7 @@ def bfs_edges_generator(graph, source, reversed=False):
     visited[frontier] = True
     frontiers = []
     while True:
-        nxt, eid = _next_hops(graph, frontier, reversed)
+        nxt, eid = _next_hops(graph, frontier, reverse)
         new = ~visited[nxt]
         nxt, eid = nxt[new], eid[new]
         if nxt.numel() == 0:
@@ -77,16 +77,16 @@ def bfs_edges_generator(graph, source, reversed=False):
         frontiers.append(eid[first])
 
 
-def topological_nodes_generator(graph, reversed=False):
+def topological_nodes_generator(graph, reverse=False):
     """Node frontiers of Kahn's algorithm (traversal.h:174-212); raises on a cycle."""
     dev = graph._need_device()
     n = graph.number_of_nodes()
-    deg = (graph.out_degrees() if reversed else graph.in_degrees()).clone()
+    deg = (graph.out_degrees() if reverse else graph.in_degrees()).clone()
     frontier = (deg == 0).nonzero().reshape(-1)
     visited = int(frontier.numel())
     frontiers = [frontier]
     while frontier.numel() > 0:
-        nxt, _ = _next_hops(graph, frontier, reversed)
+        nxt, _ = _next_hops(graph, frontier, reverse)
         if nxt.numel() == 0:
             break
         uniq, inv = ops.unique_sorted(nxt, n)

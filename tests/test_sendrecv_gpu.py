@@ -326,14 +326,14 @@ def test_frontier_generators_bit_exact(trav):
     import dgl_b200
     g = _graph_of(trav, "dag")
     _same_frontiers(dgl_b200.topological_nodes_generator(g), trav, "dag_topo")
-    _same_frontiers(dgl_b200.topological_nodes_generator(g, True), trav, "dag_topo_rev")
+    _same_frontiers(dgl_b200.topological_nodes_generator(g, reverse=True), trav, "dag_topo_rev")   # the reference's keyword (traversal.py:91)
     roots = cu(trav["in_dag_bfs_src"])
     _same_frontiers(dgl_b200.bfs_nodes_generator(g, roots), trav, "dag_bfs")
     _same_frontiers(dgl_b200.bfs_edges_generator(g, roots), trav, "dag_bfs_edges")
     c = _graph_of(trav, "cyc")
     start = cu(trav["in_cyc_bfs_src"])
     _same_frontiers(dgl_b200.bfs_nodes_generator(c, start), trav, "cyc_bfs")
-    _same_frontiers(dgl_b200.bfs_nodes_generator(c, start, True), trav, "cyc_bfs_rev")
+    _same_frontiers(dgl_b200.bfs_nodes_generator(c, start, reverse=True), trav, "cyc_bfs_rev")
     _same_frontiers(dgl_b200.bfs_edges_generator(c, start), trav, "cyc_bfs_edges")
     _same_frontiers(dgl_b200.bfs_edges_generator(c, start, True), trav, "cyc_bfs_edges_rev")
     from dgl_b200.base import DGLError
