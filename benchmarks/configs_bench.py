@@ -332,9 +332,71 @@ def cpu_layers():
            sorted(ts)[2] * 1e3, graphs.spmm_alg_bytes(e, n, hid, weights=True), n=n, e=e)
 
 
+def sampling():
+    """Neighbour sampling on a C2-shaped graph (232,965 nodes, power-law degrees; 1/5 of
+    Reddit's edges so that the reference's ImmutableGraph - two std::sorts of the edge list on one core - builds
+    in a bounded time): batches of 1000 seeds, fanout 10, 2 hops, in-neighbours.
+      * this engine: dgl_b200.sampling.sample_subgraph end to end (2 sampling launches + 3 sorted-set unions +
+        the subgraph's CSR build, with the size-returning syncs), and the sampling kernel alone over every row;
+      * CPU arm: the UNMODIFIED compiled reference (oracle/_ref/libdgl.so) through its C ABI - one batch per call
+        (one core) and 16 batches per call (its OpenMP path, graph_apis.cc:451-454)."""
+    import time
+    import numpy as np
+    from dgl_b200 import sampling as engine
+    c = graphs.C2_REDDIT
+    n, e = c["n"], c["e"] // 5
+    src, dst = graphs.powerlaw_symmetric(n, e, c["seed"], DEV)
+    e = int(src.shape[0])
+    csr = ops.csr_build(dst, src, n, n, order=1)
+    gen = torch.Generator(device="cpu").manual_seed(0)
+    batches = [torch.randperm(n, generator=gen)[:1000].to(DEV) for _ in range(16)]
+    fanout, hops = 10, 2
+    state = {"i": 0, "nodes": 0, "edges": 0, "calls": 0}
+
+    def one_batch():
+        sub = engine.sample_subgraph(csr, batches[state["i"] % 16], fanout, hops, seed=state["i"])
+        state["i"] += 1
+        state["nodes"] += int(sub.induced_nodes.shape[0])
+        state["edges"] += int(sub.induced_edges.shape[0])
+        state["calls"] += 1
+    ms = timeit(one_batch, warm=5, iters=40)
+    nodes, edges = state["nodes"] / state["calls"], state["edges"] / state["calls"]
+    report("C2/5", "neighbour sampling, 1000 seeds x fanout 10 x 2 hops: sample_subgraph end to end", ms,
+           edges * (8 + 3 * 8), n=n, e=e, nodes_per_subgraph=round(nodes), edges_per_subgraph=round(edges),
+           sampled_edges_per_s=round(edges / ms * 1e3))
+    rows = torch.arange(n, dtype=torch.int64, device=DEV)
+    for k in (10, 25):
+        picks = int(torch.clamp(ops.degrees(csr), max=k).sum())
+        ms_k = timeit(lambda: ops.neighbor_sample(csr, rows, k, seed=1), warm=3, iters=20)
+        report("C2/5", "sampling kernel pair (offsets + fill) over all %d rows, fanout %d" % (n, k), ms_k,
+               n * 32 + picks * (8 + 3 * 8), picks=picks, sampled_edges_per_s=round(picks / ms_k * 1e3))
+    del csr
+    # ---- CPU arm: the compiled reference
+    from oracle import ref_ffi
+    if not ref_ffi.available():
+        report("C2/5", "CPU BASELINE: reference NeighborUniformSample - oracle/_ref/libdgl.so not present", 0.0, 0)
+        return
+    t0 = time.perf_counter()
+    g = ref_ffi.RefGraph(src.cpu().numpy(), dst.cpu().numpy(), n, readonly=True, multigraph=True)
+    build_s = time.perf_counter() - t0
+    seeds_np = [b.cpu().numpy() for b in batches]
+    for per_call in (1, 16):
+        ts, got_edges = [], 0
+        for rep in range(6):
+            t0 = time.perf_counter()
+            res = ref_ffi.graph_uniform_sampling(g, seeds_np[:per_call], "in", hops, fanout)
+            ts.append(time.perf_counter() - t0)
+            got_edges = sum(len(r[1]) for r in res) / per_call
+        t = sorted(ts[1:])[len(ts[1:]) // 2] / per_call
+        report("C2/5", "CPU BASELINE: reference NeighborUniformSample (libdgl.so, %d batch(es) per call, %d cores)"
+               % (per_call, min(per_call, os.cpu_count() or 1)), t * 1e3, got_edges * (8 + 3 * 8),
+               edges_per_subgraph=round(got_edges), sampled_edges_per_s=round(got_edges / t),
+               immutable_graph_build_s=round(build_s, 1), speedup_of_engine=round(t * 1e3 / ms, 2))
+
+
 if __name__ == "__main__":
     sections = dict(c1=c1, c3=c3, c4=c4, c4rel=c4_per_relation, c2=c2_structure, c2ref=c2_torch_sparse,
-                    c3big=c3_at_c2_size, c5=c5_kernel, cpu=cpu_layers)
+                    c3big=c3_at_c2_size, c5=c5_kernel, cpu=cpu_layers, sampling=sampling)
     for name in (sys.argv[1:] or list(sections)):
         sections[name]()
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)

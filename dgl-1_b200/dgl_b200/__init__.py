@@ -14,6 +14,8 @@ from .batched_graph import (BatchedDGLGraph, batch, unbatch, sum_nodes, sum_edge
                             mean_edges, max_nodes, max_edges)
 from .edge_ops import sddmm, edge_softmax, gat_attention
 from .propagate import prop_nodes, prop_edges, prop_nodes_bfs, prop_nodes_topo
+from .subgraph import DGLSubGraph
+from . import contrib
 from .traversal import bfs_nodes_generator, bfs_edges_generator, topological_nodes_generator
 
 __version__ = "0.1.0"

@@ -57,6 +57,10 @@ SIGNATURES = {
     "dglb200_csr_select_expand": (c_int, [c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
                                           c_vp, c_vp]),
     "dglb200_degrees_of": (c_int, [c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp]),
+    "dglb200_neighbor_sample_offsets": (c_int, [c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, ctypes.POINTER(c_i64),
+                                                c_vp, c_sz, c_vp]),
+    "dglb200_neighbor_sample_fill": (c_int, [c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, ctypes.c_uint64,
+                                             c_vp, c_vp, c_vp, c_vp, c_vp]),
     "dglb200_spmm_plan_workspace_bytes": (c_int, [c_i64, ctypes.POINTER(c_sz)]),
     "dglb200_spmm_plan": (c_int, [c_i64, c_vp, c_i32, c_i64, c_vp, c_vp, ctypes.POINTER(c_i64),
                                   c_vp, c_sz, c_vp]),

@@ -65,7 +65,11 @@ def _as_ids(v, device=None):
 
 
 class DGLGraph(object):
-    def __init__(self, multigraph=True, readonly=False):
+    def __init__(self, graph_data=None, multigraph=True, readonly=False):
+        """graph_data: None, a scipy sparse matrix (row = source, column = destination, edge ids in the
+        order of its COO form: GraphIndex.from_scipy_sparse_matrix, python/dgl/graph_index.py:752-768) or an
+        edge list [(u, v), ...] (from_edge_list, :771-790).  readonly=True freezes the structure after
+        construction (the reference's ImmutableGraph; needed by the neighbour sampler)."""
         self._n = 0
         self._src = torch.empty(0, dtype=torch.int64)
         self._dst = torch.empty(0, dtype=torch.int64)
@@ -84,9 +88,50 @@ class DGLGraph(object):
         self._apply_edge_func = None
         self.last_prog = None
         self.execute = True         # False: only record the plan in last_prog (tests diff it)
+        self._imm = {}              # neighbour type -> (row, col)-sorted CSR (ImmutableGraph::CSR::FromEdges)
+        self._frozen = False
+        if graph_data is None and readonly:
+            raise DGLError("can't create an empty immutable graph")        # graph_index.py:971-972
+        if graph_data is not None:
+            self._from_data(graph_data)
+        self._frozen = bool(readonly)
+
+    def _from_data(self, data):
+        if hasattr(data, "tocoo"):
+            coo = data.tocoo()
+            n = max(coo.shape[0], coo.shape[1])
+            u = torch.as_tensor(coo.row, dtype=torch.int64)
+            v = torch.as_tensor(coo.col, dtype=torch.int64)
+        else:
+            try:
+                pairs = [(int(a), int(b)) for a, b in data]
+            except Exception:
+                raise DGLError('Error while creating graph from input of type "%s".' % type(data))
+            u = torch.tensor([p[0] for p in pairs], dtype=torch.int64)
+            v = torch.tensor([p[1] for p in pairs], dtype=torch.int64)
+            n = int(max(int(u.max()), int(v.max())) + 1) if pairs else 0
+        self.add_nodes(n)
+        if u.numel():
+            self.add_edges(u, v)
+
+    def is_readonly(self):
+        return self._readonly
+
+    def immutable_csr(self, neighbor_type="in"):
+        """The (row, column)-sorted CSR of the reference's ImmutableGraph (CSR::FromEdges,
+        src/graph/immutable_graph.cc:206-237; "in": keyed by destination, else by source), cached."""
+        key = "in" if neighbor_type == "in" else "out"
+        if key not in self._imm:
+            self._need_device()
+            src, dst = self.edges()
+            r, c = (dst, src) if key == "in" else (src, dst)
+            self._imm[key] = ops.csr_build(r, c, self._n, self._n, order=1)
+        return self._imm[key]
 
     # ---- structure -----------------------------------------------------------------------
     def add_nodes(self, num):
+        if self._frozen:
+            raise DGLError("Readonly graph. Mutation is not allowed.")
         self._n += int(num)
         self.clear_cache()
 
@@ -95,6 +140,8 @@ class DGLGraph(object):
 
     def add_edges(self, u, v):
         """Append edges; edge ids are assigned in insertion order (Graph::AddEdges, graph.cc:66-97)."""
+        if self._frozen:
+            raise DGLError("Readonly graph. Mutation is not allowed.")
         dev = self._device if self._device is not None else (u.device if torch.is_tensor(u) else None)
         u = _as_ids(u, dev)
         v = _as_ids(v, u.device)
@@ -142,6 +189,7 @@ class DGLGraph(object):
     def clear_cache(self):
         """Drop the cached device CSRs (GraphIndex.clear_cache, graph_index.py:113-115)."""
         self._adj = None
+        self._imm = {}
 
     def _reset_messages(self):
         """Structure changed: pending messages are dropped (the reference appends zero rows to

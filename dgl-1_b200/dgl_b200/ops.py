@@ -160,6 +160,38 @@ def csr_select(csr, rows, want=("which", "slot")):
     return tuple(outs[k] for k in want)
 
 
+def neighbor_sample(csr, rows, fanout, seed, want=("row", "col", "eid")):
+    """One hop of uniform neighbour sampling: min(degree, fanout) distinct slots of every CSR row in `rows`
+    (int64 CUDA, each row at most once per call), ascending slot order per row, rows in the order given:
+    dglb200_neighbor_sample_offsets + dglb200_neighbor_sample_fill.  Returns (offsets, outputs named by
+    `want` out of "row", "col", "eid", "slot"; all int64)."""
+    lib = _lib.get_lib()
+    _need_cuda(rows, csr.indptr)
+    rows = rows.contiguous()
+    if rows.dtype != torch.int64:
+        raise DGLError("neighbor_sample: ids must be int64")
+    dev = csr.device
+    n_sel = int(rows.shape[0])
+    nbytes = ctypes.c_size_t(0)
+    _lib.check_call(lib.dglb200_csr_select_workspace_bytes(n_sel, ctypes.byref(nbytes)))
+    ws = _workspace(nbytes.value, dev)
+    offsets = torch.empty(n_sel + 1, dtype=torch.int64, device=dev)
+    total = ctypes.c_int64(0)
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_neighbor_sample_offsets(n_sel, _ptr(rows), csr.n_rows, _ptr(csr.indptr),
+                                                            int(fanout), _ptr(offsets), ctypes.byref(total),
+                                                            _ptr(ws), nbytes.value, _stream()))
+    total = int(total.value)
+    outs = {k: (torch.empty(total, dtype=torch.int64, device=dev) if k in want else None)
+            for k in ("row", "col", "eid", "slot")}
+    with torch.cuda.device(dev):
+        _lib.check_call(lib.dglb200_neighbor_sample_fill(
+            n_sel, _ptr(rows), _ptr(offsets), _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids), int(fanout),
+            int(seed) & 0xFFFFFFFFFFFFFFFF, _ptr(outs["row"]), _ptr(outs["col"]), _ptr(outs["eid"]),
+            _ptr(outs["slot"]), _stream()))
+    return (offsets,) + tuple(outs[k] for k in want)
+
+
 def degrees_of(csr, rows):
     """Degrees of the CSR rows `rows` (int64 CUDA): dglb200_degrees_of."""
     _need_cuda(rows, csr.indptr)

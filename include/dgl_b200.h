@@ -131,6 +131,33 @@ int dglb200_csr_select_expand(int64_t n_sel, int64_t total, const int64_t* rows,
 int dglb200_degrees_of(int64_t n_sel, const int64_t* rows, int64_t n_rows, const int64_t* indptr,
                        int64_t* deg, int32_t* bad_flag, void* stream);
 
+/*
+ * One hop of uniform neighbour sampling over a CSR - replaces the loop body of
+ * ImmutableGraph::SampleSubgraph with GetUniformSample (src/graph/immutable_graph.cc:701-741, 772-874;
+ * reached from NeighborSampler, python/dgl/contrib/sampling/sampler.py:196, through
+ * graph_index._CAPI_DGLGraphUniformSampling*, src/graph/graph_apis.cc:434-472).  For every selected row,
+ * min(degree, fanout) DISTINCT slots, every subset of that size equally likely, emitted in ascending
+ * slot order (the reference sorts its picks, :720/:727).  Rows with degree <= fanout are copied whole.
+ * Two steps because the output size is data dependent:
+ *   neighbor_sample_offsets: offsets[i] = sum of min(degree, fanout) over rows[0..i); *total_host =
+ *     offsets[n_sel].  Workspace: dglb200_csr_select_workspace_bytes(n_sel).  An id outside [0, n_rows) is
+ *     an error.  Syncs the stream (returns the total).
+ *   neighbor_sample_fill: for the j-th pick (ascending slot s) of selection i, at p = offsets[i] + j:
+ *     out_row[p] = rows[i], out_col[p] = indices[s], out_eid[p] = eids[s] (s when eids == NULL),
+ *     out_slot[p] = s.  Every output is nullable.  Does not sync.
+ * The draws come from a counter-based generator keyed by (seed, row id, draw, attempt): the same seed gives
+ * the same sample whatever the launch geometry.  The reference seeds rand_r with time(nullptr) (:778), so
+ * its samples are not reproducible and parity is pinned on what IS deterministic (degree <= fanout: whole
+ * rows, golden vectors of the unmodified reference) plus the distribution (tests).
+ */
+int dglb200_neighbor_sample_offsets(int64_t n_sel, const int64_t* rows, int64_t n_rows, const int64_t* indptr,
+                                    int64_t fanout, int64_t* offsets, int64_t* total_host,
+                                    void* workspace, size_t workspace_bytes, void* stream);
+int dglb200_neighbor_sample_fill(int64_t n_sel, const int64_t* rows, const int64_t* offsets,
+                                 const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                                 int64_t fanout, uint64_t seed, int64_t* out_row, int64_t* out_col,
+                                 int64_t* out_eid, int64_t* out_slot, void* stream);
+
 /* ---- (1)(2) SpMM: generalised message -> reduce over a CSR -------------------------- */
 
 /*

@@ -291,3 +291,111 @@ def canonicalize_bucketing(degs, nids, nid_section, mids, mid_section):
         o_nids.extend(sorted(nodes))
     i64 = lambda a: np.asarray(a, dtype=np.int64)
     return i64(o_degs), i64(o_nids), i64(o_nsec), i64(o_mids), i64(o_msec)
+
+
+# ---------------------------------------------------------------------------------------
+# neighbour sampling
+# ---------------------------------------------------------------------------------------
+
+def neighbor_sample_subgraph(indptr, indices, eids, seeds, fanout, num_hops, rng=None):
+    """ImmutableGraph::NeighborUniformSample = SampleSubgraph + CompactSubgraph
+    (src/graph/immutable_graph.cc:772-1008) over one CSR of the immutable graph (in-CSR for
+    neighbor_type "in", else the out-CSR, :780): a BFS queue over (vertex, layer); every queued vertex
+    below the last layer contributes min(degree, fanout) slots of its row - the whole row
+    (GetUniformSample :710-716) or `fanout` distinct slots in ascending slot order (:717-741; drawn with
+    `rng`, a numpy RandomState - the reference uses rand_r seeded by time(), so only calls that never
+    meet degree > fanout are reproducible).  Returns int64 arrays
+      induced_nodes (ascending), layer_ids, induced_edges (parent edge ids, subgraph-edge order),
+      sub_indptr, sub_indices (compacted ids) - the CSR of the subgraph whose edge ids are 0..E-1."""
+    indptr = np.asarray(indptr, dtype=np.int64)
+    indices = np.asarray(indices, dtype=np.int64)
+    eids = np.asarray(eids, dtype=np.int64)
+    layer = {}
+    queue = []
+    for s in np.asarray(seeds, dtype=np.int64).tolist():         # :787-793
+        if s not in layer:
+            layer[s] = 0
+            queue.append(s)
+    picked = {}                                                  # vertex -> (neighbours, edge ids)
+    q = 0
+    while q < len(queue):                                        # :806-861
+        v = queue[q]
+        q += 1
+        if layer[v] >= num_hops:
+            continue
+        lo, hi = int(indptr[v]), int(indptr[v + 1])
+        deg = hi - lo
+        if deg <= fanout:
+            slots = np.arange(lo, hi)
+        else:
+            if rng is None:
+                raise ValueError("degree %d > fanout %d needs an rng" % (deg, fanout))
+            slots = lo + np.sort(rng.choice(deg, int(fanout), replace=False))
+        picked[v] = (indices[slots], eids[slots])
+        for u in indices[slots].tolist():                        # :852-860
+            if u not in layer:
+                layer[u] = layer[v] + 1
+                queue.append(u)
+    nodes = np.array(sorted(layer), dtype=np.int64)              # :875-895
+    layers = np.array([layer[v] for v in nodes.tolist()], dtype=np.int64)
+    sub_indptr = np.zeros(len(nodes) + 1, dtype=np.int64)
+    cols, edges = [], []
+    for i, v in enumerate(nodes.tolist()):                       # :919-946
+        if v in picked:
+            cols.append(picked[v][0])
+            edges.append(picked[v][1])
+            sub_indptr[i + 1] = sub_indptr[i] + len(picked[v][0])
+        else:
+            sub_indptr[i + 1] = sub_indptr[i]
+    cols = np.concatenate(cols) if cols else np.zeros(0, dtype=np.int64)
+    edges = np.concatenate(edges) if edges else np.zeros(0, dtype=np.int64)
+    sub_indices = np.searchsorted(nodes, cols).astype(np.int64)  # CompactSubgraph :963-983
+    return nodes, layers, edges.astype(np.int64), sub_indptr, sub_indices
+
+
+def check_neighbor_subgraph(indptr, indices, eids, seeds, fanout, num_hops,
+                            induced_nodes, layer_ids, induced_edges, sub_rows, sub_cols):
+    """Everything SampleSubgraph guarantees about its output whatever the random draws were, asserted.
+    (indptr, indices, eids): the parent CSR that was sampled; sub_rows / sub_cols: per subgraph edge (in
+    subgraph-edge-id order) the compacted id of the row vertex (the one whose neighbour list was sampled)
+    and of the sampled neighbour.  Pinned on real outputs of the reference (tests/golden/sampling_*.npz).
+      1. induced_nodes strictly ascending; layer 0 is exactly the set of seeds;
+      2. subgraph edges are grouped by row vertex in ascending order (the sub-CSR, :919-946);
+      3. edge i is a slot of its row vertex in the parent CSR: column = the neighbour, edge id =
+         induced_edges[i]; within a row the slots are distinct and ascending (:720-741);
+      4. a vertex below the last layer has min(degree, fanout) edges - its whole row when
+         degree <= fanout (:710-716); a vertex of the last layer has none (:814-815);
+      5. a non-seed vertex's layer is 1 + the smallest layer among the rows that picked it (BFS, :852-860)."""
+    indptr = np.asarray(indptr, dtype=np.int64)
+    indices = np.asarray(indices, dtype=np.int64)
+    eids = np.asarray(eids, dtype=np.int64)
+    nodes = np.asarray(induced_nodes, dtype=np.int64)
+    layers = np.asarray(layer_ids, dtype=np.int64)
+    edges = np.asarray(induced_edges, dtype=np.int64)
+    rows = np.asarray(sub_rows, dtype=np.int64)
+    cols = np.asarray(sub_cols, dtype=np.int64)
+    assert len(nodes) == len(layers) and len(edges) == len(rows) == len(cols)
+    assert np.all(np.diff(nodes) > 0), "induced_nodes not strictly ascending"
+    seeds = np.unique(np.asarray(seeds, dtype=np.int64))
+    assert np.array_equal(nodes[layers == 0], seeds), "layer 0 != the seeds"
+    assert layers.min(initial=0) >= 0 and layers.max(initial=0) <= num_hops
+    assert np.all(np.diff(rows) >= 0), "subgraph edges not grouped by ascending row vertex"
+    slot_of_eid = np.full(int(eids.max(initial=-1)) + 1, -1, dtype=np.int64)
+    slot_of_eid[eids] = np.arange(len(eids))
+    slots = slot_of_eid[edges]
+    assert np.all(slots >= 0)
+    pr = nodes[rows]
+    assert np.all((slots >= indptr[pr]) & (slots < indptr[pr + 1])), "edge is not a slot of its row"
+    assert np.array_equal(indices[slots], nodes[cols]), "column does not match the parent edge"
+    same = rows[1:] == rows[:-1]
+    assert np.all(slots[1:][same] > slots[:-1][same]), "slots of a row not distinct ascending"
+    cnt = np.bincount(rows, minlength=len(nodes))
+    deg = indptr[nodes + 1] - indptr[nodes]
+    want = np.where(layers < num_hops, np.minimum(deg, fanout), 0)
+    assert np.array_equal(cnt, want), "edges per vertex != min(degree, fanout)"
+    best = np.full(len(nodes), num_hops + 1, dtype=np.int64)
+    np.minimum.at(best, cols, layers[rows] + 1)
+    non_seed = layers > 0
+    assert np.array_equal(best[non_seed], layers[non_seed]), "layer ids are not BFS levels"
+    assert np.all(best[~non_seed] >= 1)
+    return True

@@ -200,3 +200,25 @@ def degree_bucketing(msg_ids, vids, recv_ids):
     b = get_global("runtime.degree_bucketing._CAPI_DGLDegreeBucketing")(
         np.asarray(msg_ids, np.int64), np.asarray(vids, np.int64), np.asarray(recv_ids, np.int64))
     return tuple(b(i) for i in range(5))
+
+
+def graph_uniform_sampling(g, seed_arrays, neighbor_type, num_hops, fanout, want_graph=False):
+    """ImmutableGraph::NeighborUniformSample for 1, 2, 4 .. 128 seed arrays in ONE call (sampled on OpenMP
+    threads, one per array: src/graph/graph_apis.cc:434-472).  `g` must be readonly.  Returns a list of
+    (induced_nodes, induced_edges, layer_ids) int64 arrays; with want_graph also the subgraph's in-/out-CSR
+    (indptr, indices, eid) as a 4th entry."""
+    k = len(seed_arrays)
+    assert k in (1, 2, 4, 8, 16, 32, 64, 128)
+    name = "graph_index._CAPI_DGLGraphUniformSampling" + ("" if k == 1 else str(k))
+    args = [np.ascontiguousarray(s, dtype=np.int64) for s in seed_arrays]
+    rst = get_global(name)(g.handle, *args, neighbor_type, int(num_hops), int(fanout), k)
+    out = []
+    for i in range(k):
+        handle = rst(i)
+        rec = (rst(k + i), rst(2 * k + i), rst(3 * k + i))
+        if want_graph:
+            adj = get_global("graph_index._CAPI_DGLGraphGetAdj")(handle, neighbor_type != "in", "csr")
+            rec = rec + ((adj(0), adj(1), adj(2)),)
+        get_global("graph_index._CAPI_DGLGraphFree")(handle)
+        out.append(rec)
+    return out

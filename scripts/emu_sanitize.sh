@@ -7,7 +7,7 @@
 #   scripts/emu_sanitize.sh address|thread
 set -e
 KIND=${1:-address}
-SEL="spmm or csr or sddmm or gather or softmax or bucketing"
+SEL="spmm or csr or sddmm or gather or softmax or bucketing or sampling"
 if [ "$KIND" = address ]; then
   export LD_PRELOAD=$(gcc -print-file-name=libasan.so) ASAN_OPTIONS=detect_leaks=0:halt_on_error=1
 else

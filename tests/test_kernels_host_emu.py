@@ -31,6 +31,7 @@ from tests import test_uopv_edge_ops_gpu as t_edge
 from tests import test_wire_convert_gpu as t_wire
 from tests import test_zz_no_alloc as t_noalloc
 from tests import test_fused_gcn_gpu as t_fused
+from tests import test_sampling_gpu as t_samp
 
 pytestmark = pytest.mark.timeout(900)     # a lost rendezvous must fail the test, not hang the tier
 
@@ -84,7 +85,7 @@ def emu(monkeypatch, emu_lib):
         monkeypatch.setattr(torch, name, wrapped)
     real_gen = torch.Generator
     monkeypatch.setattr(torch, "Generator", lambda device="cpu": real_gen(device=_cpu_device(device)))
-    for mod in (t_msg, t_edge, t_noalloc, t_fused):
+    for mod in (t_msg, t_edge, t_noalloc, t_fused, t_samp):
         monkeypatch.setattr(mod, "device", lambda: torch.device("cpu"))
     launches0 = emu_lib.dglb200_launch_count()
     yield emu_lib
@@ -251,3 +252,26 @@ def test_static_scratch_entry_point_on_emulated_kernels(emu):
 def test_fused_gcn_layer_against_reference_example(emu):
     t_fused.test_fused_layer_matches_reference_example_layer(t_fused.GOLDEN[0])
     t_fused.test_epilogue_on_long_rows_ragged_width_and_empty_rows()
+
+
+# ---- neighbour sampling ------------------------------------------------------------
+
+def test_sampling_golden_cases_of_the_reference(emu):
+    t_samp.test_golden_cases_of_the_reference()
+
+
+@pytest.mark.parametrize("deg,fanout,branch", [(40, 5, "kept set"), (12, 11, "dropped set"), (300, 172, "dropped set"),
+                                               (700, 300, "selection")])
+def test_sampling_distribution(emu, monkeypatch, deg, fanout, branch):
+    monkeypatch.setattr(t_samp, "TRIALS", 240)
+    t_samp.test_every_slot_and_every_pair_equally_likely(deg, fanout, branch)
+
+
+def test_sampling_reproducible_and_hubs(emu):
+    t_samp.test_same_seed_same_sample_and_seeds_differ()
+    t_samp.test_hubs_multigraph_and_zero_fanout()
+
+
+def test_sampling_reference_sampler_test_with_features(emu):
+    # the 1-seed-per-batch loops of the reference's test_sampler.py (300 subgraphs) are left to the GPU tier
+    t_samp.test_reference_test_10neighbor_sampler_all_and_features()
