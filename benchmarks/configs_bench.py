@@ -54,7 +54,8 @@ OUT = []
 
 def report(config, op, ms, alg_bytes, **extra):
     rec = dict(config=config, op=op, us=round(ms * 1e3, 2), alg_bytes=int(alg_bytes),
-               alg_GBps=round(alg_bytes / ms / 1e6, 1), frac_of_hbm_peak=round(alg_bytes / ms / 1e6 / PEAK, 4))
+               alg_GBps=round(alg_bytes / max(ms, 1e-9) / 1e6, 1),
+               frac_of_hbm_peak=round(alg_bytes / max(ms, 1e-9) / 1e6 / PEAK, 4))
     rec.update(extra)
     OUT.append(rec)
     print(json.dumps(rec), flush=True)
@@ -336,8 +337,9 @@ def sampling():
     """Neighbour sampling on a C2-shaped graph (232,965 nodes, power-law degrees; 1/5 of
     Reddit's edges so that the reference's ImmutableGraph - two std::sorts of the edge list on one core - builds
     in a bounded time): batches of 1000 seeds, fanout 10, 2 hops, in-neighbours.
-      * this engine: dgl_b200.sampling.sample_subgraph end to end (2 sampling launches + 3 sorted-set unions +
-        the subgraph's CSR build, with the size-returning syncs), and the sampling kernel alone over every row;
+      * this engine: dgl_b200.sampling.sample_subgraph end to end (per hop: offsets + the sampling kernel that
+        also discovers the next frontier; then the bitmap compaction and the placement of the picks; 3 syncs that
+        return sizes), and the sampling kernel alone over every row;
       * CPU arm: the UNMODIFIED compiled reference (oracle/_ref/libdgl.so) through its C ABI - one batch per call
         (one core) and 16 batches per call (its OpenMP path, graph_apis.cc:451-454)."""
     import time
@@ -394,9 +396,158 @@ def sampling():
                immutable_graph_build_s=round(build_s, 1), speedup_of_engine=round(t * 1e3 / ms, 2))
 
 
+def _capture(step, warm=3):
+    """torch.cuda.CUDAGraph of `step` (which must use static input tensors): warm up on a side stream, capture,
+    return the graph.  Any cudaStreamSynchronize / size-returning call inside `step` makes the capture fail -
+    which is the point of the exercise (round-1 review: "impossible as written")."""
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        for _ in range(warm):
+            step()
+    torch.cuda.current_stream().wait_stream(s)
+    torch.cuda.synchronize()
+    gph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(gph):
+        out = step()
+    return gph, out
+
+
+def graph_capture():
+    """The launch-latency-bound configs as ONE CUDA graph per training step: the structure (CSR
+    pair, long-row plan) is built once per graph, the steady-state step of the builtin path has no
+    size-returning call left in it, so a whole forward + backward + SGD update is captured and replayed.
+      C1: 2-layer GCN (gcn_spmv.py) on the Cora-shaped graph through DGLGraph.update_all;
+      C3: one GAT layer (8 heads x 8) on the PubMed-shaped graph through gat_attention (SDDMM -> edge softmax ->
+          weighted SpMM and their gradient kernels);
+      C4: one R-GCN layer on the AIFB-shaped graph, src_mul_edge -> sum with a per-edge norm, all relations in one
+          launch."""
+    import dgl_b200
+    import dgl_b200.function as fn
+    from dgl_b200 import _lib, autograd, edge_ops
+    lr = 1e-2
+
+    def sgd(params):
+        with torch.no_grad():
+            for p in params:
+                p.add_(p.grad, alpha=-lr)
+                p.grad = None
+
+    only = os.environ.get("CAPTURE_ONLY")          # a failed capture poisons the process: one config per process
+
+    def measure(tag, step, params, n, e):
+        # capture FIRST: the parameters' AccumulateGrad nodes must not have been created on the default stream
+        try:
+            gph, out = _capture(step)
+        except Exception as ex:  # noqa: BLE001
+            import traceback
+            traceback.print_exc()
+            report(tag, "training step: CUDA-graph capture FAILED: %s | %s" % (str(ex).splitlines()[0][:200],
+                                                                              _lib.last_error()[:200]), 0.0, 0, n=n, e=e)
+            return
+        l0 = _lib.launch_count()
+        step()
+        torch.cuda.synchronize()
+        launches = _lib.launch_count() - l0
+        eager_ms = timeit(step, warm=5, iters=30)
+        # replay equals eager: same weights in, same loss / weights out
+        saved = [p.detach().clone() for p in params]
+        gph.replay()
+        torch.cuda.synchronize()
+        after_graph = [p.detach().clone() for p in params]
+        with torch.no_grad():
+            for p, q in zip(params, saved):
+                p.copy_(q)
+        torch.manual_seed(0)
+        step()
+        torch.cuda.synchronize()
+        same = all(torch.allclose(a, p.detach(), rtol=1e-5, atol=1e-6) for a, p in zip(after_graph, params))
+        graph_ms = timeit(gph.replay, warm=5, iters=30)
+        report(tag, "training step (fwd + bwd + SGD): eager", eager_ms, 0, n=n, e=e, engine_launches_per_step=launches)
+        report(tag, "training step (fwd + bwd + SGD): ONE CUDA graph replay", graph_ms, 0, n=n, e=e,
+               engine_launches_per_step=launches, speedup_vs_eager=round(eager_ms / graph_ms, 2),
+               replay_equals_eager=bool(same))
+
+    # ---- C1
+    c = graphs.C1_CORA
+    n = c["n"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], DEV, self_loops=True)
+    g = dgl_b200.DGLGraph()
+    g.add_nodes(n)
+    g.add_edges(src, dst)
+    g.to(DEV)
+    norm = g.in_degrees().float().clamp(min=1).pow(-0.5).unsqueeze(1)
+    x = torch.randn(n, c["feat_in"], device=DEV)
+    labels = torch.randint(0, c["classes"], (n,), device=DEV)
+    w1 = (torch.randn(c["feat_in"], c["hidden"], device=DEV) * 0.05).requires_grad_(True)
+    w2 = (torch.randn(c["hidden"], c["classes"], device=DEV) * 0.05).requires_grad_(True)
+    b1 = torch.zeros(c["hidden"], device=DEV, requires_grad=True)
+    b2 = torch.zeros(c["classes"], device=DEV, requires_grad=True)
+
+    def agg(h):
+        g.ndata["h"] = h
+        g.update_all(fn.copy_src("h", "m"), fn.sum("m", "h"))
+        return g.ndata.pop("h")
+
+    def gcn_step():
+        h = torch.relu(agg(torch.mm(x, w1) * norm) * norm + b1)
+        logits = agg(torch.mm(h, w2) * norm) * norm + b2
+        loss = torch.nn.functional.cross_entropy(logits, labels)
+        loss.backward()
+        sgd([w1, w2, b1, b2])
+        return loss
+    if only in (None, "C1"):
+        g.ndata["h"] = torch.zeros(n, 1, device=DEV)
+        g.update_all(fn.copy_src("h", "m"), fn.sum("m", "h"))     # structure + plan built before the capture
+        measure("C1", gcn_step, [w1, w2, b1, b2], n, int(src.shape[0]))
+
+    # ---- C3
+    c = graphs.C3_PUBMED
+    n, heads, hid = c["n"], c["heads"], c["hidden"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], DEV, self_loops=True)
+    adj = autograd.Adjacency(n, n, coo=(dst, src, None))
+    _ = adj.csr_in, adj.csr_out
+    x3 = torch.randn(n, c["feat_in"], device=DEV)
+    wf = (torch.randn(c["feat_in"], heads * hid, device=DEV) * 0.05).requires_grad_(True)
+    al = (torch.randn(heads, hid, device=DEV) * 0.1).requires_grad_(True)
+    ar = (torch.randn(heads, hid, device=DEV) * 0.1).requires_grad_(True)
+
+    def gat_step():
+        ft = torch.mm(x3, wf).reshape(n, heads, hid)
+        a1 = (ft * al).sum(-1)
+        a2 = (ft * ar).sum(-1)
+        out, _ = edge_ops.gat_attention(adj, a1, a2, ft, 0.2)
+        loss = out.square().mean()
+        loss.backward()
+        sgd([wf, al, ar])
+        return loss
+    if only in (None, "C3"):
+        measure("C3", gat_step, [wf, al, ar], n, int(src.shape[0]))
+
+    # ---- C4
+    c = graphs.C4_AIFB
+    n, hid = c["n"], c["hidden"]
+    src, dst = graphs.uniform_graph(n, c["e"], c["seed"], DEV)
+    adj4 = autograd.Adjacency(n, n, coo=(dst, src, None))
+    _ = adj4.csr_in, adj4.csr_out
+    e4 = int(src.shape[0])
+    enorm = torch.rand(e4, 1, device=DEV)
+    emb = (torch.randn(n, hid, device=DEV) * 0.1).requires_grad_(True)
+    w4 = (torch.randn(hid, hid, device=DEV) * 0.1).requires_grad_(True)
+
+    def rgcn_step():
+        h = autograd.aggregate(adj4, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=torch.mm(emb, w4), w=enorm, w_width=1)
+        loss = torch.relu(h).square().mean()
+        loss.backward()
+        sgd([emb, w4])
+        return loss
+    if only in (None, "C4"):
+        measure("C4", rgcn_step, [emb, w4], n, e4)
+
+
 if __name__ == "__main__":
     sections = dict(c1=c1, c3=c3, c4=c4, c4rel=c4_per_relation, c2=c2_structure, c2ref=c2_torch_sparse,
-                    c3big=c3_at_c2_size, c5=c5_kernel, cpu=cpu_layers, sampling=sampling)
+                    c3big=c3_at_c2_size, c5=c5_kernel, cpu=cpu_layers, sampling=sampling, capture=graph_capture)
     for name in (sys.argv[1:] or list(sections)):
         sections[name]()
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)

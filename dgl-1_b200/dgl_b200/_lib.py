@@ -40,6 +40,13 @@ class SpmmExtStruct(ctypes.Structure):
 
 
 # name -> (restype, argtypes); must list every symbol of include/dgl_b200.h
+class SampledSubgraphStruct(ctypes.Structure):
+    """dglb200_sampled_subgraph_t (include/dgl_b200.h)."""
+    _fields_ = [("n_nodes", ctypes.c_int64), ("n_edges", ctypes.c_int64), ("nodes", ctypes.c_void_p),
+                ("layers", ctypes.c_void_p), ("sub_indptr", ctypes.c_void_p), ("sub_indices", ctypes.c_void_p),
+                ("sub_rows", ctypes.c_void_p), ("induced_edges", ctypes.c_void_p), ("needed_bytes", ctypes.c_size_t)]
+
+
 SIGNATURES = {
     "dglb200_abi_version": (c_int, []),
     "dglb200_last_error": (ctypes.c_char_p, []),
@@ -57,10 +64,12 @@ SIGNATURES = {
     "dglb200_csr_select_expand": (c_int, [c_i64, c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
                                           c_vp, c_vp]),
     "dglb200_degrees_of": (c_int, [c_i64, c_vp, c_i64, c_vp, c_vp, c_vp, c_vp]),
-    "dglb200_neighbor_sample_offsets": (c_int, [c_i64, c_vp, c_i64, c_vp, c_i64, c_vp, ctypes.POINTER(c_i64),
-                                                c_vp, c_sz, c_vp]),
-    "dglb200_neighbor_sample_fill": (c_int, [c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, ctypes.c_uint64,
-                                             c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "dglb200_neighbor_sample_offsets": (c_int, [c_i64, c_vp, c_vp, c_i64, c_vp, c_i64, c_vp, ctypes.POINTER(c_i64),
+                                                ctypes.POINTER(c_i64), c_vp, c_sz, c_vp]),
+    "dglb200_neighbor_sample_fill": (c_int, [c_i64, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i64, ctypes.c_uint64,
+                                             c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_vp]),
+    "dglb200_sample_subgraph": (c_int, [c_i64, c_vp, c_vp, c_vp, c_i64, c_vp, c_i64, c_i32, ctypes.c_uint64, c_vp,
+                                        c_vp, c_vp, c_vp, c_sz, ctypes.POINTER(SampledSubgraphStruct), c_vp]),
     "dglb200_spmm_plan_workspace_bytes": (c_int, [c_i64, ctypes.POINTER(c_sz)]),
     "dglb200_spmm_plan": (c_int, [c_i64, c_vp, c_i32, c_i64, c_vp, c_vp, ctypes.POINTER(c_i64),
                                   c_vp, c_sz, c_vp]),

@@ -163,8 +163,9 @@ def csr_select(csr, rows, want=("which", "slot")):
 def neighbor_sample(csr, rows, fanout, seed, want=("row", "col", "eid")):
     """One hop of uniform neighbour sampling: min(degree, fanout) distinct slots of every CSR row in `rows`
     (int64 CUDA, each row at most once per call), ascending slot order per row, rows in the order given:
-    dglb200_neighbor_sample_offsets + dglb200_neighbor_sample_fill.  Returns (offsets, outputs named by
-    `want` out of "row", "col", "eid", "slot"; all int64)."""
+    dglb200_neighbor_sample_offsets + dglb200_neighbor_sample_fill (without the device-side frontier / discovery
+    arguments, which dglb200_sample_subgraph drives itself).  Returns (offsets, outputs named by `want` out of
+    "row", "col", "eid", "slot"; all int64)."""
     lib = _lib.get_lib()
     _need_cuda(rows, csr.indptr)
     rows = rows.contiguous()
@@ -178,18 +179,69 @@ def neighbor_sample(csr, rows, fanout, seed, want=("row", "col", "eid")):
     offsets = torch.empty(n_sel + 1, dtype=torch.int64, device=dev)
     total = ctypes.c_int64(0)
     with torch.cuda.device(dev):
-        _lib.check_call(lib.dglb200_neighbor_sample_offsets(n_sel, _ptr(rows), csr.n_rows, _ptr(csr.indptr),
-                                                            int(fanout), _ptr(offsets), ctypes.byref(total),
+        _lib.check_call(lib.dglb200_neighbor_sample_offsets(n_sel, _ptr(rows), None, csr.n_rows, _ptr(csr.indptr),
+                                                            int(fanout), _ptr(offsets), ctypes.byref(total), None,
                                                             _ptr(ws), nbytes.value, _stream()))
     total = int(total.value)
     outs = {k: (torch.empty(total, dtype=torch.int64, device=dev) if k in want else None)
             for k in ("row", "col", "eid", "slot")}
     with torch.cuda.device(dev):
         _lib.check_call(lib.dglb200_neighbor_sample_fill(
-            n_sel, _ptr(rows), _ptr(offsets), _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids), int(fanout),
-            int(seed) & 0xFFFFFFFFFFFFFFFF, _ptr(outs["row"]), _ptr(outs["col"]), _ptr(outs["eid"]),
-            _ptr(outs["slot"]), _stream()))
+            n_sel, _ptr(rows), None, _ptr(offsets), _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids),
+            int(fanout), int(seed) & 0xFFFFFFFFFFFFFFFF, _ptr(outs["row"]), _ptr(outs["col"]), _ptr(outs["eid"]),
+            _ptr(outs["slot"]), None, None, 0, None, None, _stream()))
     return (offsets,) + tuple(outs[k] for k in want)
+
+
+class SampleState(object):
+    """Persistent discovery state of the sampler for one parent graph (dglb200_sample_subgraph):
+    layer int32[n] = -1, bitmap uint32[ceil(n / 32)] = 0, word-prefix scratch.  One sampling call at a time."""
+
+    def __init__(self, n_rows, device):
+        self.n_rows = int(n_rows)
+        words = (self.n_rows + 31) // 32
+        self.layer = torch.full((self.n_rows,), -1, dtype=torch.int32, device=device)
+        self.bitmap = torch.zeros(words, dtype=torch.int32, device=device)
+        self.word_prefix = torch.empty(words + 1, dtype=torch.int32, device=device)
+        self.ws_bytes = 0          # workspace size that carried the largest call so far
+
+
+def sample_subgraph(csr, state, seeds, fanout, num_hops, seed):
+    """dglb200_sample_subgraph: the whole multi-hop call.  Returns (nodes, layers, sub_indptr, sub_indices int32,
+    sub_rows, induced_edges) - views into one workspace tensor that the call's results live in.  The workspace
+    is sized from the largest call seen on this state; a call that needs more is retried once it says how much."""
+    lib = _lib.get_lib()
+    _need_cuda(seeds, csr.indptr, state.layer)
+    dev = csr.device
+    seeds = seeds.contiguous()
+    out = _lib.SampledSubgraphStruct()
+    guess = max(state.ws_bytes, 1 << 16)
+    for _ in range(2 * int(num_hops) + 4):      # at most two shortfalls per hop (offsets, picks) + the outputs
+        ws = _workspace(guess, dev)
+        with torch.cuda.device(dev):
+            rc = lib.dglb200_sample_subgraph(
+                csr.n_rows, _ptr(csr.indptr), _ptr(csr.indices), _ptr(csr.eids), int(seeds.shape[0]), _ptr(seeds),
+                int(fanout), int(num_hops), int(seed) & 0xFFFFFFFFFFFFFFFF, _ptr(state.layer), _ptr(state.bitmap),
+                _ptr(state.word_prefix), _ptr(ws), guess, ctypes.byref(out), _stream())
+        if rc == 0:
+            break
+        if out.needed_bytes <= guess:
+            raise DGLError(_lib.last_error())
+        guess = int(out.needed_bytes)
+    else:
+        raise DGLError(_lib.last_error())
+    state.ws_bytes = max(state.ws_bytes, int(out.needed_bytes) * 5 // 4)
+    base = ws.data_ptr()
+
+    def view(ptr, count, dtype):
+        if count == 0 or not ptr:
+            return torch.empty(0, dtype=dtype, device=dev)
+        off = ptr - base
+        return ws[off:off + count * dtype.itemsize].view(dtype)
+    n, e = int(out.n_nodes), int(out.n_edges)
+    return (view(out.nodes, n, torch.int64), view(out.layers, n, torch.int64), view(out.sub_indptr, n + 1, torch.int64),
+            view(out.sub_indices, e, torch.int32), view(out.sub_rows, e, torch.int64),
+            view(out.induced_edges, e, torch.int64))
 
 
 def degrees_of(csr, rows):

@@ -3,8 +3,10 @@
 
 The reference pops one vertex at a time from a BFS queue, draws its neighbours, and looks every neighbour up
 in a hash set.  Layers of that queue are independent of the order inside a layer, so here a layer is ONE
-launch of the sampling kernel (csrc/sampling.cu: a warp per frontier vertex) and the "seen before?" test is a
-sorted-set union (dglb200_unique_sorted, kernel 4).  Outputs have the reference's shape exactly:
+launch of the sampling kernel (csrc/sampling.cu: a warp per frontier vertex) which also does the "seen before?"
+test - an atomicCAS on a per-vertex layer array instead of a hash set - and appends the next layer's frontier.
+The discovered set is kept as a bitmap; its popcount scan gives both the ascending vertex list and the
+compaction map, so no sort is needed anywhere.  Outputs have the reference's shape exactly:
 induced vertices ascending, their layer ids, the parent edge id of every subgraph edge, and the subgraph's
 CSR with compacted column ids and edge ids 0..E-1 (:875-955, CompactSubgraph :963-983).
 """
@@ -35,9 +37,14 @@ class SampledSubgraph(object):
         return self.sub_rows, self.sub_cols
 
 
-def sample_subgraph(csr, seeds, fanout, num_hops, seed=0, neighbor_type="in"):
+def sample_subgraph(csr, seeds, fanout, num_hops, seed=0, neighbor_type="in", state=None):
     """`csr`: the (row, column)-sorted CSR of the parent (DGLGraph.immutable_csr); `seeds` int64 ids on its
-    device (duplicates allowed, :787-793); `fanout` = the reference's expand_factor / num_neighbor."""
+    device (duplicates allowed, :787-793); `fanout` = the reference's expand_factor / num_neighbor.
+    `state`: an ops.SampleState of the parent to reuse across calls (one is made, and cached on the CSR,
+    otherwise).  The whole call is dglb200_sample_subgraph: per hop the offsets of the frontier's picks (one
+    sync: their number sizes the outputs) and the sampling kernel, which also discovers the next frontier; at
+    the end the discovered set is compacted out of the bitmap and the picks are placed into the subgraph's CSR
+    (one more sync: the vertex count)."""
     if int(fanout) < 0 or int(num_hops) < 0:
         raise DGLError("sample_subgraph: fanout and num_hops must be >= 0")
     dev = csr.device
@@ -45,45 +52,13 @@ def sample_subgraph(csr, seeds, fanout, num_hops, seed=0, neighbor_type="in"):
     seeds = seeds.to(dev).to(torch.int64).reshape(-1).contiguous()
     if seeds.numel() == 0:
         raise DGLError("sample_subgraph: no seed vertices")
-    if int(seeds.min()) < 0 or int(seeds.max()) >= n:
-        raise DGLError("Invalid vertex: a seed id is outside [0, %d)" % n)
-    nodes, _ = ops.unique_sorted(seeds, n, want_inverse=False)         # layer 0, ascending
-    layers = torch.zeros(nodes.shape[0], dtype=torch.int64, device=dev)
-    frontier = nodes
-    rows_l, cols_l, eids_l = [], [], []
-    for hop in range(int(num_hops)):
-        if frontier.numel() == 0:
-            break
-        _, r, c, e = ops.neighbor_sample(csr, frontier, fanout, seed, want=("row", "col", "eid"))
-        rows_l.append(r)
-        cols_l.append(c)
-        eids_l.append(e)
-        if c.numel() == 0:
-            break
-        # union of the known vertices and this layer's picks; what is new forms the next frontier
-        known = nodes.shape[0]
-        merged, inv = ops.unique_sorted(torch.cat([nodes, c]), n)
-        old_pos = inv[:known]
-        new_layers = torch.full((merged.shape[0],), hop + 1, dtype=torch.int64, device=dev)
-        new_layers[old_pos] = layers
-        is_new = torch.ones(merged.shape[0], dtype=torch.bool, device=dev)
-        is_new[old_pos] = False
-        frontier = merged[is_new]
-        nodes, layers = merged, new_layers
+    if state is None:
+        state = getattr(csr, "_sample_state", None)
+        if state is None:
+            state = csr._sample_state = ops.SampleState(n, dev)
+    nodes, layers, sub_indptr, sub_indices, sub_rows, induced = ops.sample_subgraph(csr, state, seeds, fanout,
+                                                                                    int(num_hops), seed)
     n_sub = int(nodes.shape[0])
-    if rows_l:
-        rows = torch.cat(rows_l)
-        cols = torch.cat(cols_l)
-        eids = torch.cat(eids_l)
-    else:
-        rows = cols = eids = torch.empty(0, dtype=torch.int64, device=dev)
-    # compaction (nodes is sorted and holds every id) + the subgraph's CSR: rows ascending, the picks of a
-    # row in the order the kernel emitted them (ascending slot) - a stable build keyed by the row
-    sub_r = torch.searchsorted(nodes, rows)
-    sub_c = torch.searchsorted(nodes, cols)
-    sub = ops.csr_build(sub_r, sub_c, n_sub, n_sub, order=0)
-    perm = sub.eids.long()
-    induced_edges = eids[perm]
-    sub.eids = torch.arange(sub.nnz, dtype=torch.int32, device=dev)   # :948-949
-    sub_rows = ops.csr_row_ids(sub) if sub.nnz else torch.empty(0, dtype=torch.int64, device=dev)
-    return SampledSubgraph(nodes, layers, induced_edges, sub, sub_rows, neighbor_type)
+    sub = ops.CSR(n_sub, n_sub, sub_indptr, sub_indices,
+                  torch.arange(sub_indices.shape[0], dtype=torch.int32, device=dev))     # :948-949
+    return SampledSubgraph(nodes, layers, induced, sub, sub_rows, neighbor_type)

@@ -141,22 +141,61 @@ int dglb200_degrees_of(int64_t n_sel, const int64_t* rows, int64_t n_rows, const
  * Two steps because the output size is data dependent:
  *   neighbor_sample_offsets: offsets[i] = sum of min(degree, fanout) over rows[0..i); *total_host =
  *     offsets[n_sel].  Workspace: dglb200_csr_select_workspace_bytes(n_sel).  An id outside [0, n_rows) is
- *     an error.  Syncs the stream (returns the total).
+ *     an error.  n_sel_dev (nullable): the number of live rows is on the device (a frontier appended by the
+ *     previous hop's fill); rows beyond it count 0, and *n_sel_host (nullable) receives min(n_sel, live).
+ *     Syncs the stream (returns the totals).
  *   neighbor_sample_fill: for the j-th pick (ascending slot s) of selection i, at p = offsets[i] + j:
  *     out_row[p] = rows[i], out_col[p] = indices[s], out_eid[p] = eids[s] (s when eids == NULL),
  *     out_slot[p] = s.  Every output is nullable.  Does not sync.
+ *     Discovery (layer != NULL; the hash set + queue of :783-793, 852-860 for a whole layer at once): a
+ *     picked column c with layer[c] == -1 gets layer[c] = hop + 1, its bit in `bitmap`, and is appended to
+ *     next_frontier[(*next_count)++] (order unspecified; the next hop's samples do not depend on it).
  * The draws come from a counter-based generator keyed by (seed, row id, draw, attempt): the same seed gives
  * the same sample whatever the launch geometry.  The reference seeds rand_r with time(nullptr) (:778), so
  * its samples are not reproducible and parity is pinned on what IS deterministic (degree <= fanout: whole
  * rows, golden vectors of the unmodified reference) plus the distribution (tests).
  */
-int dglb200_neighbor_sample_offsets(int64_t n_sel, const int64_t* rows, int64_t n_rows, const int64_t* indptr,
-                                    int64_t fanout, int64_t* offsets, int64_t* total_host,
-                                    void* workspace, size_t workspace_bytes, void* stream);
-int dglb200_neighbor_sample_fill(int64_t n_sel, const int64_t* rows, const int64_t* offsets,
-                                 const int64_t* indptr, const int32_t* indices, const int32_t* eids,
-                                 int64_t fanout, uint64_t seed, int64_t* out_row, int64_t* out_col,
-                                 int64_t* out_eid, int64_t* out_slot, void* stream);
+int dglb200_neighbor_sample_offsets(int64_t n_sel, const int64_t* rows, const int32_t* n_sel_dev, int64_t n_rows,
+                                    const int64_t* indptr, int64_t fanout, int64_t* offsets, int64_t* total_host,
+                                    int64_t* n_sel_host, void* workspace, size_t workspace_bytes, void* stream);
+int dglb200_neighbor_sample_fill(int64_t n_sel, const int64_t* rows, const int32_t* n_sel_dev,
+                                 const int64_t* offsets, const int64_t* indptr, const int32_t* indices,
+                                 const int32_t* eids, int64_t fanout, uint64_t seed, int64_t* out_row,
+                                 int64_t* out_col, int64_t* out_eid, int64_t* out_slot, int32_t* layer,
+                                 uint32_t* bitmap, int32_t hop, int64_t* next_frontier, int32_t* next_count,
+                                 void* stream);
+/*
+ * ImmutableGraph::NeighborUniformSample = SampleSubgraph + CompactSubgraph (:772-1008) in one call: the per-hop
+ * pair above for every layer of the BFS, then the compaction.  (indptr, indices, eids): the parent's CSR keyed
+ * by the vertex whose neighbours are sampled (the immutable graph's in-CSR for neighbor_type "in").
+ * Persistent state per parent graph, owned by the caller: layer int32[n_rows] (all -1), bitmap
+ * uint32[ceil(n_rows / 32)] (all 0), word_prefix int32[ceil(n_rows / 32) + 1] (scratch).  A call leaves layer /
+ * bitmap clean again by resetting only what it touched, so it costs O(subgraph) - apart from the bitmap's
+ * popcount scan, n_rows / 32 words.  One call at a time per state.
+ * Results are placed IN the caller's workspace (device pointers in *out_host, valid while the workspace is):
+ *   nodes[n_nodes] ascending, layers[n_nodes] (hop of first discovery; seeds = 0),
+ *   sub_indptr[n_nodes + 1], sub_indices[n_edges] (compacted neighbour), sub_rows[n_edges] (compacted row
+ *   vertex), induced_edges[n_edges] (parent edge id): the subgraph's CSR, rows ascending, the picks of a row in
+ *   ascending slot order (:919-946); its own edge ids are 0 .. n_edges-1 (:948-949).
+ * The number of picks is only known hop by hop: when the workspace is too small the call fails with
+ * out_host->needed_bytes > 0 (a size that would have carried it that far, plus slack), the state wiped; retry
+ * with a larger workspace.  On success needed_bytes = the bytes used.  Syncs the stream once per hop and once
+ * at the end (sizes come back to the host).
+ */
+typedef struct {
+  int64_t n_nodes, n_edges;
+  int64_t* nodes;
+  int64_t* layers;
+  int64_t* sub_indptr;
+  int32_t* sub_indices;
+  int64_t* sub_rows;
+  int64_t* induced_edges;
+  size_t needed_bytes;
+} dglb200_sampled_subgraph_t;
+int dglb200_sample_subgraph(int64_t n_rows, const int64_t* indptr, const int32_t* indices, const int32_t* eids,
+                            int64_t n_seeds, const int64_t* seeds, int64_t fanout, int32_t num_hops, uint64_t seed,
+                            int32_t* layer, uint32_t* bitmap, int32_t* word_prefix, void* workspace,
+                            size_t workspace_bytes, dglb200_sampled_subgraph_t* out_host, void* stream);
 
 /* ---- (1)(2) SpMM: generalised message -> reduce over a CSR -------------------------- */
 

@@ -290,6 +290,12 @@ inline float atomicAdd(float* p, float v) {
   return __uint_as_float(old);
 }
 template <typename T> inline T atomicExch(T* p, T v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
+template <typename T> inline T atomicCAS(T* p, T expect, T v) {
+  __atomic_compare_exchange_n(p, &expect, v, false, __ATOMIC_SEQ_CST, __ATOMIC_SEQ_CST);
+  return expect;    // the old value, as CUDA returns it
+}
+inline int atomicCAS(int* p, int expect, int v) { return atomicCAS<int>(p, expect, v); }
+template <typename T> inline T atomicOr(T* p, T v) { return __atomic_fetch_or(p, v, __ATOMIC_SEQ_CST); }
 inline int atomicExch(int* p, int v) { return __atomic_exchange_n(p, v, __ATOMIC_SEQ_CST); }
 template <typename T> inline T atomicMax(T* p, T v) {
   T old = __atomic_load_n(p, __ATOMIC_SEQ_CST);

@@ -270,6 +270,8 @@ def test_sampling_distribution(emu, monkeypatch, deg, fanout, branch):
 def test_sampling_reproducible_and_hubs(emu):
     t_samp.test_same_seed_same_sample_and_seeds_differ()
     t_samp.test_hubs_multigraph_and_zero_fanout()
+    t_samp.test_bad_seed_is_an_error_and_the_state_recovers()
+    t_samp.test_c_abi_too_small_workspace_reports_needed_bytes_and_wipes_the_state()
 
 
 def test_sampling_reference_sampler_test_with_features(emu):

@@ -168,6 +168,8 @@ def test_hubs_multigraph_and_zero_fanout():
         oracle.check_neighbor_subgraph(indptr, indices, eids, seeds, fanout, hops, sub.induced_nodes.cpu().numpy(),
                                        sub.layer_ids.cpu().numpy(), sub.induced_edges.cpu().numpy(),
                                        sub.sub_rows.cpu().numpy(), sub.sub_cols.cpu().numpy())
+        st = csr._sample_state                                 # reused by every call on this CSR: left clean
+        assert int((st.layer != -1).sum()) == 0 and int((st.bitmap != 0).sum()) == 0
         if fanout >= 10 ** 6:                                  # deterministic: equals the oracle's restatement
             want = oracle.neighbor_sample_subgraph(indptr, indices, eids, seeds, fanout, hops)
             assert np.array_equal(sub.induced_nodes.cpu().numpy(), want[0])
@@ -175,6 +177,68 @@ def test_hubs_multigraph_and_zero_fanout():
             assert np.array_equal(sub.induced_edges.cpu().numpy(), want[2])
             assert np.array_equal(sub.csr.indptr.cpu().numpy(), want[3])
             assert np.array_equal(sub.sub_cols.cpu().numpy(), want[4])
+
+
+def test_bad_seed_is_an_error_and_the_state_recovers():
+    from dgl_b200 import DGLError, ops, sampling
+    dev = device()
+    rng = np.random.RandomState(8)
+    n, e = 400, 6000
+    src, dst = rng.randint(0, n, e), rng.randint(0, n, e)
+    csr = ops.csr_build(torch.from_numpy(dst).to(dev), torch.from_numpy(src).to(dev), n, n, order=1)
+    indptr, indices, eids = (t.cpu().numpy().astype(np.int64) for t in (csr.indptr, csr.indices, csr.eids))
+    good = np.array([5, 9, 5, 77], dtype=np.int64)
+    for bad in ([3, n], [-1, 4]):
+        with pytest.raises(DGLError):
+            sampling.sample_subgraph(csr, torch.tensor(bad, dtype=torch.int64, device=dev), 4, 2)
+        sub = sampling.sample_subgraph(csr, torch.from_numpy(good).to(dev), 4, 2, seed=3)
+        oracle.check_neighbor_subgraph(indptr, indices, eids, good, 4, 2, sub.induced_nodes.cpu().numpy(),
+                                       sub.layer_ids.cpu().numpy(), sub.induced_edges.cpu().numpy(),
+                                       sub.sub_rows.cpu().numpy(), sub.sub_cols.cpu().numpy())
+    # the same call twice: the same subgraph (counter-based draws, order-independent discovery)
+    again = sampling.sample_subgraph(csr, torch.from_numpy(good).to(dev), 4, 2, seed=3)
+    assert torch.equal(again.induced_nodes, sub.induced_nodes) and torch.equal(again.induced_edges, sub.induced_edges)
+    assert torch.equal(again.layer_ids, sub.layer_ids) and torch.equal(again.csr.indptr, sub.csr.indptr)
+    assert torch.equal(again.csr.indices, sub.csr.indices)
+    with pytest.raises(DGLError):
+        sampling.sample_subgraph(csr, torch.empty(0, dtype=torch.int64, device=dev), 4, 2)
+
+
+def test_c_abi_too_small_workspace_reports_needed_bytes_and_wipes_the_state():
+    """dglb200_sample_subgraph straight through ctypes: a workspace that cannot hold the picks fails with
+    needed_bytes > given and leaves layer / bitmap clean; the retry with that size succeeds."""
+    import ctypes
+    from dgl_b200 import _lib, ops
+    dev = device()
+    rng = np.random.RandomState(21)
+    n, e = 2000, 60000
+    src, dst = rng.randint(0, n, e), rng.randint(0, n, e)
+    csr = ops.csr_build(torch.from_numpy(dst).to(dev), torch.from_numpy(src).to(dev), n, n, order=1)
+    st = ops.SampleState(n, dev)
+    seeds = torch.from_numpy(rng.choice(n, 200, replace=False).astype(np.int64)).to(dev)
+    lib = _lib.get_lib()
+    out = _lib.SampledSubgraphStruct()
+
+    def call(nbytes):
+        ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+        rc = lib.dglb200_sample_subgraph(n, ops._ptr(csr.indptr), ops._ptr(csr.indices), ops._ptr(csr.eids), 200,
+                                         ops._ptr(seeds), 20, 2, 11, ops._ptr(st.layer), ops._ptr(st.bitmap),
+                                         ops._ptr(st.word_prefix), ops._ptr(ws), nbytes, ctypes.byref(out),
+                                         ops._stream())
+        return rc, ws
+    given = 48 << 10                          # holds the seeds and hop 0's offsets, not its 4000 picks
+    rc, _ = call(given)
+    assert rc == -1 and out.needed_bytes > given and "too small" in _lib.last_error()
+    assert int((st.layer != -1).sum()) == 0 and int((st.bitmap != 0).sum()) == 0
+    need = int(out.needed_bytes)
+    for _ in range(8):                        # a later hop may ask for more again
+        rc, ws = call(need)
+        if rc == 0:
+            break
+        assert out.needed_bytes > need
+        need = int(out.needed_bytes)
+    assert rc == 0 and out.n_nodes > 200 and out.n_edges > 4000 and out.needed_bytes <= need
+    assert int((st.layer != -1).sum()) == 0 and int((st.bitmap != 0).sum()) == 0
 
 
 # ---- the reference's tests/compute/test_sampler.py on this package's NeighborSampler ----------------------
