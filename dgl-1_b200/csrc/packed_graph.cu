@@ -9,6 +9,9 @@
 // list ONCE through the reference's original _CAPI_DGLGraphEdges, builds the in-/out-edge CSRs with
 // kernel (4) and keeps them keyed by the handle; the mutators (AddVertices / AddEdge / AddEdges / Clear /
 // Free) are wrapped so that they drop the cached index before calling the original.
+// READ-ONLY handles (ImmutableGraph: other slot orders - immutable_graph.cc:206-237, 458-493) are passed
+// through to the reference's originals by these six; what runs on the GPU for them is the neighbour sampler
+// (packed_sampling.cuh: _CAPI_DGLGraphUniformSampling*).
 #include <mutex>
 #include <unordered_map>
 #include <vector>
@@ -229,4 +232,5 @@ bool valid_ids(const RefDLTensor* t) {  // IsValidIdArray, src/c_api_common.h:35
 }  // namespace packed
 }  // namespace dglb200
 
+#include "packed_sampling.cuh"
 #include "packed_graph_funcs.cuh"

@@ -178,8 +178,34 @@ int pf_out_degrees(RefValue* a, int* c, int n, void* ret, void*) {
 }
 
 // ---- mutators: drop the cached index, then the reference's original -----------------------------------
+// forward a call to one of libdgl's originals and hand its return value on (our reference is released)
+int forward_call(void* original, RefValue* a, int* c, int n, void* ret) {
+  RefValue r;
+  int rcode = kRefNull;
+  if (g_dgl.FuncCall(original, a, c, n, &r, &rcode) != 0) return -1;     // libdgl's message stands
+  if (rcode == kRefNull) return 0;
+  const int rc = g_dgl.CFuncSetReturn(ret, &r, &rcode, 1);
+  if (rcode == kRefFuncHandle) g_dgl.FuncFree(r.v_handle);
+  if (rcode == kRefNDArrayContainer) g_dgl.ArrayFree(static_cast<RefDLTensor*>(r.v_handle));
+  return rc;
+}
+
+// the six index queries: a read-only handle keeps the reference's own implementation
+struct Dispatch {
+  PackedCFunc mine;
+  void* original;
+};
+int pf_dispatch(RefValue* a, int* c, int n, void* ret, void* resource) {
+  Dispatch* d = static_cast<Dispatch*>(resource);
+  if (n >= 1 && call_count(g_sorig.is_readonly, as_ptr(a[0], c[0])) == 1) return forward_call(d->original, a, c, n, ret);
+  return d->mine(a, c, n, ret, nullptr);
+}
+
 int pf_forward_mutator(RefValue* a, int* c, int n, void* ret, void* original) {
-  if (n >= 1) drop_index(as_ptr(a[0], c[0]));
+  if (n >= 1) {
+    drop_index(as_ptr(a[0], c[0]));
+    drop_sample_index(as_ptr(a[0], c[0]));
+  }
   RefValue r;
   int rcode = kRefNull;
   if (g_dgl.FuncCall(original, a, c, n, &r, &rcode) != 0) return -1;     // libdgl's message stands
@@ -236,8 +262,21 @@ int register_graph_overrides() {
       {"graph_index._CAPI_DGLGraphInDegrees", pf_in_degrees},
       {"graph_index._CAPI_DGLGraphOutDegrees", pf_out_degrees},
   };
+  const int n_sampling = register_sampling_overrides();      // also resolves g_sorig.is_readonly used below
+  if (n_sampling < 0) return -1;
+  n += n_sampling;
   for (auto& t : table) {
-    if (register_one(t.name, t.fn, 1) != 0) return -1;
+    Dispatch* d = new Dispatch{t.fn, nullptr};               // lives as long as the registry entry
+    if (std::string(t.name) == "graph_index._CAPI_DGLGraphEdges") {
+      d->original = g_orig.edges;
+    } else if (keep_original(t.name, &d->original) != 0) {
+      return -1;
+    }
+    void* h = nullptr;
+    if (g_dgl.FuncCreateFromCFunc(pf_dispatch, d, nullptr, &h) != 0) return -1;
+    const int rc = g_dgl.FuncRegisterGlobal(t.name, h, 1);
+    g_dgl.FuncFree(h);
+    if (rc != 0) { set_error("cannot register %s", t.name); return -1; }
     ++n;
   }
   done = true;

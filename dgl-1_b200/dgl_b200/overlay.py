@@ -14,8 +14,11 @@ builtin message-passing path (SURVEY.md 8b "who calls it") are patched in place,
      through 1. (F.copy_to of the index to the device + F.sparse_matrix);
   4. the PackedFunc globals (`runtime.degree_bucketing._CAPI_DGLDegreeBucketing`,
      `graph_index._CAPI_DGLGraph{GetAdj,InEdges_2,OutEdges_2,Edges,InDegrees,OutDegrees}`) are overridden
-     inside the loaded libdgl.so by dglb200_register_packed_funcs (csrc/packed.cu, packed_graph.cu); the
-     reference's module attributes point INTO the registry entries, so they see the overrides at once.
+     and `graph_index._CAPI_DGLGraphUniformSampling{,2,..,128}` (the neighbour sampler) are overridden
+     inside the loaded libdgl.so by dglb200_register_packed_funcs (csrc/packed.cu, packed_graph.cu,
+     packed_sampling.cuh).  The reference's Python holds COPIES of the PackedFuncs taken at import
+     (DGLFuncGetGlobal, src/runtime/registry.cc:137-147), so install() re-fetches the overridden names into
+     the module attributes (and the sampler's dispatch table, graph_index.py:1005-1014).
 
     import dgl                      # the reference
     from dgl_b200 import overlay
@@ -160,4 +163,33 @@ def install(dgl_mod=None, register_packed=True, override_reference=True):
         if n < 0:
             raise RuntimeError("dglb200_register_packed_funcs: " + _lib.last_error())
         ov.registered = n
+        if override_reference:
+            _rebind_globals(ov, dgl_mod)
     return ov
+
+
+# global names dglb200_register_packed_funcs overrides -> the module attribute that caches each
+_OVERRIDDEN = (["runtime.degree_bucketing._CAPI_DGLDegreeBucketing"] +
+               ["graph_index._CAPI_DGLGraph" + n for n in
+                ("GetAdj", "InEdges_2", "OutEdges_2", "Edges", "InDegrees", "OutDegrees", "AddVertices", "AddEdge",
+                 "AddEdges", "Clear", "Free")] +
+               ["graph_index._CAPI_DGLGraphUniformSampling" + k for k in ("", "2", "4", "8", "16", "32", "64", "128")])
+
+
+def _rebind_globals(ov, dgl_mod):
+    """Point the reference's cached function objects at the overridden registry entries."""
+    import sys
+    get = dgl_mod._ffi.function.get_global_func
+    for full in _OVERRIDDEN:
+        modname, attr = full.rsplit(".", 1)
+        mod = sys.modules.get(dgl_mod.__name__ + "." + modname)
+        if mod is None or not hasattr(mod, attr):
+            continue
+        fresh = get(full)
+        fresh.is_global = True
+        ov._patch(mod, attr, fresh)
+    gi = dgl_mod.graph_index
+    if hasattr(gi, "_NEIGHBOR_SAMPLING_APIS"):
+        table = {k: getattr(gi, "_CAPI_DGLGraphUniformSampling" + ("" if k == 1 else str(k)))
+                 for k in gi._NEIGHBOR_SAMPLING_APIS}
+        ov._patch(gi, "_NEIGHBOR_SAMPLING_APIS", table)

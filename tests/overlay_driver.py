@@ -14,6 +14,7 @@ import contextlib
 import ctypes
 import os
 import sys
+import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 REF = "/root/reference"
@@ -26,6 +27,11 @@ for p in (ROOT, os.path.join(ROOT, "dgl-1_b200"), os.path.join(REF, "python"), o
 
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
+
+
+# the three slowest of the reference's tests on the emulated kernels (every index query builds its device index
+# on one host thread per CUDA thread): GPU tier only
+EMU_SKIP = ("test_pull_multi_fallback", "test_spmv_3d_feat", "test_v2v_update_all")
 
 
 def setup_engine(mode):
@@ -115,7 +121,7 @@ def main():
     want = cases(dgl, fn, torch.device("cpu"))               # the unmodified reference
     l0 = _lib.launch_count()
     ov = overlay.install(dgl)
-    assert ov.registered >= 17, ov.registered
+    assert ov.registered >= 25, ov.registered
     got = cases(dgl, fn, dev)
     launches = _lib.launch_count() - l0
     assert launches > 100, "the overlay launched only %d kernels" % launches
@@ -134,10 +140,23 @@ def main():
     for modname in ("test_specialization", "test_function"):
         mod = importlib.import_module(modname)
         for name in sorted(dir(mod)):
-            if name.startswith("test_"):
+            if name.startswith("test_") and not (mode == "emu" and name in EMU_SKIP):
+                t0 = time.time()
                 getattr(mod, name)()
                 ran += 1
+                if os.environ.get("OVERLAY_TIMES"):
+                    print("  %s.%s %.1fs" % (modname, name, time.time() - t0))
     print("REFERENCE_TESTS_OK %d" % ran)
+    # the reference's NeighborSampler (python/dgl/contrib/sampling/sampler.py) now draws on the engine: its own
+    # tests/compute/test_sampler.py, unchanged (emu: the cheapest of them)
+    l1 = _lib.launch_count()
+    mod = importlib.import_module("test_sampler")
+    names = ["test_10neighbor_sampler_all"] if mode == "emu" else \
+        [nm for nm in sorted(dir(mod)) if nm.startswith("test_")]
+    for name in names:
+        getattr(mod, name)()
+    assert _lib.launch_count() > l1 + 50, "the reference sampler did not reach the engine"
+    print("REFERENCE_SAMPLER_TESTS_OK %d" % len(names))
     ov.uninstall()
     assert dgl.backend.spmm.__module__.startswith("dgl.")
     print("OVERLAY_OK")

@@ -61,9 +61,52 @@ def same(a, b, what):
             assert np.array_equal(x, y), "%s: %s[%d] differs" % (what, k, i)
 
 
+def sampling_cases(n, rng):
+    """(seed arrays, neighbour type, fanout, hops): deterministic ones (fanout covers every degree) and random ones."""
+    out = []
+    for ntype in ("in", "out"):
+        for fanout, hops, k in ((10 ** 6, 2, 1), (10 ** 6, 1, 4), (4, 2, 2), (1, 3, 1), (600, 1, 1)):
+            seeds = [rng.randint(0, n, 25).astype(np.int64) for _ in range(k)]
+            seeds[0][0] = 3                  # a hub
+            out.append((seeds, ntype, fanout, hops))
+    return out
+
+
+def check_sampling(g, ro_src, ro_dst, n, cases, want):
+    """Every case through graph_index._CAPI_DGLGraphUniformSampling*: the invariants of SampleSubgraph on the
+    parent's immutable CSR; deterministic cases bit for bit against `want` (the unmodified reference's answers,
+    taken before the override; None = just the invariants)."""
+    for ci, (seeds, ntype, fanout, hops) in enumerate(cases):
+        csr = oracle.immutable_csr(ro_src, ro_dst, n, 1 if ntype == "in" else 0)
+        res = ref_ffi.graph_uniform_sampling(g, seeds, ntype, hops, fanout, want_graph=True)
+        for si, (s, (nodes, edges, layers, adj)) in enumerate(zip(seeds, res)):
+            rows = np.repeat(np.arange(len(nodes)), np.diff(adj[0]))
+            assert np.array_equal(adj[2], np.arange(len(edges)))
+            oracle.check_neighbor_subgraph(*csr, s, fanout, hops, nodes, layers, edges, rows, adj[1])
+            if want is not None and fanout >= 10 ** 6:
+                w_nodes, w_edges, w_layers, w_adj = want[ci][si]
+                assert np.array_equal(nodes, w_nodes) and np.array_equal(edges, w_edges)
+                assert np.array_equal(layers, w_layers)
+                assert all(np.array_equal(a, b) for a, b in zip(adj, w_adj))
+    return True
+
+
 def main():
     mode = sys.argv[1]
     lib = load(mode)
+    # a read-only (immutable) graph of the reference for the sampler: simple graph, hub at 3
+    rng_s = np.random.RandomState(4)
+    ro_n = 400
+    rs, rd = rng_s.randint(0, ro_n, 6000), rng_s.randint(0, ro_n - 30, 6000)
+    rd[rng_s.choice(6000, 700, replace=False)] = 3
+    key = np.unique(rs * ro_n + rd)
+    ro_src, ro_dst = (key // ro_n).astype(np.int64), (key % ro_n).astype(np.int64)
+    ro = ref_ffi.RefGraph(ro_src, ro_dst, ro_n, readonly=True, multigraph=False)
+    cases = sampling_cases(ro_n, rng_s)
+    check_sampling(ro, ro_src, ro_dst, ro_n, cases, None)                  # the unmodified reference passes
+    want_samples = [ref_ffi.graph_uniform_sampling(ro, s, t, h, f, want_graph=True) for s, t, f, h in cases]
+    ro_vids = np.array([3, 0, 17, 399], np.int64)
+    want_ro = queries(ro, ro_n, ro_vids)
     n = 300
     src, dst = random_graph(n, 4000, 7, hubs=3, hub_deg=500, zero_deg_frac=0.2)
     rng = np.random.RandomState(0)
@@ -79,7 +122,7 @@ def main():
 
     l0 = lib.dglb200_launch_count()
     k = lib.dglb200_register_packed_funcs(ctypes.c_void_p(ref_ffi.lib()._handle), 1)
-    assert k >= 17, (k, lib.dglb200_last_error())
+    assert k >= 25, (k, lib.dglb200_last_error())            # 5 + 6 queries + 5 mutators + 8 sampling + bucketing
     got, got_tiny = queries(g, n, vids), queries(tiny, 4, tv)
     assert lib.dglb200_launch_count() > l0, "the overrides launched no kernel"
     same(want, got, "300-node multigraph")
@@ -112,6 +155,23 @@ def main():
             raise AssertionError("an invalid query did not raise")
     del g, tiny            # _CAPI_DGLGraphFree (wrapped) drops the device index
     print("PACKED_GRAPH_OK")
+    # the neighbour sampler behind the reference's own global names, on the read-only graph; the six index
+    # queries pass a read-only handle through to the reference's originals (other slot orders)
+    l1 = lib.dglb200_launch_count()
+    check_sampling(ro, ro_src, ro_dst, ro_n, cases, want_samples)
+    assert lib.dglb200_launch_count() > l1 + 50, "the sampling overrides launched no kernel"
+    same(want_ro, queries(ro, ro_n, ro_vids), "read-only graph (pass-through)")
+    for bad_call in (lambda: ref_ffi.graph_uniform_sampling(ro, [np.array([ro_n + 1], np.int64)], "in", 1, 2),
+                     lambda: ref_ffi.graph_uniform_sampling(ref_ffi.RefGraph(ro_src, ro_dst, ro_n), [ro_vids], "in", 1, 2)):
+        try:
+            bad_call()
+        except ref_ffi.RefError:
+            pass
+        else:
+            raise AssertionError("an invalid sampling call did not raise")
+    check_sampling(ro, ro_src, ro_dst, ro_n, cases[:2], want_samples)       # the state survived the failed call
+    del ro
+    print("PACKED_SAMPLING_OK")
     # degree bucketing: the override against the reference's raw output taken BEFORE the override
     ours = ref_ffi.degree_bucketing(*bucket_in)
     for a, b in zip(oracle.canonicalize_bucketing(*bucket_ref), ours):

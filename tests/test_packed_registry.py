@@ -50,6 +50,7 @@ def _run_driver(mode):
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=900)
     out = p.stdout.decode("utf-8", "replace")
     assert p.returncode == 0 and "PACKED_GRAPH_OK" in out and "BUCKETING_OK" in out, out[-3000:]
+    assert "PACKED_SAMPLING_OK" in out, out[-3000:]
 
 
 @needs_ref
