@@ -727,6 +727,62 @@ def c5_n1_reference():
         return None, "unavailable"
 
 
+def sampling_record():
+    """Neighbour sampling beside the headline, N = 1 only: batches of 1000 seeds x fanout 10 x 2 hops on
+    a C2-shaped graph with 1/5 of Reddit's edges (so the reference's ImmutableGraph builds in seconds), this engine's
+    dglb200_sample_subgraph against the compiled reference's NeighborUniformSample on the host cores (1 batch per
+    call = 1 core; 16 per call = its OpenMP path), one batch checked against the oracle's invariant checker."""
+    import time
+    from dgl_b200 import ops, sampling as engine
+    from oracle import oracle, ref_ffi
+    dev = torch.device("cuda")
+    c = graphs.C2_REDDIT
+    n = c["n"]
+    src, dst = graphs.powerlaw_symmetric(n, c["e"] // 5, c["seed"], dev)
+    e = int(src.shape[0])
+    csr = ops.csr_build(dst, src, n, n, order=1)
+    gen = torch.Generator(device="cpu").manual_seed(0)
+    batches = [torch.randperm(n, generator=gen)[:1000].to(dev) for _ in range(16)]
+    fanout, hops = 10, 2
+    for i in range(5):
+        sub = engine.sample_subgraph(csr, batches[i], fanout, hops, seed=i)
+    torch.cuda.synchronize()
+    ts, edges = [], 0
+    for i in range(40):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        sub = engine.sample_subgraph(csr, batches[i % 16], fanout, hops, seed=100 + i)
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+        edges += int(sub.induced_edges.shape[0])
+    ms = sorted(ts)[len(ts) // 2]
+    rec = {"workload": "1000 seeds x fanout 10 x 2 hops, in-neighbours, C2-shaped graph n=%d e=%d" % (n, e),
+           "ms_per_batch": round(ms, 4), "edges_per_subgraph": edges // 40,
+           "sampled_edges_per_s": round(edges / 40 / ms * 1e3)}
+    small = batches[0][:50]
+    sub = engine.sample_subgraph(csr, small, fanout, hops, seed=7)
+    try:
+        rec["checked"] = bool(oracle.check_neighbor_subgraph(
+            csr.indptr.cpu().numpy(), csr.indices.cpu().numpy().astype("int64"), csr.eids.cpu().numpy().astype("int64"),
+            small.cpu().numpy(), fanout, hops, sub.induced_nodes.cpu().numpy(), sub.layer_ids.cpu().numpy(),
+            sub.induced_edges.cpu().numpy(), sub.sub_rows.cpu().numpy(), sub.sub_cols.cpu().numpy()))
+    except AssertionError as ex:
+        rec["checked"], rec["check_error"] = False, str(ex)
+    if ref_ffi.available():
+        g = ref_ffi.RefGraph(src.cpu().numpy(), dst.cpu().numpy(), n, readonly=True, multigraph=True)
+        seeds_np = [b.cpu().numpy() for b in batches]
+        for per_call in (1, 16):
+            tt = []
+            for _ in range(4):
+                t0 = time.perf_counter()
+                ref_ffi.graph_uniform_sampling(g, seeds_np[:per_call], "in", hops, fanout)
+                tt.append((time.perf_counter() - t0) / per_call)
+            rec["reference_ms_per_batch_%d_per_call" % per_call] = round(sorted(tt[1:])[1] * 1e3, 3)
+        rec["reference"] = "oracle/_ref/libdgl.so NeighborUniformSample through its C ABI, %d host cores" % (os.cpu_count() or 1)
+    return rec
+
+
 def c5_record(args, ctx, wire=None):
     """The north-star's multi-GPU configuration (C5: RMAT 50M nodes / 150M edges, F = 128) measured in
     the same invocation as the headline and reported beside it (`c5` key); `value` / `config` of the
@@ -984,6 +1040,14 @@ def run_b200(args):
             barrier()
             c5_bf16 = c5_record(args, ctx, wire="bf16")
 
+    samp = None
+    if rank == 0 and world == 1 and not args.no_sampling:
+        try:
+            samp = sampling_record()
+        except Exception as ex:  # noqa: BLE001 - an auxiliary record must not take the headline down
+            samp = {"error": str(ex)[:300]}
+        torch.cuda.empty_cache()
+
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
         cpu = cpu_reference(cfg, 2, 1, budget_s=20.0)
@@ -1007,6 +1071,7 @@ def run_b200(args):
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": keep["launches"], "clocks": keep["clocks"], "gcn_epoch": gcn,
             "checked": bool(keep["check"] and keep["check"]["ok"]), "check": keep["check"], "c5": c5, "c5_bf16_wire": c5_bf16,
+            "neighbor_sampling": samp,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -1032,6 +1097,7 @@ def main():
                          "oracle; N>1: the exchange against the all-gather path)")
     ap.add_argument("--no-fused", action="store_true", help="GCN epoch with the unfused layer (4 eager passes around the SpMM)")
     ap.add_argument("--no-c5", action="store_true", help="skip the C5 record measured beside the C2 headline")
+    ap.add_argument("--no-sampling", action="store_true", help="skip the neighbour-sampling record (N = 1)")
     ap.add_argument("--ref-budget", type=float, default=150.0,
                     help="--impl reference: seconds of timed CPU passes over the full configuration")
     ap.add_argument("--ref-sample", action="store_true", help="--impl reference on a bounded edge sample")

@@ -14,6 +14,13 @@ namespace dglb200 {
 
 constexpr int kSampleWarps = 4;          // warps (= rows in flight) per CTA
 constexpr int kSampleMaxDraw = 128;      // draws a warp holds in shared memory; more: sequential selection
+// picks per hop the whole-call entry point over-allocates for instead of waiting for the exact number (the host
+// emulation of tests/native/cuda_emu pays one host thread per CUDA thread of the capacity-sized grids: lower there)
+#ifdef DGLB200_HOST_EMU
+constexpr int64_t kSampleBoundLimit = 1 << 11;
+#else
+constexpr int64_t kSampleBoundLimit = 1 << 21;
+#endif
 
 __device__ __forceinline__ uint64_t sample_mix(uint64_t z) {      // splitmix64 finaliser
   z += 0x9E3779B97F4A7C15ull;
@@ -245,11 +252,11 @@ __device__ __forceinline__ int64_t sub_id(const uint32_t* bitmap, const int32_t*
 
 // picks of every sampled row -> edge count of its compacted vertex (rows never sampled keep 0, :919-946)
 __global__ void __launch_bounds__(256)
-place_count_kernel(int64_t n_sel, const int64_t* __restrict__ rows, const int64_t* __restrict__ offsets,
-                   const uint32_t* __restrict__ bitmap, const int32_t* __restrict__ word_prefix,
-                   int64_t* __restrict__ sub_count) {
+place_count_kernel(int64_t n_sel, const int32_t* __restrict__ n_sel_dev, const int64_t* __restrict__ rows,
+                   const int64_t* __restrict__ offsets, const uint32_t* __restrict__ bitmap,
+                   const int32_t* __restrict__ word_prefix, int64_t* __restrict__ sub_count) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n_sel) return;
+  if (i >= n_sel || (n_sel_dev != nullptr && i >= *n_sel_dev)) return;
   sub_count[sub_id(bitmap, word_prefix, rows[i])] = offsets[i + 1] - offsets[i];
 }
 
@@ -400,15 +407,17 @@ extern "C" int dglb200_sample_subgraph(int64_t n_rows, const int64_t* indptr, co
       n_seeds, seeds, n_rows, layer, bitmap, frontier0, counters, counters + n_counters - 1);
   DGLB200_POST_LAUNCH("sample_seeds_kernel");
 
-  struct Hop { int64_t n_sel, total; const int64_t *rows, *offsets, *cols, *pe; };
+  // n_sel / total: exact when the hop synchronised, else capacities (live counts: n_sel_dev, offsets[n_sel])
+  struct Hop { int64_t n_sel, total; const int32_t* n_sel_dev; const int64_t *rows, *offsets, *cols, *pe; };
   Hop hops[64];
   int n_hops = 0;
   const int64_t* frontier = frontier0;
   int64_t cap = n_seeds, total_picks = 0;
+  bool exact = true;                                           // every hop returned its sizes to the host
   const int64_t grid_cap = (int64_t)kNumSMsB200 * 16;
   for (int h = 0; h < num_hops && cap > 0; ++h) {
     TAKE(offsets, int64_t, cap + 1);
-    const size_t mark0 = ws.used;                              // lens + scan scratch is released after the hop
+    const size_t mark0 = ws.used;
     if (ws.used + align_up((size_t)(cap + 1) * 8) + scan_workspace_bytes(cap, 8) > ws.size)
       return too_small(align_up((size_t)(cap + 1) * 8) + scan_workspace_bytes(cap, 8));
     int64_t* len = ws.take<int64_t>(cap + 1);
@@ -416,21 +425,30 @@ extern "C" int dglb200_sample_subgraph(int64_t n_rows, const int64_t* indptr, co
                                                                          fanout, len, nullptr);
     DGLB200_POST_LAUNCH("sample_lens_kernel");
     if (exclusive_scan<int64_t, int64_t>(len, offsets, cap, 1, ws, stream) != 0) return -1;
-    int64_t total = 0;
-    int32_t live = 0, bad = 0;
-    DGLB200_CUDA(cudaMemcpyAsync(&total, offsets + cap, sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
-    DGLB200_CUDA(cudaMemcpyAsync(&live, counters + h, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
-    if (h == 0) DGLB200_CUDA(cudaMemcpyAsync(&bad, counters + n_counters - 1, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
-    DGLB200_CUDA(cudaStreamSynchronize(stream));
-    if (bad != 0) {
-      (void)too_small(0);
-      out->needed_bytes = 0;
-      set_error("Invalid vertex: a seed id is outside [0, %lld)", (long long)n_rows);
-      return -1;
+    // A hop's picks are at most cap * fanout.  While that bound is small the outputs are sized by it and the
+    // host does NOT wait for the exact number: the kernels read the live counts from device memory.
+    const bool bounded = fanout <= kSampleBoundLimit && cap <= kSampleBoundLimit / (fanout > 0 ? fanout : 1);
+    int64_t total = bounded ? cap * fanout : 0, n_sel = cap;
+    const int32_t* n_sel_dev = counters + h;
+    if (!bounded) {
+      int32_t live = 0, bad = 0;
+      DGLB200_CUDA(cudaMemcpyAsync(&total, offsets + cap, sizeof(int64_t), cudaMemcpyDeviceToHost, stream));
+      DGLB200_CUDA(cudaMemcpyAsync(&live, counters + h, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+      DGLB200_CUDA(cudaMemcpyAsync(&bad, counters + n_counters - 1, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
+      DGLB200_CUDA(cudaStreamSynchronize(stream));
+      if (bad != 0) {
+        (void)too_small(0);
+        out->needed_bytes = 0;
+        set_error("Invalid vertex: a seed id is outside [0, %lld)", (long long)n_rows);
+        return -1;
+      }
+      ws.used = mark0;                                         // the stream is idle: lens + scan scratch is free again
+      n_sel = live < cap ? live : cap;
+      n_sel_dev = nullptr;
+    } else {
+      exact = false;
     }
-    ws.used = mark0;
-    if (live > cap) live = (int32_t)cap;
-    hops[n_hops] = Hop{live, total, frontier, offsets, nullptr, nullptr};
+    hops[n_hops] = Hop{n_sel, total, n_sel_dev, frontier, offsets, nullptr, nullptr};
     if (total > 0) {
       if (ws.used + 3 * align_up((size_t)total * 8) > ws.size) return too_small(3 * align_up((size_t)total * 8));
       TAKE(cols, int64_t, total);
@@ -438,11 +456,11 @@ extern "C" int dglb200_sample_subgraph(int64_t n_rows, const int64_t* indptr, co
       TAKE(next, int64_t, total);
       hops[n_hops].cols = cols;
       hops[n_hops].pe = pe;
-      int64_t blocks = ceil_div(live, kSampleWarps);
+      int64_t blocks = ceil_div(n_sel, kSampleWarps);
       if (blocks > grid_cap) blocks = grid_cap;
       SampleMark mk{layer, bitmap, next, counters + h + 1, h};
       neighbor_sample_kernel<true><<<(unsigned)blocks, kSampleWarps * kWarp, 0, stream>>>(
-          live, nullptr, frontier, offsets, indptr, indices, eids, fanout, seed, nullptr, cols, pe, nullptr, mk);
+          n_sel, n_sel_dev, frontier, offsets, indptr, indices, eids, fanout, seed, nullptr, cols, pe, nullptr, mk);
       DGLB200_POST_LAUNCH("neighbor_sample_kernel");
       frontier = next;
     }
@@ -459,6 +477,13 @@ extern "C" int dglb200_sample_subgraph(int64_t n_rows, const int64_t* indptr, co
   DGLB200_POST_LAUNCH("bitmap_popc_kernel");
   if (exclusive_scan<int32_t, int32_t>(cnt, word_prefix, words, 1, ws, stream) != 0) return -1;
   int32_t n_sub32 = 0, bad = 0;
+  int64_t real_total[64];
+  for (int h = 0; h < n_hops; ++h) {                           // bounded hops: their pick counts come back only now
+    real_total[h] = hops[h].total;
+    if (hops[h].n_sel_dev != nullptr)
+      DGLB200_CUDA(cudaMemcpyAsync(&real_total[h], hops[h].offsets + hops[h].n_sel, sizeof(int64_t),
+                                   cudaMemcpyDeviceToHost, stream));
+  }
   DGLB200_CUDA(cudaMemcpyAsync(&n_sub32, word_prefix + words, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
   DGLB200_CUDA(cudaMemcpyAsync(&bad, counters + n_counters - 1, sizeof(int32_t), cudaMemcpyDeviceToHost, stream));
   DGLB200_CUDA(cudaStreamSynchronize(stream));
@@ -470,6 +495,9 @@ extern "C" int dglb200_sample_subgraph(int64_t n_rows, const int64_t* indptr, co
   }
   ws.used = mark1;
   const int64_t n_sub = n_sub32;
+  (void)exact;
+  total_picks = 0;
+  for (int h = 0; h < n_hops; ++h) total_picks += real_total[h];
   {
     const size_t e8 = align_up((size_t)(total_picks > 0 ? total_picks : 1) * 8), n8 = align_up((size_t)(n_sub + 1) * 8);
     const size_t rest = 3 * e8 + 4 * n8 + scan_workspace_bytes(n_sub + 1, 8);
@@ -490,14 +518,14 @@ extern "C" int dglb200_sample_subgraph(int64_t n_rows, const int64_t* indptr, co
   for (int h = 0; h < n_hops; ++h) {
     if (hops[h].n_sel == 0) continue;
     place_count_kernel<<<(unsigned)ceil_div(hops[h].n_sel, 256), 256, 0, stream>>>(
-        hops[h].n_sel, hops[h].rows, hops[h].offsets, bitmap, word_prefix, sub_count);
+        hops[h].n_sel, hops[h].n_sel_dev, hops[h].rows, hops[h].offsets, bitmap, word_prefix, sub_count);
     DGLB200_POST_LAUNCH("place_count_kernel");
   }
   if (exclusive_scan<int64_t, int64_t>(sub_count, sub_indptr, n_sub, 1, ws, stream) != 0) return -1;
   for (int h = 0; h < n_hops; ++h) {
-    if (hops[h].n_sel == 0 || hops[h].total == 0) continue;
-    place_picks_kernel<<<(unsigned)ceil_div(hops[h].total, 256), 256, 0, stream>>>(
-        hops[h].n_sel, hops[h].total, hops[h].rows, hops[h].offsets, hops[h].cols, hops[h].pe, bitmap, word_prefix,
+    if (hops[h].n_sel == 0 || real_total[h] == 0) continue;
+    place_picks_kernel<<<(unsigned)ceil_div(real_total[h], 256), 256, 0, stream>>>(
+        hops[h].n_sel, real_total[h], hops[h].rows, hops[h].offsets, hops[h].cols, hops[h].pe, bitmap, word_prefix,
         sub_indptr, sub_indices, sub_rows, induced);
     DGLB200_POST_LAUNCH("place_picks_kernel");
   }

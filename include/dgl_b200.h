@@ -179,8 +179,9 @@ int dglb200_neighbor_sample_fill(int64_t n_sel, const int64_t* rows, const int32
  *   ascending slot order (:919-946); its own edge ids are 0 .. n_edges-1 (:948-949).
  * The number of picks is only known hop by hop: when the workspace is too small the call fails with
  * out_host->needed_bytes > 0 (a size that would have carried it that far, plus slack), the state wiped; retry
- * with a larger workspace.  On success needed_bytes = the bytes used.  Syncs the stream once per hop and once
- * at the end (sizes come back to the host).
+ * with a larger workspace.  On success needed_bytes = the bytes used.  Syncs the stream once at the end (the
+ * sizes come back to the host), plus once per hop whose bound frontier x fanout exceeds 2^21 picks (such a hop
+ * waits for its exact pick count instead of over-allocating).
  */
 typedef struct {
   int64_t n_nodes, n_edges;
