@@ -29,10 +29,12 @@ __device__ __forceinline__ uint64_t sample_mix(uint64_t z) {      // splitmix64 
   return z ^ (z >> 31);
 }
 
-// draw number `i`, attempt `a`, of row `r`: uniform in [0, bound)
-__device__ __forceinline__ int64_t sample_draw(uint64_t seed, int64_t r, uint32_t i, uint32_t a, int64_t bound) {
-  const uint64_t h = sample_mix(sample_mix(seed ^ ((uint64_t)r * 0xD6E8FEB86659FD93ull)) + (((uint64_t)a << 32) | i));
-  return (int64_t)__umul64hi(h, (uint64_t)bound);
+// draw number `i`, attempt `a`, of row `r`: uniform in [0, bound).  row_key(seed, r) is hoisted out of the draws.
+__device__ __forceinline__ uint64_t sample_row_key(uint64_t seed, int64_t r) {
+  return sample_mix(seed ^ ((uint64_t)r * 0xD6E8FEB86659FD93ull));
+}
+__device__ __forceinline__ int64_t sample_draw(uint64_t row_key, uint32_t i, uint32_t a, int64_t bound) {
+  return (int64_t)__umul64hi(sample_mix(row_key + (((uint64_t)a << 32) | i)), (uint64_t)bound);
 }
 
 // len[i] = min(degree of rows[i], fanout); bad ids as in select_lens_kernel.
@@ -130,13 +132,45 @@ neighbor_sample_kernel(int64_t n_sel, const int32_t* __restrict__ n_sel_dev, con
     }
     const bool keep = fanout <= deg - fanout;               // draw the kept set, else the dropped one
     const int64_t m = keep ? fanout : deg - fanout;
+    const uint64_t rk = sample_row_key(seed, r);
+    if (m <= kWarp && deg < (1ll << 31)) {
+      // At most one draw per lane: everything stays in registers.  Same draws and the same redraw rule as the
+      // shared-memory path below (a draw equal to an EARLIER-numbered one is redrawn), so the picks are identical.
+      const int mi = (int)m;
+      const unsigned lt = (1u << lane) - 1u;
+      uint32_t attempt = 0;
+      int pick = lane < mi ? (int)sample_draw(rk, (uint32_t)lane, 0u, deg) : -1 - lane;   // idle lanes: unique
+      for (;;) {
+        const bool dup = (__match_any_sync(0xffffffffu, pick) & lt) != 0u;
+        if (__ballot_sync(0xffffffffu, dup) == 0u) break;
+        if (dup) pick = (int)sample_draw(rk, (uint32_t)lane, ++attempt, deg);
+      }
+      if (keep) {
+        int rank = 0;                                        // picks below mine = my place in ascending slot order
+        for (int j = 0; j < mi; ++j) rank += (__shfl_sync(0xffffffffu, pick, j) < pick) ? 1 : 0;
+        emit(lane < mi, off + rank, start + (lane < mi ? pick : 0));
+      } else {
+        for (int64_t b = 0; b < deg; b += kWarp) {
+          const int j = (int)b + lane;
+          int before = 0;                                    // dropped slots below j
+          bool dropped = false;
+          for (int t = 0; t < mi; ++t) {
+            const int v = __shfl_sync(0xffffffffu, pick, t);
+            before += (v < j) ? 1 : 0;
+            dropped |= (v == j);
+          }
+          emit(j < deg && !dropped, off + j - before, start + j);
+        }
+      }
+      continue;
+    }
     if (m > kSampleMaxDraw) {
       // selection sampling (Knuth 3.4.2 S) by one lane: slot j is kept with probability
       // (still needed) / (still to come); emits in ascending order by construction
       if (lane == 0) {
         int64_t need = fanout, p = off;
         for (int64_t j = 0; j < deg && need > 0; ++j) {
-          if (sample_draw(seed, r, (uint32_t)j, (uint32_t)(j >> 32) + 1u, deg - j) < need) {
+          if (sample_draw(rk, (uint32_t)j, (uint32_t)(j >> 32) + 1u, deg - j) < need) {
             const int64_t s = start + j, c = indices[s];
             if (out_row) out_row[p] = r;
             if (out_col) out_col[p] = c;
@@ -156,7 +190,7 @@ neighbor_sample_kernel(int64_t n_sel, const int32_t* __restrict__ n_sel_dev, con
     }
     const int mi = (int)m;
     uint32_t attempt[kSampleMaxDraw / kWarp] = {0, 0, 0, 0};
-    for (int q = lane; q < mi; q += kWarp) pick[q] = sample_draw(seed, r, (uint32_t)q, 0u, deg);
+    for (int q = lane; q < mi; q += kWarp) pick[q] = sample_draw(rk, (uint32_t)q, 0u, deg);
     for (;;) {
       __syncwarp();
       unsigned redo = 0;                                     // bit t: my t-th draw equals an earlier-numbered draw
@@ -169,7 +203,7 @@ neighbor_sample_kernel(int64_t n_sel, const int32_t* __restrict__ n_sel_dev, con
       if (__ballot_sync(0xffffffffu, redo != 0) == 0u) break;
       __syncwarp();                                          // all compares done before any rewrite
       for (int q = lane, t = 0; q < mi; q += kWarp, ++t)
-        if (redo & (1u << t)) pick[q] = sample_draw(seed, r, (uint32_t)q, ++attempt[t], deg);
+        if (redo & (1u << t)) pick[q] = sample_draw(rk, (uint32_t)q, ++attempt[t], deg);
     }
     // rank sort (all picks are distinct)
     for (int q = lane; q < mi; q += kWarp) {
