@@ -247,6 +247,17 @@ def c3_at_c2_size():
     ms = timeit(lambda: ops.edge_softmax_backward(cin, alpha, s), warm=2, iters=5)
     report("C2x8h", "edge_softmax backward H=8", ms, e * heads * 4 * 3 + e * 4, n=n, e=e)
     del s, alpha
+    # the same three kernels with edge data in CSR SLOT order (eids = NULL: what Adjacency.slot_view() hands them)
+    cslot = ops.CSR(n, n, cin.indptr, cin.indices, None)
+    ms = timeit(lambda: ops.sddmm(cslot, ops.SDDMM_ADD, a1, a2, heads, 1), warm=2, iters=5)
+    report("C2x8h", "sddmm u+v H=8 D=1, slot order", ms, e * (2 * heads * 4 + 4 + heads * 4), n=n, e=e)
+    s = ops.sddmm(cslot, ops.SDDMM_ADD, a1, a2, heads, 1)
+    ms = timeit(lambda: ops.edge_softmax(cslot, s), warm=2, iters=5)
+    report("C2x8h", "edge_softmax H=8, slot order", ms, e * heads * 4 * 2, n=n, e=e)
+    alpha = ops.edge_softmax(cslot, s)
+    ms = timeit(lambda: ops.edge_softmax_backward(cslot, alpha, s), warm=2, iters=5)
+    report("C2x8h", "edge_softmax backward H=8, slot order", ms, e * heads * 4 * 3, n=n, e=e)
+    del s, alpha
     u = ft.reshape(n, -1)
     ms = timeit(lambda: ops.sddmm(cin, ops.SDDMM_DOT, u, u, heads, hid), warm=2, iters=5)
     report("C2x8h", "sddmm u.v H=8 D=32", ms, e * (2 * heads * hid * 4 + 4 + heads * 4), n=n, e=e)
@@ -254,6 +265,33 @@ def c3_at_c2_size():
     for fl, name in ((ops.SOFTMAX_GAT_EXAMPLE, "example"), (ops.SOFTMAX_STABLE, "stable")):
         ms = timeit(lambda: ops.gat_aggregate(cin, a1, a2, ft, 0.2, flavour=fl, want_edge=False), warm=1, iters=3)
         report("C2x8h", "fused GAT aggregation (%s flavour) H=8 D=32" % name, ms, fused_bytes, n=n, e=e)
+
+
+def gat_chain():
+    """The differentiable GAT edge path (edge_ops.gat_attention: SDDMM -> leaky_relu -> edge softmax -> weighted SpMM,
+    forward + backward) at C2 size with 8 heads x 16, through the edge-id indirection and over the slot view."""
+    from dgl_b200 import autograd, edge_ops
+    c = graphs.C2_REDDIT
+    n, e, heads, hid = c["n"], c["e"], 8, 16
+    src, dst = graphs.powerlaw_symmetric(n, e, c["seed"], DEV)
+    adj = autograd.Adjacency(n, n, coo=(dst, src, None))
+    _ = adj.csr_in, adj.csr_out
+    adj.slot_view()
+    adj.drop_coo()
+    del src, dst
+    torch.cuda.empty_cache()
+    a1 = torch.randn(n, heads, device=DEV, requires_grad=True)
+    a2 = torch.randn(n, heads, device=DEV, requires_grad=True)
+    ft = torch.randn(n, heads, hid, device=DEV, requires_grad=True)
+    gout = torch.randn(n, heads, hid, device=DEV)
+    for slot in (False, True):
+        def step():
+            out, _ = edge_ops.gat_attention(adj, a1, a2, ft, 0.2, want_alpha=False, slot_order=slot)
+            out.backward(gout)
+            a1.grad = a2.grad = ft.grad = None
+        ms = timeit(step, warm=2, iters=5)
+        report("C2x8h", "gat_attention forward + backward (autograd chain), %s" % ("slot order" if slot else "edge-id order"),
+               ms, 0, n=n, e=e, heads=heads, dim=hid)
 
 
 def c5_kernel():
@@ -547,7 +585,7 @@ def graph_capture():
 
 if __name__ == "__main__":
     sections = dict(c1=c1, c3=c3, c4=c4, c4rel=c4_per_relation, c2=c2_structure, c2ref=c2_torch_sparse,
-                    c3big=c3_at_c2_size, c5=c5_kernel, cpu=cpu_layers, sampling=sampling, capture=graph_capture)
+                    c3big=c3_at_c2_size, c5=c5_kernel, cpu=cpu_layers, sampling=sampling, capture=graph_capture, gatchain=gat_chain)
     for name in (sys.argv[1:] or list(sections)):
         sections[name]()
     os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)

@@ -23,6 +23,9 @@ class Adjacency(object):
         self._in = csr_in
         self._out = csr_out
         self._coo = coo          # (dst_row, src_col, eid or None) int64 CUDA tensors
+        # edge ids are 0..nnz-1 (a whole graph built from its edge list): the precondition of slot_view()
+        self._dense_eids = coo is not None and coo[2] is None
+        self._slot = None
 
     @property
     def csr_in(self):
@@ -37,6 +40,25 @@ class Adjacency(object):
             r, c, e = self._coo
             self._out = ops.csr_build(c, r, self.n_src, self.n_dst, eid=e)
         return self._out
+
+    def slot_view(self):
+        """(Adjacency, slot_of_edge) - the same graph with its edges RENUMBERED by their slot in csr_in, or None
+        when the edge ids are not 0..nnz-1.  Edge data produced and consumed by a chain of kernels over this view
+        (SDDMM -> edge softmax -> weighted SpMM and their gradients) is then read and written sequentially by the
+        row-wise kernels instead of through the edge-id indirection (random 4 * H-byte accesses on a graph built
+        from an unsorted edge list); slot_of_edge[e] maps a result back to the caller's edge order."""
+        if not self._dense_eids:
+            return None
+        if self._slot is None:
+            cin, cout = self.csr_in, self.csr_out
+            dev = cin.device
+            slot_of_edge = torch.empty(cin.nnz, dtype=torch.int64, device=dev)
+            slot_of_edge[cin.eids.long()] = torch.arange(cin.nnz, dtype=torch.int64, device=dev)
+            vin = ops.CSR(cin.n_rows, cin.n_cols, cin.indptr, cin.indices, None)
+            vout = ops.CSR(cout.n_rows, cout.n_cols, cout.indptr, cout.indices, slot_of_edge[cout.eids.long()].int())
+            view = Adjacency(self.n_dst, self.n_src, csr_in=vin, csr_out=vout)
+            self._slot = (view, slot_of_edge)
+        return self._slot
 
     def drop_coo(self):
         _ = self.csr_in, self.csr_out

@@ -118,13 +118,16 @@ def edge_softmax(adj, score):
     return _EdgeSoftmax.apply(adj, score.reshape(shape[0], -1).float()).reshape(shape)
 
 
-def gat_attention(adj, a_src, a_dst, ft, negative_slope=0.2, want_alpha=False):
+def gat_attention(adj, a_src, a_dst, ft, negative_slope=0.2, want_alpha=None, slot_order=True):
     """GAT edge path with a softmax-normalised attention, end to end on kernels and differentiable:
     alpha = softmax_dst(leaky_relu(a_src[src] + a_dst[dst])),  out[v] = sum_e alpha_e * ft[src_e].
     a_src: (n_src, H[, 1]), a_dst: (n_dst, H[, 1]), ft: (n_src, H, D).  Returns (out (n_dst, H, D),
-    alpha (E, H) or None).  When no gradient is needed and alpha is not asked for, the whole thing is
-    ONE launch (dglb200_gat_aggregate_csr, stable flavour); otherwise SDDMM -> leaky_relu ->
-    edge softmax -> weighted SpMM, each with its gradient kernel."""
+    alpha (E, H) in edge-id order, or None).  When no gradient is needed and alpha is not asked for, the whole
+    thing is ONE launch (dglb200_gat_aggregate_csr, stable flavour); otherwise SDDMM -> leaky_relu ->
+    edge softmax -> weighted SpMM, each with its gradient kernel.  want_alpha=False skips the copy of alpha
+    back to edge-id order on that path.
+    slot_order: run the chain over Adjacency.slot_view() - scores and alpha live in CSR slot order between the
+    kernels, so none of them goes through the edge-id indirection."""
     from .autograd import aggregate
     adj = _adj(adj)
     heads, dim = int(ft.shape[1]), int(ft.shape[2])
@@ -135,8 +138,14 @@ def gat_attention(adj, a_src, a_dst, ft, negative_slope=0.2, want_alpha=False):
         out, _, _ = ops.gat_aggregate(adj.csr_in, a_src, a_dst, ft, negative_slope,
                                       flavour=ops.SOFTMAX_STABLE, want_edge=False)
         return out, None
-    score = torch.nn.functional.leaky_relu(sddmm(adj, "u_add_v", a_src, a_dst), negative_slope)
-    alpha = edge_softmax(adj, score)
-    out = aggregate(adj, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=ft.reshape(ft.shape[0], heads * dim),
+    view = adj.slot_view() if slot_order else None
+    work, slot_of_edge = view if view is not None else (adj, None)
+    score = torch.nn.functional.leaky_relu(sddmm(work, "u_add_v", a_src, a_dst), negative_slope)
+    alpha = edge_softmax(work, score)
+    out = aggregate(work, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=ft.reshape(ft.shape[0], heads * dim),
                     w=alpha, w_width=heads)
+    if want_alpha is False:
+        alpha = None
+    elif slot_of_edge is not None:
+        alpha = alpha[slot_of_edge]
     return out.reshape(-1, heads, dim), alpha

@@ -240,6 +240,7 @@ def test_edge_ops_on_emulated_kernels(emu):
         t_edge.test_sddmm_forward_and_gradients(op, (4, 8))
     t_edge.test_edge_softmax_forward_and_gradient()
     t_edge.test_gat_attention_matches_udf_formulation_with_gradients()
+    t_edge.test_gat_attention_slot_order_equals_edge_order()
 
 
 def test_static_scratch_entry_point_on_emulated_kernels(emu):

@@ -126,6 +126,40 @@ def test_gat_attention_matches_udf_formulation_with_gradients():
     close(fused, want)
 
 
+def test_gat_attention_slot_order_equals_edge_order():
+    """The chain over Adjacency.slot_view() (scores / alpha in CSR slot order between the kernels) against the chain
+    through the edge-id indirection: same output, same alpha in edge-id order, same gradients; multigraph with hubs."""
+    import dgl_b200
+    from tests.util import random_graph
+    n = 300
+    s_np, d_np = random_graph(n, 5000, 21, hubs=2, hub_deg=700, zero_deg_frac=0.1)
+    g = dgl_b200.DGLGraph()
+    g.add_nodes(n)
+    g.add_edges(torch.from_numpy(s_np), torch.from_numpy(d_np))
+    g.to(device())
+    heads, dim = 4, 8
+    res = []
+    for slot in (False, True):
+        a1, a2, ft = _leaf(n, heads, 1, seed=31), _leaf(n, heads, 1, seed=32), _leaf(n, heads, dim, seed=33)
+        out, alpha = dgl_b200.gat_attention(g, a1, a2, ft, 0.2, slot_order=slot)
+        gout = torch.randn(n, heads, dim, generator=torch.Generator().manual_seed(34)).to(device())
+        (out * gout).sum().backward()
+        res.append((out.detach(), alpha.detach(), a1.grad, a2.grad, ft.grad))
+        out2, none = dgl_b200.gat_attention(g, a1, a2, ft, 0.2, want_alpha=False, slot_order=slot)
+        assert none is None
+        close(out2.detach(), out.detach())
+    view, slot_of_edge = g.adjacency().slot_view()
+    assert view.csr_in.eids is None and torch.equal(g.adjacency().csr_in.eids.long()[slot_of_edge],
+                                                    torch.arange(len(s_np), device=device()))
+    for a, b in zip(*res):
+        close(a, b)
+    # an adjacency with explicit edge ids (an edge subset) has no slot view: the chain falls back
+    from dgl_b200.autograd import Adjacency
+    sub = Adjacency(n, n, coo=(torch.from_numpy(d_np[:50]).to(device()), torch.from_numpy(s_np[:50]).to(device()),
+                               torch.arange(50, device=device())))
+    assert sub.slot_view() is None
+
+
 def test_apply_edges_builtin_is_one_sddmm_executor():
     from dgl_b200 import function as fn
     g, src, dst = _setup(4)
