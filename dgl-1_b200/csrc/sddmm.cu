@@ -80,6 +80,142 @@ sddmm_kernel(int64_t n_rows, int64_t nnz, const int64_t* __restrict__ indptr,
   }
 }
 
+// ---- DOT, warp per run of slots ----------------------------------------------------------------------
+// The generic kernel above gives a slot to `dim / VEC` lanes and walks its heads one after the other: at 8 heads
+// x 32 that is 8 dependent (load, reduce, store) rounds per slot, 187 warp instructions per edge, and ncu shows it
+// latency-bound at 1.4 TB/s (profiles/r02_sddmm_dot_ncu_raw.csv).  Here a WARP owns kDotSlots consecutive slots and
+// a lane owns K 16-byte chunks of the WHOLE feature row (chunk c = k * 32 + lane belongs to head c / LPH, LPH =
+// dim / VEC lanes per head): the destination row stays in registers while the row lasts, the source rows of U
+// slots are loaded back to back before any is used, the heads of a slot reduce side by side (log2(LPH) shuffles
+// per register for LPH <= 32, a whole-warp reduce per head for LPH a multiple of 32), and a slot's results leave
+// as one store instruction per register.  Lane-local sums and the butterfly order are those of the generic
+// kernel: the results are bit-identical.
+constexpr int kDotSlots = 64;
+constexpr int kDotWarps = 8;
+
+// LPH: lanes per head as a compile-time power of two <= 32 (shifts and unrolled butterflies), or 0 = a multiple of
+// 32 given at run time in `lph_rt`.
+template <typename T, int VEC, int K, int U, int LPH>
+__global__ void __launch_bounds__(kDotWarps * 32)
+sddmm_dot_warp_kernel(int64_t n_rows, int64_t nnz, const int64_t* __restrict__ indptr,
+                      const int32_t* __restrict__ indices, const int32_t* __restrict__ eids,
+                      const T* __restrict__ u, const T* __restrict__ v, int64_t heads, int lph_rt,
+                      T* __restrict__ out) {
+  const int lph = LPH > 0 ? LPH : lph_rt;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (int64_t)blockIdx.x * kDotWarps + (threadIdx.x >> 5);
+  int64_t p = warp * kDotSlots;
+  if (p >= nnz) return;
+  const int64_t p_end = min(p + (int64_t)kDotSlots, nnz);
+  const int64_t feat = heads * (int64_t)lph * VEC;
+  const int chunks = (int)(heads * lph);
+  int64_t lo = 0, hi = n_rows;                       // row of the first slot: last r with indptr[r] <= p
+  while (hi - lo > 1) {
+    const int64_t mid = (lo + hi) >> 1;
+    if (indptr[mid] <= p) lo = mid; else hi = mid;
+  }
+  int64_t r = lo, r_end = indptr[r + 1];
+  float vv[K][VEC];
+  auto load_row = [&](const T* base, float (&dst)[K][VEC]) {
+#pragma unroll
+    for (int k = 0; k < K; ++k) {
+      const int c = k * 32 + lane;
+      if (c < chunks) {
+        Chunk<T, VEC>::load(base + (int64_t)c * VEC, dst[k]);
+      } else {
+#pragma unroll
+        for (int t = 0; t < VEC; ++t) dst[k][t] = 0.f;
+      }
+    }
+  };
+  load_row(v + r * feat, vv);
+  while (p < p_end) {
+    const int n = (int)min((int64_t)U, p_end - p);
+    float uu[U][K][VEC];
+#pragma unroll
+    for (int j = 0; j < U; ++j)
+      if (j < n) load_row(u + (int64_t)ld_stream_i32(indices + p + j) * feat, uu[j]);
+#pragma unroll
+    for (int j = 0; j < U; ++j) {
+      if (j >= n) break;
+      const int64_t q = p + j;
+      if (q >= r_end) {                              // next non-empty row: its destination operand
+        while (q >= r_end) { ++r; r_end = indptr[r + 1]; }
+        load_row(v + r * feat, vv);
+      }
+      const int64_t e = eids ? (int64_t)eids[q] : q;
+      if (LPH > 0) {
+        T* orow = out + e * heads;
+#pragma unroll
+        for (int k = 0; k < K; ++k) {
+          float acc = 0.f;
+#pragma unroll
+          for (int t = 0; t < VEC; ++t) acc = fmaf(uu[j][k][t], vv[k][t], acc);
+#pragma unroll
+          for (int o = LPH / 2; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+          const int c = k * 32 + lane;
+          if (c < chunks && (c & (LPH - 1)) == 0) store_one<T>(orow + c / (LPH > 0 ? LPH : 1), acc);
+        }
+      } else {
+        const int per_head = lph >> 5;               // registers of one head
+        for (int h = 0; h < (int)heads; ++h) {
+          float acc = 0.f;
+#pragma unroll
+          for (int k = 0; k < K; ++k) {
+            if (k / per_head == h) {
+#pragma unroll
+              for (int t = 0; t < VEC; ++t) acc = fmaf(uu[j][k][t], vv[k][t], acc);
+            }
+          }
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+          if (lane == 0) store_one<T>(out + e * heads + h, acc);
+        }
+      }
+    }
+    p += n;
+  }
+}
+
+// Shapes the warp kernel takes: 16-byte chunks, a head = a power of two <= 32 of them or a multiple of 32, the
+// row in at most 8 registers per lane.  Returns 0 when it launched, 1 when the generic kernel must do it.
+template <typename T, int VEC>
+int try_launch_sddmm_dot_warp(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32_t* indices,
+                              const int32_t* eids, const T* u, const T* v, int64_t heads, int64_t dim,
+                              T* out, cudaStream_t stream) {
+  if (VEC == 1 || dim % VEC != 0 || nnz == 0) return 1;
+  const int64_t lph = dim / VEC, chunks = heads * lph;
+  const bool small = lph <= 32 && (lph & (lph - 1)) == 0;
+  const bool large = lph > 32 && lph % 32 == 0;
+  if (!(small || large) || chunks > 256 || lph < 2) return 1;
+  const int k = (int)ceil_div(chunks, 32);
+  const int64_t blocks = ceil_div(ceil_div(nnz, kDotSlots), kDotWarps);
+  if (blocks >= (1ll << 31)) return 1;
+#define DGLB200_DOT_CASE(KK, UU, LL)                                                                      \
+  sddmm_dot_warp_kernel<T, VEC, KK, UU, LL><<<(unsigned)blocks, kDotWarps * 32, 0, stream>>>(              \
+      n_rows, nnz, indptr, indices, eids, u, v, heads, (int)lph, out)
+#define DGLB200_DOT_K(LL)                                                                                 \
+  do {                                                                                                    \
+    if (k == 1) DGLB200_DOT_CASE(1, 4, LL);                                                               \
+    else if (k == 2) DGLB200_DOT_CASE(2, kBudget / 2, LL);                                                \
+    else if (k <= 4) DGLB200_DOT_CASE(4, kBudget / 4, LL);                                                \
+    else DGLB200_DOT_CASE(8, 1, LL);                                                                      \
+  } while (0)
+  constexpr int kBudget = VEC == 4 ? 8 : 4;          // chunk registers in flight per lane: U * K
+  switch (small ? (int)lph : 0) {
+    case 2: DGLB200_DOT_K(2); break;
+    case 4: DGLB200_DOT_K(4); break;
+    case 8: DGLB200_DOT_K(8); break;
+    case 16: DGLB200_DOT_K(16); break;
+    case 32: DGLB200_DOT_K(32); break;
+    default: DGLB200_DOT_K(0); break;
+  }
+#undef DGLB200_DOT_K
+#undef DGLB200_DOT_CASE
+  DGLB200_POST_LAUNCH("sddmm_dot_warp_kernel");
+  return 0;
+}
+
 template <typename T, int VEC, int OP>
 int launch_sddmm_lpe(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32_t* indices,
                      const int32_t* eids, const T* u, const T* v, int64_t heads, int64_t dim,
@@ -114,6 +250,10 @@ int launch_sddmm(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   const bool vec = dim % VECFULL == 0 && (u == nullptr || al(u)) && (v == nullptr || al(v)) &&
                    (op == DGLB200_SDDMM_DOT || al(out));
+  if (op == DGLB200_SDDMM_DOT && vec && u != nullptr && v != nullptr) {
+    const int rc = try_launch_sddmm_dot_warp<T, VECFULL>(n_rows, nnz, indptr, indices, eids, u, v, heads, dim, out, stream);
+    if (rc <= 0) return rc;
+  }
 #define DGLB200_SDDMM_OP(OPC)                                                                    \
   return vec ? launch_sddmm_lpe<T, VECFULL, OPC>(n_rows, nnz, indptr, indices, eids, u, v, heads, \
                                                  dim, out, stream)                               \

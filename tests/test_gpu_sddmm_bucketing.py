@@ -16,7 +16,10 @@ def _csr(src, dst, n):
     return ops.csr_build(torch.from_numpy(dst).cuda(), torch.from_numpy(src).cuda(), n, n)
 
 
-@pytest.mark.parametrize("heads,dim", [(1, 1), (8, 1), (8, 8), (1, 256), (2, 100), (3, 5), (4, 32)])
+@pytest.mark.parametrize("heads,dim", [(1, 1), (8, 1), (8, 8), (1, 256), (2, 100), (3, 5), (4, 32),
+                                       # shapes of the warp-per-slot-run DOT kernel: a head = 2..32 chunks, idle lanes,
+                                       # whole-warp heads (dim 256 / 512), 8 chunk registers per lane, and its fallbacks
+                                       (2, 128), (3, 8), (1, 512), (8, 128), (16, 64), (5, 24), (2, 1024)])
 @pytest.mark.parametrize("op", ["dot", "add", "mul"])
 def test_sddmm(heads, dim, op):
     from dgl_b200 import ops
@@ -30,6 +33,23 @@ def test_sddmm(heads, dim, op):
     got = ops.sddmm(_csr(src, dst, n), code, torch.from_numpy(u).cuda().reshape(n, -1),
                     torch.from_numpy(v).cuda().reshape(n, -1), heads, dim)
     np.testing.assert_allclose(got.cpu().numpy(), want, rtol=1e-5, atol=1e-5 * np.abs(want).max())
+
+
+@pytest.mark.parametrize("heads,dim", [(8, 32), (2, 8), (1, 256), (3, 40)])
+def test_sddmm_dot_bf16(heads, dim):
+    """bf16 storage, fp32 accumulation (8-element chunks in the warp kernel; (3, 40) takes the generic one): against
+    the oracle on the bf16-rounded operands, 1e-2 bar of the north-star for the stored result."""
+    from dgl_b200 import ops
+    n = 200
+    src, dst = random_graph(n, 2500, heads + dim, hubs=1, hub_deg=300, zero_deg_frac=0.1)
+    rng = np.random.RandomState(heads)
+    u = torch.from_numpy(rng.randn(n, heads * dim).astype(np.float32)).cuda().bfloat16()
+    v = torch.from_numpy(rng.randn(n, heads * dim).astype(np.float32)).cuda().bfloat16()
+    got = ops.sddmm(_csr(src, dst, n), ops.SDDMM_DOT, u, v, heads, dim)
+    assert got.dtype == torch.bfloat16
+    want = oracle.sddmm(src, dst, u.float().cpu().numpy().reshape(n, heads, dim),
+                        v.float().cpu().numpy().reshape(n, heads, dim), "dot").reshape(len(src), -1)
+    np.testing.assert_allclose(got.float().cpu().numpy(), want, rtol=1e-2, atol=1e-2 * np.abs(want).max())
 
 
 @pytest.mark.parametrize("heads", [1, 3, 8])
