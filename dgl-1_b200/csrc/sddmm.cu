@@ -12,6 +12,13 @@ namespace dglb200 {
 constexpr int kSddmmThreads = 256;
 constexpr int kSlotsPerGroup = 8;
 
+// dglb200_set_tuning("sddmm_dot_generic", 1): keep DOT on the generic slot-group kernel (tests compare the two)
+static int& sddmm_dot_generic() {
+  static int v = 0;
+  return v;
+}
+void set_sddmm_dot_generic(int v) { sddmm_dot_generic() = v; }
+
 template <typename T>
 __device__ __forceinline__ void store_one(T* p, float v);
 template <>
@@ -129,8 +136,8 @@ sddmm_dot_warp_kernel(int64_t n_rows, int64_t nnz, const int64_t* __restrict__ i
     }
   };
   load_row(v + r * feat, vv);
-  while (p < p_end) {
-    const int n = (int)min((int64_t)U, p_end - p);
+  // `n` slots starting at p; called with the literal U for full batches so that the guards fold away
+  auto batch = [&](const int n) {
     float uu[U][K][VEC];
 #pragma unroll
     for (int j = 0; j < U; ++j)
@@ -174,7 +181,9 @@ sddmm_dot_warp_kernel(int64_t n_rows, int64_t nnz, const int64_t* __restrict__ i
       }
     }
     p += n;
-  }
+  };
+  while (p + U <= p_end) batch(U);
+  if (p < p_end) batch((int)(p_end - p));
 }
 
 // Shapes the warp kernel takes: 16-byte chunks, a head = a power of two <= 32 of them or a multiple of 32, the
@@ -250,7 +259,7 @@ int launch_sddmm(int64_t n_rows, int64_t nnz, const int64_t* indptr, const int32
   auto al = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
   const bool vec = dim % VECFULL == 0 && (u == nullptr || al(u)) && (v == nullptr || al(v)) &&
                    (op == DGLB200_SDDMM_DOT || al(out));
-  if (op == DGLB200_SDDMM_DOT && vec && u != nullptr && v != nullptr) {
+  if (op == DGLB200_SDDMM_DOT && vec && u != nullptr && v != nullptr && !sddmm_dot_generic()) {
     const int rc = try_launch_sddmm_dot_warp<T, VECFULL>(n_rows, nnz, indptr, indices, eids, u, v, heads, dim, out, stream);
     if (rc <= 0) return rc;
   }

@@ -68,7 +68,8 @@ int dglb200_device_cc(void);
  * docs/source/env_var.rst).  Keys: "spmm_ucap" (edges per pipeline stage: 1,2,4,8),
  * "spmm_slab_chunks" (16-byte chunks of a feature row per pass: 16,32,64), "spmm_threads"
  * (CTA size: 128,256,512); value 0 restores the automatic choice.  Only the fp32 vectorised
- * copy_src->sum kernel honours them.  Results never depend on the knobs.
+ * copy_src->sum kernel honours them.  "sddmm_dot_generic" = 1 keeps the SDDMM DOT on its generic slot-group
+ * kernel.  Results never depend on the knobs.
  */
 int dglb200_set_tuning(const char* key, int64_t value);
 

@@ -35,6 +35,29 @@ def test_sddmm(heads, dim, op):
     np.testing.assert_allclose(got.cpu().numpy(), want, rtol=1e-5, atol=1e-5 * np.abs(want).max())
 
 
+@pytest.mark.parametrize("heads,dim", [(8, 32), (2, 8), (1, 256), (3, 8), (8, 128), (1, 512)])
+@pytest.mark.parametrize("dtype", ["f32", "bf16"])
+def test_sddmm_dot_warp_kernel_equals_generic_bitwise(heads, dim, dtype):
+    """The warp-per-slot-run DOT keeps the generic kernel's lane-local sums and butterfly order: same bits."""
+    from dgl_b200 import _lib, ops
+    n = 220
+    src, dst = random_graph(n, 3000, heads * 7 + dim, hubs=2, hub_deg=400, zero_deg_frac=0.2)
+    rng = np.random.RandomState(dim)
+    u = torch.from_numpy(rng.randn(n, heads * dim).astype(np.float32)).cuda()
+    v = torch.from_numpy(rng.randn(n, heads * dim).astype(np.float32)).cuda()
+    if dtype == "bf16":
+        u, v = u.bfloat16(), v.bfloat16()
+    csr = _csr(src, dst, n)
+    lib = _lib.get_lib()
+    fast = ops.sddmm(csr, ops.SDDMM_DOT, u, v, heads, dim)
+    try:
+        _lib.check_call(lib.dglb200_set_tuning(b"sddmm_dot_generic", 1))
+        slow = ops.sddmm(csr, ops.SDDMM_DOT, u, v, heads, dim)
+    finally:
+        _lib.check_call(lib.dglb200_set_tuning(b"sddmm_dot_generic", 0))
+    assert torch.equal(fast, slow)
+
+
 @pytest.mark.parametrize("heads,dim", [(8, 32), (2, 8), (1, 256), (3, 40)])
 def test_sddmm_dot_bf16(heads, dim):
     """bf16 storage, fp32 accumulation (8-element chunks in the warp kernel; (3, 40) takes the generic one): against

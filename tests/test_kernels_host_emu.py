@@ -194,6 +194,12 @@ def test_sddmm_kernel(emu, heads, dim, op):
     t_sddmm.test_sddmm(heads, dim, op)
 
 
+def test_sddmm_dot_warp_kernel_equals_generic(emu):
+    t_sddmm.test_sddmm_dot_warp_kernel_equals_generic_bitwise(8, 32, "f32")
+    t_sddmm.test_sddmm_dot_warp_kernel_equals_generic_bitwise(1, 256, "bf16")
+    t_sddmm.test_sddmm_dot_warp_kernel_equals_generic_bitwise(3, 8, "f32")
+
+
 def test_edge_softmax_and_gat_kernels(emu):
     t_sddmm.test_edge_softmax_fwd_bwd(3)
     t_sddmm.test_gat_aggregate(2, 5, "example")
