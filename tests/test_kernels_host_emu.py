@@ -189,7 +189,7 @@ def test_gather_kernels(emu):
 # ---- kernel (3): SDDMM, edge softmax, fused GAT; kernel (4b): bucketing, unique ------------------
 
 @pytest.mark.parametrize("heads,dim,op", [(8, 1, "add"), (8, 8, "dot"), (3, 5, "mul"), (4, 32, "dot"), (1, 256, "add"),
-                                          (1, 256, "dot"), (3, 8, "dot"), (8, 128, "dot")])
+                                          (3, 8, "dot")])
 def test_sddmm_kernel(emu, heads, dim, op):
     t_sddmm.test_sddmm(heads, dim, op)
 
