@@ -325,6 +325,49 @@ class ClockSampler(object):
 # B200 arm
 # ---------------------------------------------------------------------------------------------
 
+class numa_local(object):
+    """Allocate the pinned host buffers of the e2e legs on the NUMA node of the GPU: while inside, the process runs
+    on the GPU's own CPUs (NVML's affinity mask), so first-touch places the pages next to the PCIe root the GPU hangs
+    off; the previous affinity comes back afterwards (the CPU baselines keep all cores).  The pool's boxes are
+    16-vCPU guests that expose ONE affinity domain, so there it changes nothing ("single affinity domain") - the
+    host<->device rate still differs between boxes (e2e 13.9 - 14.1 ms per C2 step on most, 32.4 ms on one, same
+    code and clocks: placement below the guest, out of reach).  Best effort; `.note` says what was done."""
+
+    def __init__(self, dev):
+        self.dev, self.old, self.note = dev, None, "default placement"
+
+    def __enter__(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            idx = self.dev.index if self.dev.index is not None else torch.cuda.current_device()
+            props = torch.cuda.get_device_properties(idx)
+            h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + str(props.uuid)).encode()) if hasattr(props, "uuid") \
+                else pynvml.nvmlDeviceGetHandleByIndex(idx)
+            words = (os.cpu_count() + 63) // 64
+            mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+            cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (int(m) >> b) & 1}
+            allowed = os.sched_getaffinity(0)
+            cpus &= allowed
+            if cpus and cpus != allowed:
+                self.old = allowed
+                os.sched_setaffinity(0, cpus)
+                self.note = "numa-local to the GPU (%d of %d cpus during allocation)" % (len(cpus), len(allowed))
+            elif cpus:
+                self.note = "single affinity domain (%d cpus)" % len(cpus)
+        except Exception as ex:  # noqa: BLE001
+            self.note = "default placement (%s)" % str(ex)[:80]
+        return self
+
+    def __exit__(self, *exc):
+        if self.old is not None:
+            try:
+                os.sched_setaffinity(0, self.old)
+            except Exception:  # noqa: BLE001
+                pass
+        return False
+
+
 def e2e_partitioned(part, x_loc, dy_loc, y_loc, dx_loc, alg_step, barrier, dev, world, args):
     """N > 1 end-to-end: every rank's row blocks of X and dY start in HOST (pinned) memory and its
     blocks of Y and dX end there, every step, through the partition's public calls
@@ -335,10 +378,11 @@ def e2e_partitioned(part, x_loc, dy_loc, y_loc, dx_loc, alg_step, barrier, dev, 
     overwritten while a peer still reads it.  Timed with CUDA events, max over ranks."""
     import torch.distributed as dist
     rows, feat = x_loc.shape
-    xh = torch.randn(rows, feat).pin_memory()
-    dyh = torch.randn(rows, feat).pin_memory()
-    yh = torch.empty(rows, feat).pin_memory()
-    dxh = torch.empty(rows, feat).pin_memory()
+    with numa_local(dev) as placement:
+        xh = torch.randn(rows, feat).pin_memory()
+        dyh = torch.randn(rows, feat).pin_memory()
+        yh = torch.empty(rows, feat).pin_memory()
+        dxh = torch.empty(rows, feat).pin_memory()
     s_in, s_out = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
     cur = torch.cuda.current_stream(dev)
     stage = [(torch.empty_like(x_loc), torch.empty_like(dy_loc), torch.empty_like(y_loc), torch.empty_like(dx_loc))
@@ -395,7 +439,8 @@ def e2e_partitioned(part, x_loc, dy_loc, y_loc, dx_loc, alg_step, barrier, dev, 
     dist.all_reduce(nbytes)                                   # whole job, all ranks
     return {"value": alg_step / (ms * 1e-3) / 1e9, "unit": UNIT,
             "h2d_bytes_per_step": int(nbytes.item()), "d2h_bytes_per_step": int(nbytes.item()),
-            "ms_per_step": ms, "steps": k, "method": "3-stream pipeline, 2 steps in flight (same as N=1)"}
+            "ms_per_step": ms, "steps": k, "method": "3-stream pipeline, 2 steps in flight (same as N=1)",
+            "host_buffers": placement.note}
 
 
 # ---------------------------------------------------------------------------------------------
@@ -905,10 +950,11 @@ def run_b200(args):
         part.release()
         torch.cuda.empty_cache()
         from dgl_b200 import function as fn
-        xh = torch.randn(n, feat).pin_memory()
-        dyh = torch.randn(n, feat).pin_memory()
-        yh = torch.empty(n, feat).pin_memory()
-        dxh = torch.empty(n, feat).pin_memory()
+        with numa_local(dev) as placement:
+            xh = torch.randn(n, feat).pin_memory()
+            dyh = torch.randn(n, feat).pin_memory()
+            yh = torch.empty(n, feat).pin_memory()
+            dxh = torch.empty(n, feat).pin_memory()
         g.set_csr(loc_in, loc_out)
 
         # Host buffers in, host buffers out, every step; copies ride two side streams (PCIe is full
@@ -966,7 +1012,8 @@ def run_b200(args):
         t_e2e = (time.perf_counter() - t0) / k
         e2e = {"value": alg_step / t_e2e / 1e9, "unit": UNIT,
                "h2d_bytes_per_step": 2 * n * feat * 4, "d2h_bytes_per_step": 2 * n * feat * 4,
-               "ms_per_step": t_e2e * 1e3, "steps": k, "method": "3-stream pipeline, 2 steps in flight"}
+               "ms_per_step": t_e2e * 1e3, "steps": k, "method": "3-stream pipeline, 2 steps in flight",
+               "host_buffers": placement.note}
         del xh, dyh, yh, dxh
 
     # ---- GCN epoch (second half of BASELINE.json's metric) ------------------------------------
