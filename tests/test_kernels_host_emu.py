@@ -275,7 +275,9 @@ def test_sampling_distribution(emu, monkeypatch, deg, fanout, branch):
     t_samp.test_every_slot_and_every_pair_equally_likely(deg, fanout, branch)
 
 
-def test_sampling_reproducible_and_hubs(emu):
+def test_sampling_reproducible_and_hubs(emu, monkeypatch):
+    monkeypatch.setattr(t_samp, "HUB_GRAPH", dict(n=700, e=7000, hub_deg=500, fanouts=(
+        (10, 2), (100, 1), (450, 1), (1, 3), (0, 2), (5, 0), (10 ** 6, 2))))
     t_samp.test_same_seed_same_sample_and_seeds_differ()
     t_samp.test_hubs_multigraph_and_zero_fanout()
     t_samp.test_bad_seed_is_an_error_and_the_state_recovers()

@@ -20,9 +20,9 @@ def _run(mode):
     p = subprocess.run([sys.executable, os.path.join(ROOT, "tests", "overlay_driver.py"), mode],
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, timeout=1200)
     out = p.stdout.decode("utf-8", "replace")
-    ran = 11 if mode == "emu" else 14            # overlay_driver.EMU_SKIP: the three slowest are GPU-tier only
+    ran = 14
     assert p.returncode == 0 and "OVERLAY_OK" in out and "REFERENCE_TESTS_OK %d" % ran in out, out[-4000:]
-    assert "OVERLAY_CASES_OK 48 cases" in out and "REFERENCE_SAMPLER_TESTS_OK" in out
+    assert "OVERLAY_CASES_OK 48 cases" in out and "REFERENCE_SAMPLER_TESTS_OK 5" in out
 
 
 @pytest.mark.skipif(not HAVE_REF, reason="needs /root/reference/python and oracle/_ref/libdgl.so (build container)")

@@ -148,13 +148,17 @@ def test_same_seed_same_sample_and_seeds_differ():
         ops.neighbor_sample(csr, torch.tensor([0, n], dtype=torch.int64, device=dev), 3, seed=0)
 
 
+HUB_GRAPH = dict(n=3000, e=40000, hub_deg=2500, fanouts=((10, 2), (200, 2), (2400, 1), (1, 3), (0, 2), (5, 0),
+                                                         (10 ** 6, 2)))     # the host emulation shrinks it
+
+
 def test_hubs_multigraph_and_zero_fanout():
     """Parallel edges, hub rows on every branch, empty rows, fanout 0, hops 0: invariants of the reference."""
     from dgl_b200 import ops, sampling
     from tests.util import random_graph
     dev = device()
-    n = 3000
-    src, dst = random_graph(n, 40000, 77, hubs=3, hub_deg=2500, zero_deg_frac=0.2)
+    n = HUB_GRAPH["n"]
+    src, dst = random_graph(n, HUB_GRAPH["e"], 77, hubs=3, hub_deg=HUB_GRAPH["hub_deg"], zero_deg_frac=0.2)
     src = np.concatenate([src, src[:500]])                    # parallel edges
     dst = np.concatenate([dst, dst[:500]])
     csr = ops.csr_build(torch.from_numpy(dst).to(dev), torch.from_numpy(src).to(dev), n, n, order=1)
@@ -162,7 +166,7 @@ def test_hubs_multigraph_and_zero_fanout():
         csr.eids.cpu().numpy().astype(np.int64)
     rng = np.random.RandomState(1)
     hub = int(np.argmax(np.diff(indptr)))
-    for fanout, hops in ((10, 2), (200, 2), (2400, 1), (1, 3), (0, 2), (5, 0), (10 ** 6, 2)):
+    for fanout, hops in HUB_GRAPH["fanouts"]:
         seeds = np.concatenate([rng.randint(0, n, 20), [hub]]).astype(np.int64)
         sub = sampling.sample_subgraph(csr, torch.from_numpy(seeds).to(dev), fanout, hops, seed=fanout + hops)
         oracle.check_neighbor_subgraph(indptr, indices, eids, seeds, fanout, hops, sub.induced_nodes.cpu().numpy(),
