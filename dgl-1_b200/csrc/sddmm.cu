@@ -12,6 +12,13 @@ namespace dglb200 {
 constexpr int kSddmmThreads = 256;
 constexpr int kSlotsPerGroup = 8;
 
+// dglb200_set_tuning("gat_head_slab", k): heads per pass of the fused GAT kernel (0 = one pass, the default)
+static int& gat_head_slab() {
+  static int v = 0;
+  return v;
+}
+void set_gat_head_slab(int v) { gat_head_slab() = v; }
+
 // dglb200_set_tuning("sddmm_dot_generic", 1): keep DOT on the generic slot-group kernel (tests compare the two)
 static int& sddmm_dot_generic() {
   static int v = 0;
@@ -530,9 +537,12 @@ __global__ void __launch_bounds__(128)
 gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
                      const int32_t* __restrict__ indices, const int32_t* __restrict__ eids,
                      const float* __restrict__ a_src, const float* __restrict__ a_dst,
-                     const float* __restrict__ ft, int64_t heads, int64_t dim, float slope,
+                     const float* __restrict__ ft, int64_t heads, int64_t dim, int64_t ld_h, float slope,
                      int flavour, float* __restrict__ out, float* __restrict__ a_out,
                      float* __restrict__ z_out) {
+  // `heads` = the heads of THIS pass (a head slab; the pointers are already shifted to its first head), ld_h = heads
+  // of the whole operands: rows of ft / out are ld_h * dim apart, rows of a_src / a_dst / z / a_out ld_h apart.
+  const int64_t ld_f = ld_h * dim;
   constexpr int RPW = 32 / G;
   const int lane = threadIdx.x & 31;
   const int gl = lane % G, grp = lane / G;
@@ -551,7 +561,7 @@ gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
     foff[t] = (int64_t)(t * G + gl) * VEC;
     fvalid[t] = rvalid && foff[t] < feat;
     head[t] = fvalid[t] ? foff[t] / dim : 0;
-    adst[t] = fvalid[t] ? a_dst[row * heads + head[t]] : 0.f;
+    adst[t] = fvalid[t] ? a_dst[row * ld_h + head[t]] : 0.f;
     mx[t] = 0.f;
     z[t] = 0.f;
 #pragma unroll
@@ -575,7 +585,7 @@ gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
         for (int u = 0; u < 4; ++u)
 #pragma unroll
           for (int t = 0; t < TILES; ++t)
-            if (s4[u] >= 0 && fvalid[t]) mx[t] = fmaxf(mx[t], gat_score(a_src[s4[u] * heads + head[t]], adst[t], slope));
+            if (s4[u] >= 0 && fvalid[t]) mx[t] = fmaxf(mx[t], gat_score(a_src[s4[u] * ld_h + head[t]], adst[t], slope));
       }
     }
     for (int o = (int)(split ? lph >> 1 : 0); o > 0; o >>= 1) {
@@ -590,7 +600,7 @@ gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
       for (int u = 0; u < 4; ++u)
 #pragma unroll
         for (int t = 0; t < TILES; ++t)
-          if (s4[u] >= 0 && fvalid[t]) mx[t] = fmaxf(mx[t], gat_score(a_src[s4[u] * heads + head[t]], adst[t], slope));
+          if (s4[u] >= 0 && fvalid[t]) mx[t] = fmaxf(mx[t], gat_score(a_src[s4[u] * ld_h + head[t]], adst[t], slope));
     }
   }
   // Main pass, U edges per step: all U column ids, then all U x TILES score + feature loads are issued
@@ -614,8 +624,8 @@ gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
 #pragma unroll
         for (int v = 0; v < VEC; ++v) xv[u][t][v] = 0.f;
         if (u < n && fvalid[t]) {
-          as[u][t] = a_src[sidx[u] * heads + head[t]];
-          Chunk<float, VEC>::load(ft + sidx[u] * feat + foff[t], xv[u][t]);
+          as[u][t] = a_src[sidx[u] * ld_h + head[t]];
+          Chunk<float, VEC>::load(ft + sidx[u] * ld_f + foff[t], xv[u][t]);
         }
       }
 #pragma unroll
@@ -645,8 +655,8 @@ gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
     float o[VEC];
 #pragma unroll
     for (int v = 0; v < VEC; ++v) o[v] = (end > start) ? acc[t][v] / z[t] : 0.f;
-    Chunk<float, VEC>::store(out + row * feat + foff[t], o);
-    if (z_out != nullptr && foff[t] % dim == 0) z_out[row * heads + head[t]] = z[t];
+    Chunk<float, VEC>::store(out + row * ld_f + foff[t], o);
+    if (z_out != nullptr && foff[t] % dim == 0) z_out[row * ld_h + head[t]] = z[t];
   }
   if (a_out != nullptr) {
     for (int64_t p = start; p < end; ++p) {
@@ -655,8 +665,8 @@ gat_aggregate_kernel(int64_t n_rows, const int64_t* __restrict__ indptr,
 #pragma unroll
       for (int t = 0; t < TILES; ++t) {
         if (!fvalid[t] || foff[t] % dim != 0) continue;  // one writer per head
-        const float sc = gat_score(a_src[s * heads + head[t]], adst[t], slope);
-        a_out[e * heads + head[t]] = (flavour == DGLB200_SOFTMAX_STABLE)
+        const float sc = gat_score(a_src[s * ld_h + head[t]], adst[t], slope);
+        a_out[e * ld_h + head[t]] = (flavour == DGLB200_SOFTMAX_STABLE)
                                          ? expf(sc - mx[t]) / z[t]
                                          : fminf(fmaxf(expf(sc), -10.f), 10.f);
       }
@@ -669,25 +679,40 @@ int launch_gat(int64_t n_rows, const int64_t* indptr, const int32_t* indices, co
                const float* a_src, const float* a_dst, const float* ft, int64_t heads, int64_t dim,
                float slope, int flavour, float* out, float* a_out, float* z_out,
                cudaStream_t stream) {
-  const int64_t chunks = ceil_div(heads * dim, VEC);
-  DGLB200_REQUIRE(chunks <= 128, "gat_aggregate: heads*dim = %lld too wide for the fused kernel "
-                  "(max %d); use sddmm + edge_softmax + spmm", (long long)(heads * dim), 128 * VEC);
+  // Head slabs (dglb200_set_tuning("gat_head_slab", k)): a pass per slab of k heads keeps the rows it gathers
+  // L2-resident, like the feature slabs of kernel (1); heads are independent (their own score, z and output columns),
+  // so the passes write disjoint columns and the results are bit-identical.  OFF by default: at C2 size, 8 heads x 32
+  // (239 MB operand), 4 passes of 2 heads took 38.8 ms against 22.7 ms for one pass - unlike the SpMM, every pass
+  // re-does the per-edge work (column id, score, exp), and that, not the gather, is what the kernel is bound by.
+  int64_t slab = heads;
+  if (gat_head_slab() > 0) slab = gat_head_slab();
+  if (slab < 1) slab = 1;
+  if (slab > heads) slab = heads;
+  if (VEC > 1 && (slab * dim) % VEC != 0) slab = heads;
+  for (int64_t h0 = 0; h0 < heads; h0 += slab) {
+    const int64_t hs = h0 + slab < heads ? slab : heads - h0;
+    const int64_t chunks = ceil_div(hs * dim, VEC);
+    DGLB200_REQUIRE(chunks <= 128, "gat_aggregate: heads*dim = %lld too wide for the fused kernel "
+                    "(max %d); use sddmm + edge_softmax + spmm", (long long)(hs * dim), 128 * VEC);
 #define DGLB200_GAT(G_, TL)                                                                      \
   {                                                                                              \
     const int64_t rows_per_block = 4 * (32 / G_);                                                \
     gat_aggregate_kernel<VEC, G_, TL><<<(unsigned)ceil_div(n_rows, rows_per_block), 128, 0,      \
-                                        stream>>>(n_rows, indptr, indices, eids, a_src, a_dst,   \
-                                                  ft, heads, dim, slope, flavour, out, a_out,    \
-                                                  z_out);                                        \
+                                        stream>>>(n_rows, indptr, indices, eids, a_src + h0,     \
+                                                  a_dst + h0, ft + h0 * dim, hs, dim, heads,     \
+                                                  slope, flavour, out + h0 * dim,                \
+                                                  a_out ? a_out + h0 : nullptr,                  \
+                                                  z_out ? z_out + h0 : nullptr);                 \
   }
-  if (chunks <= 4) DGLB200_GAT(4, 1)
-  else if (chunks <= 8) DGLB200_GAT(8, 1)
-  else if (chunks <= 16) DGLB200_GAT(16, 1)
-  else if (chunks <= 32) DGLB200_GAT(32, 1)
-  else if (chunks <= 64) DGLB200_GAT(32, 2)
-  else DGLB200_GAT(32, 4)
+    if (chunks <= 4) DGLB200_GAT(4, 1)
+    else if (chunks <= 8) DGLB200_GAT(8, 1)
+    else if (chunks <= 16) DGLB200_GAT(16, 1)
+    else if (chunks <= 32) DGLB200_GAT(32, 1)
+    else if (chunks <= 64) DGLB200_GAT(32, 2)
+    else DGLB200_GAT(32, 4)
 #undef DGLB200_GAT
-  DGLB200_POST_LAUNCH("gat_aggregate_kernel");
+    DGLB200_POST_LAUNCH("gat_aggregate_kernel");
+  }
   return 0;
 }
 

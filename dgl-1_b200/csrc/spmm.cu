@@ -112,6 +112,7 @@ edge_data_to_slots_kernel(int64_t nnz, const int32_t* __restrict__ eids, int64_t
 
 void set_peer_push_tma(int v);   // peer.cu
 void set_sddmm_dot_generic(int v);  // sddmm.cu
+void set_gat_head_slab(int v);      // sddmm.cu
 
 SpmmTuning& spmm_tuning() {
   static SpmmTuning t;
@@ -289,6 +290,7 @@ int dglb200_set_tuning(const char* key, int64_t value) {
   else if (k == "spmm_rows_per_group") t.rows_per_group = (int)value;
   else if (k == "peer_push_tma") set_peer_push_tma((int)value);
   else if (k == "sddmm_dot_generic") set_sddmm_dot_generic((int)value);
+  else if (k == "gat_head_slab") set_gat_head_slab((int)value);
   else {
     set_error("set_tuning: unknown key '%s'", key);
     return -1;

@@ -69,7 +69,8 @@ int dglb200_device_cc(void);
  * "spmm_slab_chunks" (16-byte chunks of a feature row per pass: 16,32,64), "spmm_threads"
  * (CTA size: 128,256,512); value 0 restores the automatic choice.  Only the fp32 vectorised
  * copy_src->sum kernel honours them.  "sddmm_dot_generic" = 1 keeps the SDDMM DOT on its generic slot-group
- * kernel.  Results never depend on the knobs.
+ * kernel; "gat_head_slab" = heads per pass of the fused GAT kernel (0 = one pass; slabs measured slower,
+ * see csrc/sddmm.cu).  Results never depend on the knobs.
  */
 int dglb200_set_tuning(const char* key, int64_t value);
 

@@ -128,6 +128,38 @@ def test_gat_aggregate(heads, dim, flavour):
     np.testing.assert_allclose(out.cpu().numpy(), w_out, rtol=1e-4, atol=1e-5)
 
 
+@pytest.mark.parametrize("heads,dim,slab", [(8, 32, 2), (8, 8, 3), (5, 4, 1), (4, 100, 2), (3, 5, 2), (8, 32, 8)])
+@pytest.mark.parametrize("flavour", ["example", "stable"])
+def test_gat_aggregate_head_slabs_bitwise(heads, dim, slab, flavour):
+    """The fused kernel in passes of `slab` heads (what it does by itself once the gathered operand outgrows the L2;
+    forced here through dglb200_set_tuning): output, per-edge attention and z bit-identical to the single pass -
+    heads are independent and a row's accumulation order does not change.  (3, 5, 2) / (4, 100, 2): the scalar and the
+    vector path with a ragged last slab."""
+    from dgl_b200 import _lib, ops
+    n = 240
+    src, dst = random_graph(n, 2800, heads * 3 + dim, hubs=2, hub_deg=300)
+    loops = np.arange(n, dtype=np.int64)
+    src, dst = np.concatenate([src, loops]), np.concatenate([dst, loops])
+    rng = np.random.RandomState(slab)
+    a1 = torch.from_numpy(rng.randn(n, heads).astype(np.float32)).cuda()
+    a2 = torch.from_numpy(rng.randn(n, heads).astype(np.float32)).cuda()
+    ft = torch.from_numpy(rng.randn(n, heads, dim).astype(np.float32)).cuda()
+    csr = _csr(src, dst, n)
+    fl = ops.SOFTMAX_GAT_EXAMPLE if flavour == "example" else ops.SOFTMAX_STABLE
+    lib = _lib.get_lib()
+    one = ops.gat_aggregate(csr, a1, a2, ft, 0.2, fl)
+    l0 = _lib.launch_count()
+    try:
+        _lib.check_call(lib.dglb200_set_tuning(b"gat_head_slab", slab))
+        got = ops.gat_aggregate(csr, a1, a2, ft, 0.2, fl)
+        launches = _lib.launch_count() - l0
+    finally:
+        _lib.check_call(lib.dglb200_set_tuning(b"gat_head_slab", 0))
+    assert launches == -(-heads // slab)                       # one launch per head slab
+    for a, b in zip(got, one):
+        assert torch.equal(a, b)
+
+
 BUCKET_CASES = [(10, 17, 0, 0), (50, 400, 1, 10), (1000, 20000, 2, 300), (5, 0, 3, 5),
                 (30000, 200000, 4, 1000), (7, 3000, 5, 0)]
 

@@ -204,6 +204,8 @@ def test_edge_softmax_and_gat_kernels(emu):
     t_sddmm.test_edge_softmax_fwd_bwd(3)
     t_sddmm.test_gat_aggregate(2, 5, "example")
     t_sddmm.test_gat_aggregate(8, 8, "stable")
+    t_sddmm.test_gat_aggregate_head_slabs_bitwise(8, 8, 3, "stable")
+    t_sddmm.test_gat_aggregate_head_slabs_bitwise(5, 4, 1, "example")
 
 
 def test_bucketing_and_unique_kernels(emu):
