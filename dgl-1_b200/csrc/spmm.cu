@@ -209,7 +209,14 @@ static int run_spmm(SpmmArgs a, int msg, int red, int dtype, const dglb200_spmm_
   // two heads (a power-of-two number of 16-byte chunks dividing D), the scalar-weight kernel runs
   // with w[e, head of the pass]; otherwise the per-chunk / generic variants take over.
   a.w_slab_scalar = 0;
-  if (vec && msg == DGLB200_MSG_SRC_MUL_EDGE && a.w_mode == kWGrouped && a.w_group % full_vec == 0) {
+  // Which of the two wins is a matter of passes: a scalar-weight pass reads a whole 32-byte sector of the (E, H)
+  // weights per edge for ONE float, and a head of 4 chunks means 8 such passes at 8 heads.  C2 size, 8 heads
+  // (scripts/head_pass_probe.py): dim 16 - 10.2 ms scalar passes vs 7.7 ms chunk weights over the usual slabs;
+  // dim 32 - 13.0 vs 15.3 ms.  So: scalar passes from 8 chunks per head up ("spmm_head_pass" 1 / 2 forces either).
+  const int64_t head_chunks_all = a.w_group / full_vec;
+  const bool scalar_passes = spmm_tuning().head_pass == 1 || (spmm_tuning().head_pass == 0 && head_chunks_all >= 8);
+  if (vec && msg == DGLB200_MSG_SRC_MUL_EDGE && a.w_mode == kWGrouped && a.w_group % full_vec == 0 &&
+      scalar_passes) {
     const int64_t head_chunks = a.w_group / full_vec;
     const int cap = a.slab_chunks > 0 ? a.slab_chunks : 64;
     int p = 64;
@@ -288,6 +295,7 @@ int dglb200_set_tuning(const char* key, int64_t value) {
   else if (k == "spmm_slab_chunks") t.slab_chunks = (int)value;
   else if (k == "spmm_threads") t.threads = (int)value;
   else if (k == "spmm_rows_per_group") t.rows_per_group = (int)value;
+  else if (k == "spmm_head_pass") t.head_pass = (int)value;
   else if (k == "peer_push_tma") set_peer_push_tma((int)value);
   else if (k == "sddmm_dot_generic") set_sddmm_dot_generic((int)value);
   else if (k == "gat_head_slab") set_gat_head_slab((int)value);

@@ -498,6 +498,8 @@ struct SpmmTuning {
   int slab_chunks = 0;  // 16-byte chunks of a row per pass: 16, 32 or 64 (0 = auto)
   int threads = 0;      // CTA size: 128, 256 or 512 (0 = auto)
   int rows_per_group = 0;  // row steps per group (0 = auto from the mean degree)
+  int head_pass = 0;    // per-head weights: 0 = auto, 1 = one head (or less) per pass with a scalar weight,
+                        // 2 = the usual slabs with a weight per 16-byte chunk
 };
 SpmmTuning& spmm_tuning();
 

@@ -70,7 +70,8 @@ int dglb200_device_cc(void);
  * (CTA size: 128,256,512); value 0 restores the automatic choice.  Only the fp32 vectorised
  * copy_src->sum kernel honours them.  "sddmm_dot_generic" = 1 keeps the SDDMM DOT on its generic slot-group
  * kernel; "gat_head_slab" = heads per pass of the fused GAT kernel (0 = one pass; slabs measured slower,
- * see csrc/sddmm.cu).  Results never depend on the knobs.
+ * see csrc/sddmm.cu); "spmm_head_pass" = 1 / 2: per-head edge weights as scalar-weight passes of one head / as
+ * chunk weights over the usual slabs (0 = automatic by head width).  Results never depend on the knobs.
  */
 int dglb200_set_tuning(const char* key, int64_t value);
 

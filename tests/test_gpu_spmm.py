@@ -346,6 +346,32 @@ def test_ragged_width_takes_padded_vector_path(feat, dtype):
         _close(dx, oracle.spmm_grad(src, dst, n, x, w), rtol)
 
 
+@pytest.mark.parametrize("heads,dim", [(8, 16), (4, 32), (8, 4), (2, 64)])
+def test_per_head_weight_routes_agree_bitwise(heads, dim):
+    """Per-head edge weights (E, H) as scalar-weight passes of one head (dglb200_set_tuning "spmm_head_pass" 1) and as
+    chunk weights over the usual slabs (2): same products in the same order, same bits; both equal the oracle."""
+    from dgl_b200 import _lib, ops
+    n, feat = 240, heads * dim
+    src, dst = random_graph(n, 3200, heads * 5 + dim, hubs=2, hub_deg=600, zero_deg_frac=0.2)
+    rng = np.random.RandomState(dim)
+    x = rng.randn(n, heads, dim).astype(np.float32)
+    w = rng.rand(len(src), heads, 1).astype(np.float32)
+    csr = _csr(src, dst, n)
+    xt = torch.from_numpy(x.reshape(n, feat)).cuda()
+    wt = torch.from_numpy(w.reshape(len(src), heads)).cuda()
+    lib = _lib.get_lib()
+    got = []
+    try:
+        for mode in (1, 2, 0):
+            _lib.check_call(lib.dglb200_set_tuning(b"spmm_head_pass", mode))
+            got.append(ops.spmm(csr, ops.MSG_SRC_MUL_EDGE, ops.RED_SUM, x=xt, w=wt, w_width=heads, chunk=32)[0])
+    finally:
+        _lib.check_call(lib.dglb200_set_tuning(b"spmm_head_pass", 0))
+    assert torch.equal(got[0], got[1]) and torch.equal(got[0], got[2])
+    want = oracle.update_all(src, dst, n, "src_mul_edge", "sum", x=x, w=w).reshape(n, feat)
+    np.testing.assert_allclose(got[0].cpu().numpy(), want, rtol=1e-5, atol=1e-5 * np.abs(want).max())
+
+
 @pytest.mark.parametrize("heads,dim", [(8, 8), (4, 32), (8, 3), (2, 4)])
 def test_multi_head_weights_max_bf16_gradient(heads, dim):
     """(E, H, 1) weights against (N, H, D) features - the multi-head attention case
