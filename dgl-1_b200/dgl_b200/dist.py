@@ -59,6 +59,7 @@ SPLIT_LOCAL = bool(int(os.environ.get("DGL_B200_SPLIT_LOCAL", "1")))
 # up to 2 ranks, 128 beyond - measured on C2 x 8 (ms/step): 64 -> 2.49, 128 -> 2.12, 256 (one push) -> 2.16: at 8
 # ranks an op is ~1 ms and the per-slab launches (push, wait, SpMM, fix-up) start to bound it
 ALLGATHER_SLAB = int(os.environ.get("DGL_B200_AG_SLAB", "0"))
+ALLGATHER_SLABS = os.environ.get("DGL_B200_AG_SLABS", "")       # e.g. "64,192": widths that sum to the feature width
 
 
 def chunk_fractions(chunks):
@@ -403,8 +404,17 @@ class RowPartition(object):
     def _slabs(self, feat, dtype):
         """Column blocks [(s0, width)] of the pipelined push all-gather: the SpMM's own L2 slab width
         (64 fp32 at C2), so that the per-slab launches do the work of the one slabbed launch."""
+        es = torch.empty(0, dtype=dtype).element_size()
+        if ALLGATHER_SLABS:               # explicit, possibly unequal widths (a narrow first slab lands sooner)
+            ws = [int(v) for v in ALLGATHER_SLABS.split(",")]
+            if sum(ws) == feat and all(v > 0 and (v * es) % 16 == 0 for v in ws):
+                out, s0 = [], 0
+                for v in ws:
+                    out.append((s0, v))
+                    s0 += v
+                return out
         w = ALLGATHER_SLAB if ALLGATHER_SLAB > 0 else (64 if self.world <= 2 else 128)
-        if w <= 0 or feat <= w or feat % w or (w * torch.empty(0, dtype=dtype).element_size()) % 16:
+        if w <= 0 or feat <= w or feat % w or (w * es) % 16:
             return [(0, feat)]
         return [(s0, w) for s0 in range(0, feat, w)]
 
