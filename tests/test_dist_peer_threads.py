@@ -210,13 +210,17 @@ def test_halo_partition_peer_transports(peers, monkeypatch, mode, chunks, wire):
     assert sum(s[0] for s in stats) > 0              # there was a halo to exchange
 
 
-@pytest.mark.parametrize("mode,feat,slab", [("signal", 8, 4), ("signal", 8, 64), ("signal", 5, 64), ("push", 8, 64)])
+@pytest.mark.parametrize("mode,feat,slab", [("signal", 8, 4), ("signal", 8, 64), ("signal", 5, 64), ("push", 8, 64),
+                                            ("signal", 16, "4,12")])
 def test_row_partition_peer_all_gather(peers, monkeypatch, mode, feat, slab):
     """RowPartition over peer memory: the slab-pipelined push + flag signals (4-wide slabs of an 8-wide
     row, one slab, a width the 16-byte push cannot move -> barrier transport) and round 1's block copies."""
     from dgl_b200 import dist as dmod
     monkeypatch.setattr(dmod, "PULL_MODE", mode)
-    monkeypatch.setattr(dmod, "ALLGATHER_SLAB", slab)
+    if isinstance(slab, str):                    # explicit unequal slab widths (DGL_B200_AG_SLABS)
+        monkeypatch.setattr(dmod, "ALLGATHER_SLABS", slab)
+    else:
+        monkeypatch.setattr(dmod, "ALLGATHER_SLAB", slab)
     world, n = 3, 70
     csr_in, csr_out = _graph(n, 500, 9)
     gen = torch.Generator().manual_seed(2)
