@@ -177,6 +177,113 @@ int pf_out_degrees(RefValue* a, int* c, int n, void* ret, void*) {
   return degrees_of_vids(a, c, n, ret, false, "graph_index._CAPI_DGLGraphOutDegrees[b200]");
 }
 
+// ---- _CAPI_DGLGraphFindEdges (handle, eids) -> {src, dst, eid} (Graph::FindEdges, graph.cc:252-282) ------------
+int pf_find_edges(RefValue* a, int* c, int n, void* ret, void*) {
+  const char* who = "graph_index._CAPI_DGLGraphFindEdges[b200]";
+  if (n != 2) { set_error("expects (handle, eids)"); return fail(who); }
+  const RefDLTensor* ids = static_cast<const RefDLTensor*>(a[1].v_handle);
+  if (!(c[1] == kRefArrayHandle || c[1] == kRefNDArrayContainer) || !valid_ids(ids)) {
+    set_error("Invalid edge id array.");
+    return fail(who);
+  }
+  DevIndex* ix = get_index(as_ptr(a[0], c[0]));
+  if (ix == nullptr) return fail(who);
+  const int64_t k = ids->shape[0];
+  DevMem d_e, d_s, d_d, d_bad;
+  if (d_e.alloc((size_t)k * 8) || d_s.alloc((size_t)k * 8) || d_d.alloc((size_t)k * 8) || d_bad.alloc(8)) {
+    set_error("cudaMalloc failed");
+    return fail(who);
+  }
+  cudaMemset(d_bad.p, 0, 8);
+  if (k > 0) cudaMemcpy(d_e.p, (char*)ids->data + ids->byte_offset, (size_t)k * 8, cudaMemcpyHostToDevice);
+  // one 8-byte row gather per endpoint array; an id outside [0, E) raises the flag ("invalid edge id", graph.cc:266)
+  if (k > 0 && (dglb200_gather_rows(k, d_e.as<int64_t>(), ix->e, ix->src.p, 8, d_s.p, d_bad.as<int32_t>(), nullptr) != 0 ||
+                dglb200_gather_rows(k, d_e.as<int64_t>(), ix->e, ix->dst.p, 8, d_d.p, d_bad.as<int32_t>(), nullptr) != 0))
+    return fail(who);
+  int32_t bad = 0;
+  cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost);
+  if (bad != 0) {
+    set_error("invalid edge id: an id is outside [0, %lld)", (long long)ix->e);
+    return fail(who);
+  }
+  ArrayList* res = new ArrayList();
+  RefDLTensor* eid = cpu_ids(k);
+  if (eid && k > 0) memcpy(eid->data, (char*)ids->data + ids->byte_offset, (size_t)k * 8);
+  res->arr = {from_device(d_s.as<int64_t>(), k), from_device(d_d.as<int64_t>(), k), eid};
+  if (return_list(res, ret) != 0) return fail(who);
+  return 0;
+}
+
+// ---- _CAPI_DGLGraphEdgeIds (handle, src, dst) -> {src, dst, eid}: every edge between the pairs, a pair's edges in
+// ascending edge id (Graph::EdgeIds, graph.cc:204-249; one side may be a single id that is broadcast) -----------
+int pf_edge_ids(RefValue* a, int* c, int n, void* ret, void*) {
+  const char* who = "graph_index._CAPI_DGLGraphEdgeIds[b200]";
+  if (n != 3) { set_error("expects (handle, src, dst)"); return fail(who); }
+  const RefDLTensor* us = static_cast<const RefDLTensor*>(a[1].v_handle);
+  const RefDLTensor* vs = static_cast<const RefDLTensor*>(a[2].v_handle);
+  const bool arr = (c[1] == kRefArrayHandle || c[1] == kRefNDArrayContainer) &&
+                   (c[2] == kRefArrayHandle || c[2] == kRefNDArrayContainer);
+  if (!arr || !valid_ids(us) || !valid_ids(vs)) { set_error("Invalid src / dst id array."); return fail(who); }
+  const int64_t nu = us->shape[0], nv = vs->shape[0];
+  if (!(nu == nv || nu == 1 || nv == 1)) { set_error("Invalid src and dst id array."); return fail(who); }
+  DevIndex* ix = get_index(as_ptr(a[0], c[0]));
+  if (ix == nullptr) return fail(who);
+  const int64_t* hu = reinterpret_cast<const int64_t*>((char*)us->data + us->byte_offset);
+  const int64_t* hv = reinterpret_cast<const int64_t*>((char*)vs->data + vs->byte_offset);
+  const int64_t k = (nu == 0 || nv == 0) ? 0 : (nu > nv ? nu : nv);
+  std::vector<int64_t> pu((size_t)k), pv((size_t)k);
+  for (int64_t i = 0; i < k; ++i) {
+    pu[i] = hu[nu == 1 ? 0 : i];
+    pv[i] = hv[nv == 1 ? 0 : i];
+    if (pv[i] < 0 || pv[i] >= ix->n) {                  // the source side is range-checked by the select below
+      set_error("invalid edge: %lld -> %lld", (long long)pu[i], (long long)pv[i]);
+      return fail(who);
+    }
+  }
+  // the out-edge lists of the sources on the device (slots of a row are in ascending edge id), then keep the slots
+  // whose destination is the pair's
+  size_t ws_bytes = 0;
+  dglb200_csr_select_workspace_bytes(k, &ws_bytes);
+  DevMem d_u, d_off, ws, d_which, d_col, d_eid;
+  if (d_u.alloc((size_t)k * 8) || d_off.alloc((size_t)(k + 1) * 8) || ws.alloc(ws_bytes)) { set_error("cudaMalloc failed"); return fail(who); }
+  if (k > 0) cudaMemcpy(d_u.p, pu.data(), (size_t)k * 8, cudaMemcpyHostToDevice);
+  int64_t total = 0;
+  if (dglb200_csr_select_offsets(k, d_u.as<int64_t>(), ix->n, ix->out.ptr.as<int64_t>(), d_off.as<int64_t>(), &total,
+                                 ws.p, ws_bytes, nullptr) != 0)
+    return fail(who);
+  if (d_which.alloc((size_t)total * 8) || d_col.alloc((size_t)total * 8) || d_eid.alloc((size_t)total * 8)) {
+    set_error("cudaMalloc failed");
+    return fail(who);
+  }
+  if (dglb200_csr_select_expand(k, total, d_u.as<int64_t>(), d_off.as<int64_t>(), ix->out.ptr.as<int64_t>(),
+                                ix->out.idx.as<int32_t>(), ix->out.eid.as<int32_t>(), d_which.as<int64_t>(), nullptr,
+                                nullptr, d_col.as<int64_t>(), d_eid.as<int64_t>(), nullptr) != 0)
+    return fail(who);
+  std::vector<int64_t> which((size_t)total), col((size_t)total), eid((size_t)total);
+  if (total > 0 && (cudaMemcpy(which.data(), d_which.p, (size_t)total * 8, cudaMemcpyDeviceToHost) != cudaSuccess ||
+                    cudaMemcpy(col.data(), d_col.p, (size_t)total * 8, cudaMemcpyDeviceToHost) != cudaSuccess ||
+                    cudaMemcpy(eid.data(), d_eid.p, (size_t)total * 8, cudaMemcpyDeviceToHost) != cudaSuccess)) {
+    set_error("cudaMemcpy D2H failed");
+    return fail(who);
+  }
+  std::vector<int64_t> rs, rd, re;
+  for (int64_t p = 0; p < total; ++p)
+    if (col[p] == pv[which[p]]) {
+      rs.push_back(pu[which[p]]);
+      rd.push_back(col[p]);
+      re.push_back(eid[p]);
+    }
+  ArrayList* res = new ArrayList();
+  const int64_t m = (int64_t)rs.size();
+  RefDLTensor* out[3] = {cpu_ids(m), cpu_ids(m), cpu_ids(m)};
+  const std::vector<int64_t>* srcs[3] = {&rs, &rd, &re};
+  for (int i = 0; i < 3; ++i)
+    if (out[i] && m > 0) memcpy(out[i]->data, srcs[i]->data(), (size_t)m * 8);
+  res->arr = {out[0], out[1], out[2]};
+  if (return_list(res, ret) != 0) return fail(who);
+  return 0;
+}
+
 // ---- mutators: drop the cached index, then the reference's original -----------------------------------
 // forward a call to one of libdgl's originals and hand its return value on (our reference is released)
 int forward_call(void* original, RefValue* a, int* c, int n, void* ret) {
@@ -261,6 +368,8 @@ int register_graph_overrides() {
       {"graph_index._CAPI_DGLGraphEdges", pf_edges},
       {"graph_index._CAPI_DGLGraphInDegrees", pf_in_degrees},
       {"graph_index._CAPI_DGLGraphOutDegrees", pf_out_degrees},
+      {"graph_index._CAPI_DGLGraphFindEdges", pf_find_edges},
+      {"graph_index._CAPI_DGLGraphEdgeIds", pf_edge_ids},
   };
   const int n_sampling = register_sampling_overrides();      // also resolves g_sorig.is_readonly used below
   if (n_sampling < 0) return -1;

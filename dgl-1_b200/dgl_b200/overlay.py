@@ -13,7 +13,7 @@ builtin message-passing path (SURVEY.md 8b "who calls it") are patched in place,
      incidence_matrix, python/dgl/graph_index.py:537-662) need no patch of their own: they reach the engine
      through 1. (F.copy_to of the index to the device + F.sparse_matrix);
   4. the PackedFunc globals (`runtime.degree_bucketing._CAPI_DGLDegreeBucketing`,
-     `graph_index._CAPI_DGLGraph{GetAdj,InEdges_2,OutEdges_2,Edges,InDegrees,OutDegrees}`) are overridden
+     `graph_index._CAPI_DGLGraph{GetAdj,InEdges_2,OutEdges_2,Edges,InDegrees,OutDegrees,FindEdges,EdgeIds}`) are overridden
      and `graph_index._CAPI_DGLGraphUniformSampling{,2,..,128}` (the neighbour sampler) are overridden
      inside the loaded libdgl.so by dglb200_register_packed_funcs (csrc/packed.cu, packed_graph.cu,
      packed_sampling.cuh).  The reference's Python holds COPIES of the PackedFuncs taken at import
@@ -171,7 +171,7 @@ def install(dgl_mod=None, register_packed=True, override_reference=True):
 # global names dglb200_register_packed_funcs overrides -> the module attribute that caches each
 _OVERRIDDEN = (["runtime.degree_bucketing._CAPI_DGLDegreeBucketing"] +
                ["graph_index._CAPI_DGLGraph" + n for n in
-                ("GetAdj", "InEdges_2", "OutEdges_2", "Edges", "InDegrees", "OutDegrees", "AddVertices", "AddEdge",
+                ("GetAdj", "InEdges_2", "OutEdges_2", "Edges", "InDegrees", "OutDegrees", "FindEdges", "EdgeIds", "AddVertices", "AddEdge",
                  "AddEdges", "Clear", "Free")] +
                ["graph_index._CAPI_DGLGraphUniformSampling" + k for k in ("", "2", "4", "8", "16", "32", "64", "128")])
 

@@ -187,6 +187,17 @@ def graph_edges(g, order=""):
     return _edge_array("graph_index._CAPI_DGLGraphEdges", g.handle, order)
 
 
+def graph_find_edges(g, eids):
+    """Graph::FindEdges(eids) -> (src, dst, eid), src/graph/graph.cc:252-282."""
+    return _edge_array("graph_index._CAPI_DGLGraphFindEdges", g.handle, np.asarray(eids, np.int64))
+
+
+def graph_edge_ids(g, u, v):
+    """Graph::EdgeIds(src, dst) -> (src, dst, eid): every edge between the pairs, src/graph/graph.cc:204-249."""
+    rst = get_global("graph_index._CAPI_DGLGraphEdgeIds")(g.handle, np.asarray(u, np.int64), np.asarray(v, np.int64))
+    return rst(0), rst(1), rst(2)
+
+
 def graph_out_degrees(g, v):
     return get_global("graph_index._CAPI_DGLGraphOutDegrees")(g.handle, np.asarray(v, np.int64))
 

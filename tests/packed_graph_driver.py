@@ -39,7 +39,7 @@ def load(mode):
     return lib
 
 
-def queries(g, n, vids):
+def queries(g, n, vids, readonly=False):
     out = {}
     for tr in (False, True):
         out["csr%d" % tr] = g.get_adj_csr(tr)
@@ -50,6 +50,14 @@ def queries(g, n, vids):
     s, d, e = ref_ffi.graph_edges(g, "srcdst")
     order = np.lexsort((e, d, s))            # the reference's std::sort leaves parallel edges unordered
     out["edges_srcdst"] = (s[order], d[order], e[order])
+    ne = len(out["edges"][0])
+    pick = np.array([0, ne - 1, ne // 2, ne // 2, 3 % ne], np.int64)
+    es, ed = out["edges"][0], out["edges"][1]
+    if not readonly:                      # FindEdges is mutable-graph only (immutable_graph.h:270); Edges("") is in
+        out["find_edges"] = ref_ffi.graph_find_edges(g, pick)                          # edge-id order only there
+        out["edge_ids_pairs"] = ref_ffi.graph_edge_ids(g, es[pick], ed[pick])          # incl. parallel edges
+        out["edge_ids_bcast_src"] = ref_ffi.graph_edge_ids(g, es[pick[:1]], vids)
+        out["edge_ids_bcast_dst"] = ref_ffi.graph_edge_ids(g, vids, ed[pick[:1]])
     out["in_deg"] = (g.in_degrees(vids),)
     out["out_deg"] = (ref_ffi.graph_out_degrees(g, vids),)
     return out
@@ -106,7 +114,7 @@ def main():
     check_sampling(ro, ro_src, ro_dst, ro_n, cases, None)                  # the unmodified reference passes
     want_samples = [ref_ffi.graph_uniform_sampling(ro, s, t, h, f, want_graph=True) for s, t, f, h in cases]
     ro_vids = np.array([3, 0, 17, 399], np.int64)
-    want_ro = queries(ro, ro_n, ro_vids)
+    want_ro = queries(ro, ro_n, ro_vids, readonly=True)
     n = 300
     src, dst = random_graph(n, 4000, 7, hubs=3, hub_deg=500, zero_deg_frac=0.2)
     rng = np.random.RandomState(0)
@@ -122,7 +130,7 @@ def main():
 
     l0 = lib.dglb200_launch_count()
     k = lib.dglb200_register_packed_funcs(ctypes.c_void_p(ref_ffi.lib()._handle), 1)
-    assert k >= 25, (k, lib.dglb200_last_error())            # 5 + 6 queries + 5 mutators + 8 sampling + bucketing
+    assert k >= 27, (k, lib.dglb200_last_error())            # 5 + 8 queries + 5 mutators + 8 sampling + bucketing
     got, got_tiny = queries(g, n, vids), queries(tiny, 4, tv)
     assert lib.dglb200_launch_count() > l0, "the overrides launched no kernel"
     same(want, got, "300-node multigraph")
@@ -146,6 +154,9 @@ def main():
     # errors travel through the reference's convention
     for bad_call in (lambda: g.in_degrees(np.array([n + 5], np.int64)),
                      lambda: ref_ffi.graph_in_edges(g, np.array([-1], np.int64)),
+                     lambda: ref_ffi.graph_find_edges(g, np.array([0, 10 ** 7], np.int64)),
+                     lambda: ref_ffi.graph_edge_ids(g, np.array([0, 1, 2], np.int64), np.array([0, 1], np.int64)),
+                     lambda: ref_ffi.graph_edge_ids(g, np.array([0], np.int64), np.array([n + 3], np.int64)),
                      lambda: ref_ffi.get_global("graph_index._CAPI_DGLGraphGetAdj")(g.handle, False, "xyz")):
         try:
             bad_call()
@@ -160,7 +171,7 @@ def main():
     l1 = lib.dglb200_launch_count()
     check_sampling(ro, ro_src, ro_dst, ro_n, cases, want_samples)
     assert lib.dglb200_launch_count() > l1 + 50, "the sampling overrides launched no kernel"
-    same(want_ro, queries(ro, ro_n, ro_vids), "read-only graph (pass-through)")
+    same(want_ro, queries(ro, ro_n, ro_vids, readonly=True), "read-only graph (pass-through)")
     for bad_call in (lambda: ref_ffi.graph_uniform_sampling(ro, [np.array([ro_n + 1], np.int64)], "in", 1, 2),
                      lambda: ref_ffi.graph_uniform_sampling(ref_ffi.RefGraph(ro_src, ro_dst, ro_n), [ro_vids], "in", 1, 2)):
         try:
