@@ -4,6 +4,7 @@
 //   graph_index._CAPI_DGLGraphEdges       (:308)
 //   graph_index._CAPI_DGLGraphInDegrees   (:324)      graph_index._CAPI_DGLGraphOutDegrees  (:340)
 //   graph_index._CAPI_DGLGraphFindEdges   (:268)      graph_index._CAPI_DGLGraphEdgeIds     (:259)
+//   graph_index._CAPI_DGLGraphInEdges_1 / OutEdges_1 (:276,292)   InDegree / OutDegree (:316,332)
 // Same arity, same argument types (graph handle, CPU int64 id arrays, strings), same return order
 // (indexed PackedFunc getters over CPU int64 NDArrays), so python/dgl/graph_index.py needs no change.
 // The answers come from CSRs that live on the GPU: the first query on a graph handle fetches its edge

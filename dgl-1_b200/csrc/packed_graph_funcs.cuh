@@ -177,6 +177,50 @@ int pf_out_degrees(RefValue* a, int* c, int n, void* ret, void*) {
   return degrees_of_vids(a, c, n, ret, false, "graph_index._CAPI_DGLGraphOutDegrees[b200]");
 }
 
+// ---- single-vertex forms (handle, vid): _CAPI_DGLGraphInEdges_1 / OutEdges_1 (graph_apis.cc:276,292) return the
+// same three arrays, _CAPI_DGLGraphInDegree / OutDegree (:316,332) an integer.  The id becomes a 1-element array.
+struct OneId {
+  int64_t id, shape;
+  RefDLTensor t;
+  explicit OneId(int64_t v) : id(v), shape(1) {
+    t = RefDLTensor{&id, 1, 0, 1, 0, 64, 1, &shape, nullptr, 0};
+  }
+};
+int edges_of_one(RefValue* a, int* c, int n, void* ret, bool in_edges, const char* who) {
+  if (n != 2) { set_error("expects (handle, vid)"); return fail(who); }
+  OneId one(as_int(a[1], c[1]));
+  RefValue b[2] = {a[0], RefValue()};
+  b[1].v_handle = &one.t;
+  int bc[2] = {c[0], kRefArrayHandle};
+  return edges_of(b, bc, 2, ret, in_edges, who);
+}
+int pf_in_edges_1(RefValue* a, int* c, int n, void* ret, void*) {
+  return edges_of_one(a, c, n, ret, true, "graph_index._CAPI_DGLGraphInEdges_1[b200]");
+}
+int pf_out_edges_1(RefValue* a, int* c, int n, void* ret, void*) {
+  return edges_of_one(a, c, n, ret, false, "graph_index._CAPI_DGLGraphOutEdges_1[b200]");
+}
+int degree_of_one(RefValue* a, int* c, int n, void* ret, bool in_deg, const char* who) {
+  if (n != 2) { set_error("expects (handle, vid)"); return fail(who); }
+  DevIndex* ix = get_index(as_ptr(a[0], c[0]));
+  if (ix == nullptr) return fail(who);
+  const int64_t v = as_int(a[1], c[1]);
+  if (v < 0 || v >= ix->n) { set_error("Invalid vertex: %lld", (long long)v); return fail(who); }   // graph.cc:404
+  const DevCsr& csr = in_deg ? ix->in : ix->out;
+  int64_t pair[2] = {0, 0};
+  if (cudaMemcpy(pair, csr.ptr.as<int64_t>() + v, 16, cudaMemcpyDeviceToHost) != cudaSuccess) {
+    set_error("cudaMemcpy D2H failed");
+    return fail(who);
+  }
+  return ret_int(ret, pair[1] - pair[0]);
+}
+int pf_in_degree(RefValue* a, int* c, int n, void* ret, void*) {
+  return degree_of_one(a, c, n, ret, true, "graph_index._CAPI_DGLGraphInDegree[b200]");
+}
+int pf_out_degree(RefValue* a, int* c, int n, void* ret, void*) {
+  return degree_of_one(a, c, n, ret, false, "graph_index._CAPI_DGLGraphOutDegree[b200]");
+}
+
 // ---- _CAPI_DGLGraphFindEdges (handle, eids) -> {src, dst, eid} (Graph::FindEdges, graph.cc:252-282) ------------
 int pf_find_edges(RefValue* a, int* c, int n, void* ret, void*) {
   const char* who = "graph_index._CAPI_DGLGraphFindEdges[b200]";
@@ -368,6 +412,10 @@ int register_graph_overrides() {
       {"graph_index._CAPI_DGLGraphEdges", pf_edges},
       {"graph_index._CAPI_DGLGraphInDegrees", pf_in_degrees},
       {"graph_index._CAPI_DGLGraphOutDegrees", pf_out_degrees},
+      {"graph_index._CAPI_DGLGraphInEdges_1", pf_in_edges_1},
+      {"graph_index._CAPI_DGLGraphOutEdges_1", pf_out_edges_1},
+      {"graph_index._CAPI_DGLGraphInDegree", pf_in_degree},
+      {"graph_index._CAPI_DGLGraphOutDegree", pf_out_degree},
       {"graph_index._CAPI_DGLGraphFindEdges", pf_find_edges},
       {"graph_index._CAPI_DGLGraphEdgeIds", pf_edge_ids},
   };

@@ -171,7 +171,8 @@ def install(dgl_mod=None, register_packed=True, override_reference=True):
 # global names dglb200_register_packed_funcs overrides -> the module attribute that caches each
 _OVERRIDDEN = (["runtime.degree_bucketing._CAPI_DGLDegreeBucketing"] +
                ["graph_index._CAPI_DGLGraph" + n for n in
-                ("GetAdj", "InEdges_2", "OutEdges_2", "Edges", "InDegrees", "OutDegrees", "FindEdges", "EdgeIds", "AddVertices", "AddEdge",
+                ("GetAdj", "InEdges_2", "OutEdges_2", "Edges", "InDegrees", "OutDegrees", "FindEdges", "EdgeIds", "InEdges_1",
+                 "OutEdges_1", "InDegree", "OutDegree", "AddVertices", "AddEdge",
                  "AddEdges", "Clear", "Free")] +
                ["graph_index._CAPI_DGLGraphUniformSampling" + k for k in ("", "2", "4", "8", "16", "32", "64", "128")])
 

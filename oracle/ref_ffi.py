@@ -187,6 +187,17 @@ def graph_edges(g, order=""):
     return _edge_array("graph_index._CAPI_DGLGraphEdges", g.handle, order)
 
 
+def graph_edges_of_one(g, v, out=False):
+    """Graph::InEdges(vid) / OutEdges(vid) -> (src, dst, eid), src/graph/graph.cc:284-292, 330-338."""
+    rst = get_global("graph_index._CAPI_DGLGraph%sEdges_1" % ("Out" if out else "In"))(g.handle, int(v))
+    return rst(0), rst(1), rst(2)
+
+
+def graph_degree_of_one(g, v, out=False):
+    """Graph::InDegree(vid) / OutDegree(vid), src/graph/graph.cc:402-409, 427-431."""
+    return get_global("graph_index._CAPI_DGLGraph%sDegree" % ("Out" if out else "In"))(g.handle, int(v))
+
+
 def graph_find_edges(g, eids):
     """Graph::FindEdges(eids) -> (src, dst, eid), src/graph/graph.cc:252-282."""
     return _edge_array("graph_index._CAPI_DGLGraphFindEdges", g.handle, np.asarray(eids, np.int64))

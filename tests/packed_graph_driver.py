@@ -58,6 +58,10 @@ def queries(g, n, vids, readonly=False):
         out["edge_ids_pairs"] = ref_ffi.graph_edge_ids(g, es[pick], ed[pick])          # incl. parallel edges
         out["edge_ids_bcast_src"] = ref_ffi.graph_edge_ids(g, es[pick[:1]], vids)
         out["edge_ids_bcast_dst"] = ref_ffi.graph_edge_ids(g, vids, ed[pick[:1]])
+    for v in (int(vids[0]), int(vids[-1]), n - 1):          # single-vertex forms (ids that repeat, a zero-degree tail node)
+        out["in_edges_1_%d" % v] = ref_ffi.graph_edges_of_one(g, v)
+        out["out_edges_1_%d" % v] = ref_ffi.graph_edges_of_one(g, v, out=True)
+        out["degree_1_%d" % v] = (np.array([ref_ffi.graph_degree_of_one(g, v), ref_ffi.graph_degree_of_one(g, v, out=True)]),)
     out["in_deg"] = (g.in_degrees(vids),)
     out["out_deg"] = (ref_ffi.graph_out_degrees(g, vids),)
     return out
@@ -130,7 +134,7 @@ def main():
 
     l0 = lib.dglb200_launch_count()
     k = lib.dglb200_register_packed_funcs(ctypes.c_void_p(ref_ffi.lib()._handle), 1)
-    assert k >= 27, (k, lib.dglb200_last_error())            # 5 + 8 queries + 5 mutators + 8 sampling + bucketing
+    assert k >= 31, (k, lib.dglb200_last_error())            # 5 + 12 queries + 5 mutators + 8 sampling + bucketing
     got, got_tiny = queries(g, n, vids), queries(tiny, 4, tv)
     assert lib.dglb200_launch_count() > l0, "the overrides launched no kernel"
     same(want, got, "300-node multigraph")
@@ -155,6 +159,8 @@ def main():
     for bad_call in (lambda: g.in_degrees(np.array([n + 5], np.int64)),
                      lambda: ref_ffi.graph_in_edges(g, np.array([-1], np.int64)),
                      lambda: ref_ffi.graph_find_edges(g, np.array([0, 10 ** 7], np.int64)),
+                     lambda: ref_ffi.graph_edges_of_one(g, n + 1),
+                     lambda: ref_ffi.graph_degree_of_one(g, -2, out=True),
                      lambda: ref_ffi.graph_edge_ids(g, np.array([0, 1, 2], np.int64), np.array([0, 1], np.int64)),
                      lambda: ref_ffi.graph_edge_ids(g, np.array([0], np.int64), np.array([n + 3], np.int64)),
                      lambda: ref_ffi.get_global("graph_index._CAPI_DGLGraphGetAdj")(g.handle, False, "xyz")):
