@@ -22,7 +22,8 @@ class NSSubgraphLoader(object):
         if not g.is_readonly():
             raise NotImplementedError("subgraph loader only support read-only graphs.")   # sampler.py:24-25
         if node_prob is not None:
-            # GetNonUniformSample (immutable_graph.cc:746-770) draws from an ArrayHeap; not built here
+            # unreachable in the reference too: graph_index.py:674 calls `_nonuniform_sampling`, defined nowhere, and no
+            # PackedFunc is registered for GetNonUniformSample (immutable_graph.cc:746-770; graph_apis.cc:434-472)
             raise NotImplementedError("node_prob: only uniform neighbour sampling runs on the device")
         if neighbor_type not in ("in", "out"):
             raise DGLError("neighbor_type must be 'in' or 'out'")
